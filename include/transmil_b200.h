@@ -1,0 +1,226 @@
+/*
+ * libtransmil_b200 -- C ABI of the B200-native TransMIL bag-level hot path.
+ *
+ * Every entry point is `extern "C"`, takes plain pointers and sizes (no torch
+ * types), launches on the caller's stream and never synchronises the device
+ * unless it says so.  All tensors are fp32, row-major, owned by the caller.
+ * Return value: 0 on success, a negative tm_status otherwise; the text of the
+ * last error on the calling thread is available from tm_last_error().
+ *
+ * Each function cites the reference interface it replaces; paths are relative
+ * to the reference repository root (Ycblue/TransMIL-DeepGraft @ 78f530b).
+ *
+ * Notation: B bags per call, n patches per bag, D = in_features, C = 512,
+ * h = 8 heads, d = 64, m = 256 landmarks, G = ceil(sqrt(n)), N = G*G,
+ * dup = N - n, S = N + 1, l = ceil(S/m), Sp = l*m, P = Sp - S (front pad).
+ */
+#ifndef TRANSMIL_B200_H
+#define TRANSMIL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TM_DIM 512
+#define TM_HEADS 8
+#define TM_DHEAD 64
+#define TM_LANDMARKS 256
+#define TM_PINV_ITERS 6
+#define TM_CONV_TAPS 33
+
+typedef enum tm_status {
+  TM_OK = 0,
+  TM_ERR_BAD_SHAPE = -1,
+  TM_ERR_BAD_ALIGNMENT = -2,
+  TM_ERR_UNSUPPORTED_ARCH = -3,
+  TM_ERR_WORKSPACE_TOO_SMALL = -4,
+  TM_ERR_CUDA = -5,
+  TM_ERR_BAD_ARGUMENT = -6
+} tm_status;
+
+/* fc1 stem variants (code/models/TransMIL.py:100-133). */
+typedef enum tm_fc1_kind {
+  TM_FC1_SINGLE = 0,  /* Linear(D,512) GELU                      TransMIL.py:130-133, MDMIL.py:66 */
+  TM_FC1_2048 = 1,    /* Linear(2048,1024) GELU LN(1024) Linear(1024,512) GELU   TransMIL.py:109-110 */
+  TM_FC1_768 = 2      /* Linear(768,768) GELU LN(768) Linear(768,512) GELU LN(512)  TransMIL.py:123-126 (eval) */
+} tm_fc1_kind;
+
+/* Flags for tm_transmil_fwd / tm_workspace_bytes. */
+#define TM_FLAG_SIMT_ONLY 1u     /* force the fp32 CUDA-core kernels (on-device cross-check of the tensor-core path) */
+#define TM_FLAG_KEEP_STAGES 2u   /* keep per-stage buffers addressable through tm_stage_ptr */
+
+/* Index contract of one bag (TransMIL.py:177-179,184-186,190-193 and the
+ * nystrom-attention 0.0.11 front pad / landmark grouping).  Pure host code. */
+typedef struct tm_plan {
+  int64_t n, G, N, dup, S, l, Sp, P, padding;
+} tm_plan;
+
+/* Parameters of one NystromAttention TransLayer (TransMIL.py:19-57).
+ * Shapes are those of the reference state_dict. */
+typedef struct tm_layer_weights {
+  const float* norm_w;   /* layerX.norm.weight            [512]        */
+  const float* norm_b;   /* layerX.norm.bias              [512]        */
+  const float* qkv_w;    /* layerX.attn.to_qkv.weight     [1536,512]   */
+  const float* out_w;    /* layerX.attn.to_out.0.weight   [512,512]    */
+  const float* out_b;    /* layerX.attn.to_out.0.bias     [512]        */
+  const float* conv_w;   /* layerX.attn.res_conv.weight   [8,1,33,1]   */
+} tm_layer_weights;
+
+/* All parameters of TransMIL (state_dict layout, TransMIL.py:79-155). */
+typedef struct tm_weights {
+  int32_t fc1_kind;      /* tm_fc1_kind */
+  int32_t in_features;   /* D */
+  int32_t n_classes;
+  int32_t reserved;
+  const float* fc1_w0;   /* _fc1.0.weight [F0,D]  (F0 = 512 | 1024 | 768) */
+  const float* fc1_b0;   /* _fc1.0.bias   [F0]    */
+  const float* fc1_ln_w; /* _fc1.2.* (2048) or _fc1.3.* (768): LayerNorm(F0) ; NULL for SINGLE */
+  const float* fc1_ln_b;
+  const float* fc1_w1;   /* _fc1.3.weight (2048) or _fc1.4.weight (768)  [512,F0] ; NULL for SINGLE */
+  const float* fc1_b1;
+  const float* fc1_ln2_w; /* _fc1.7.* (768 only): LayerNorm(512) ; else NULL */
+  const float* fc1_ln2_b;
+  const float* cls_token; /* cls_token [1,1,512] */
+  tm_layer_weights layer1, layer2;
+  const float* ppeg_w7;  /* pos_layer.proj.weight  [512,1,7,7] */
+  const float* ppeg_b7;  /* pos_layer.proj.bias    [512]       */
+  const float* ppeg_w5;  /* pos_layer.proj1.weight [512,1,5,5] */
+  const float* ppeg_b5;
+  const float* ppeg_w3;  /* pos_layer.proj2.weight [512,1,3,3] */
+  const float* ppeg_b3;
+  const float* norm_w;   /* norm.weight [512] */
+  const float* norm_b;
+  const float* fc_w;     /* _fc.weight [n_classes,512] */
+  const float* fc_b;     /* _fc.bias   [n_classes]     */
+} tm_weights;
+
+/* ---- library ---------------------------------------------------------- */
+const char* tm_version(void);
+const char* tm_last_error(void);
+/* 1 when the current device is sm_100 (tcgen05/TMA kernels usable). */
+int tm_device_supported(void);
+/* Number of kernel launches issued by this library on the calling thread
+ * since the last tm_reset_launch_count(). */
+int64_t tm_launch_count(void);
+void tm_reset_launch_count(void);
+
+/* ---- index contract (host only) --------------------------------------- */
+/* TransMIL.py:177-179 (G, N, dup), :184-186 (S), :190-193 (padding);
+ * nystrom-attention forward (l, Sp, P). */
+int tm_make_plan(int64_t n, tm_plan* out);
+/* Source row of token t (0 <= t < N) after the duplicate pad: t < n ? t : t - n.  TransMIL.py:180 */
+int64_t tm_dup_source(const tm_plan* p, int64_t t);
+/* Landmark group of padded row r (0 <= r < Sp): r / l.  nystrom-attention reduce '(n l) d -> n d'. */
+int64_t tm_landmark_group(const tm_plan* p, int64_t r);
+/* Padded row that holds sequence position s (0 = cls, 1.. = tokens): P + s. */
+int64_t tm_padded_row(const tm_plan* p, int64_t s);
+/* PPEG pixel of token t (TransMIL.py:69): y = t / G, x = t % G. */
+void tm_ppeg_pixel(const tm_plan* p, int64_t t, int64_t* y, int64_t* x);
+
+/* ---- whole path -------------------------------------------------------- */
+/* Bytes of device workspace tm_transmil_fwd needs for B bags of n patches. */
+int tm_workspace_bytes(int64_t B, int64_t n, const tm_weights* w, uint32_t flags, size_t* bytes);
+
+/* TransMIL.forward (TransMIL.py:167-211), eval mode, return_attn=False.
+ * x [B,n,D] fp32 (device), logits [B,n_classes] fp32 (device).
+ * The dense [B,8,Sp,Sp] attention is never built. */
+int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n,
+                    float* logits, void* workspace, size_t workspace_bytes,
+                    uint32_t flags, void* stream);
+
+/* Same call with HOST buffers: x_host [B,n,D] (pinned or pageable), logits_host
+ * [B,n_classes].  Copies host->device, runs tm_transmil_fwd, copies the logits
+ * back and synchronises `stream`.  d_x is a caller-owned device staging buffer
+ * of B*n*D floats, d_logits one of B*n_classes floats.  This is the call
+ * ModelInterface.step makes once per slide (code/models/model_interface.py:316-322). */
+int tm_transmil_fwd_host(const tm_weights* w, const float* x_host, int64_t B, int64_t n,
+                         float* logits_host, float* d_x, float* d_logits,
+                         void* workspace, size_t workspace_bytes, uint32_t flags, void* stream);
+
+/* Device pointer of a named stage buffer inside `workspace` after a
+ * tm_transmil_fwd with TM_FLAG_KEEP_STAGES (for parity tests):
+ * "h0" [B,S,512] fc1+pad+cls, "xn" [B,Sp,512] (layer 2's at the end),
+ * "q","k","v" [B,8,Sp,64], "q_lm","k_lm" [B,8,256,64], "attn2","Z" [B,8,256,256],
+ * "W3","M" [B,8,256,64], "merged" [B,Sp,512], "h1","h2","h3" [B,S,512]
+ * (stages of the LAST layer executed unless suffixed "1", e.g. "Z1", "q_lm1"). */
+int tm_stage_ptr(const char* name, int64_t B, int64_t n, const tm_weights* w, uint32_t flags,
+                 void* workspace, void** ptr, int64_t* numel);
+
+/* ---- per-kernel entry points (all device pointers) -------------------- */
+/* K1+K2: _fc1 (TransMIL.py:175) fused with the duplicate pad (:177-180) and the
+ * cls token (:184-186).  x [B,n,D] -> h0 [B,S,512].  scratch: B*n*F0 floats
+ * (unused for TM_FC1_SINGLE). */
+int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n, float* h0,
+               float* scratch, uint32_t flags, void* stream);
+
+/* K3: TransLayer.norm (TransMIL.py:23,47) + the FRONT zero pad of
+ * NystromAttention.forward.  h [B,S,512] -> xn [B,Sp,512] (rows < P zero). */
+int tm_ln_pad_fwd(const float* h, const float* gamma, const float* beta, int64_t B, int64_t S,
+                  int64_t P, float* xn, void* stream);
+
+/* K4: to_qkv (no bias), head split 'b n (h d) -> b h n d', q *= 64^-0.5.
+ * xn [B,Sp,512] -> q,k,v [B,8,Sp,64]. */
+int tm_qkv_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, float* q, float* k,
+               float* v, uint32_t flags, void* stream);
+
+/* K5: landmark means over l consecutive padded rows.  q,k [B,8,Sp,64] -> q_lm,k_lm [B,8,256,64]. */
+int tm_landmarks_fwd(const float* q, const float* k, int64_t B, int64_t Sp, int64_t l,
+                     float* q_lm, float* k_lm, void* stream);
+
+/* K6+K7: attn2 = softmax(q_lm k_lm^T); Z = moore_penrose_iter_pinv(attn2, 6) with
+ * the global (batch x heads) init scalar.  scratch: tm_pinv_scratch_floats(B) floats. */
+int64_t tm_pinv_scratch_floats(int64_t B);
+int tm_pinv_fwd(const float* q_lm, const float* k_lm, int64_t B, float* attn2, float* Z,
+                float* scratch, uint32_t flags, void* stream);
+
+/* K8: W3 = softmax_t(q_lm k^T) v over all Sp padded tokens, flash-style
+ * (the [256,Sp] matrix never reaches HBM).  scratch: tm_attn3v_scratch_floats(). */
+int64_t tm_attn3v_scratch_floats(int64_t B, int64_t Sp);
+int tm_attn3v_fwd(const float* q_lm, const float* k, const float* v, int64_t B, int64_t Sp,
+                  float* W3, float* scratch, uint32_t flags, void* stream);
+
+/* M = Z @ W3  [B,8,256,64]  (re-association of (attn1 @ Z) @ W3). */
+int tm_zw_fwd(const float* Z, const float* W3, int64_t B, float* M, void* stream);
+
+/* K9+K10+K11: merged[b,t,h*64:(h+1)*64] = softmax_j(q_t . k_lm_j) @ M_h + res_conv(v)[t]
+ * (33-tap depthwise conv along the padded token axis, zero outside [0,Sp)).
+ * -> merged [B,Sp,512] ('b h n d -> b n (h d)'). */
+int tm_nystrom_out_fwd(const float* q, const float* k_lm, const float* M, const float* v,
+                       const float* conv_w, int64_t B, int64_t Sp, float* merged,
+                       uint32_t flags, void* stream);
+
+/* K12: to_out Linear(512,512)+bias on rows [P,Sp) of merged (the `[:, -S:]` slice),
+ * plus the TransLayer residual (TransMIL.py:53).  h_out may alias h_in. */
+int tm_to_out_residual_fwd(const float* merged, const float* out_w, const float* out_b,
+                           const float* h_in, int64_t B, int64_t S, int64_t P, float* h_out,
+                           uint32_t flags, void* stream);
+
+/* K13: PPEG.forward (TransMIL.py:60-75): x + dw7(x) + dw5(x) + dw3(x) on the GxG
+ * token image, cls row passed through.  h_in,h_out [B,S,512], S = G*G+1.
+ * packed: 512*50 floats of scratch (effective 7x7 filter + bias). */
+int tm_ppeg_fwd(const tm_weights* w, const float* h_in, int64_t B, int64_t G, float* h_out,
+                float* packed, void* stream);
+
+/* K14: final LayerNorm on the cls row + _fc (TransMIL.py:202-204).  h [B,S,512] -> logits [B,n_classes]. */
+int tm_head_fwd(const tm_weights* w, const float* h, int64_t B, int64_t S, float* logits,
+                void* stream);
+
+/* K15 (return_attn rows): rows of attn1 @ Z @ attn3 for one layer without the
+ * dense matrix: out[b,h,i,:] = attn1[b,h,rows[i],:] @ Z @ attn3  -> [B,8,n_rows,Sp].
+ * Consumers read attn[0,:,padding+1,padding+1:...] (code/visualize_mil.py:581). */
+int tm_attn_rows_fwd(const float* q, const float* k, const float* q_lm, const float* k_lm,
+                     const float* Z, int64_t B, int64_t Sp, const int64_t* rows_host,
+                     int64_t n_rows, float* out, float* scratch, void* stream);
+int64_t tm_attn_rows_scratch_floats(int64_t B, int64_t Sp, int64_t n_rows);
+
+/* Generic fp32 GEMM of the library (C[M,N] = A[M,K] W[N,K]^T), exposed for tests. */
+int tm_gemm_nt(const float* A, const float* W, float* C, int64_t M, int64_t N, int64_t K,
+               uint32_t flags, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TRANSMIL_B200_H */

@@ -1,0 +1,88 @@
+"""CPU suite: the C-ABI library loads, exports every symbol include/transmil_b200.h declares,
+and its host-only entry points (index contract, argument validation) behave."""
+import ctypes as C
+import math
+import os
+import re
+
+import numpy as np
+import pytest
+
+from common import ROOT
+
+
+@pytest.fixture(scope="module")
+def capi(built_lib):
+    import transmil_b200 as T
+    return T.capi
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "transmil_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(tm_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported(capi):
+    lib = capi.lib()
+    names = _declared_symbols()
+    assert len(names) >= 25
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in include/transmil_b200.h but not exported"
+    assert set(names) == set(capi.SIGNATURES), "ctypes signature table out of sync with the header"
+    assert b"sm_100a" in lib.tm_version()
+
+
+def test_plan_bit_exact_against_reference_expressions(capi):
+    lib = capi.lib()
+    p = capi.Plan()
+    ns = list(range(1, 20000)) + list(range(20000, 300001, 37)) + [50000, 100000, 200000, 300000]
+    for n in ns:
+        assert lib.tm_make_plan(n, C.byref(p)) == 0
+        G = int(np.ceil(np.sqrt(n)))                                 # TransMIL.py:178
+        S = G * G + 1
+        padding = 256 - S % 256 if S % 256 > 0 else 0                 # TransMIL.py:190-193
+        assert (p.n, p.G, p.N, p.dup, p.S) == (n, G, G * G, G * G - n, S)
+        assert (p.l, p.Sp, p.P, p.padding) == (math.ceil(S / 256), S + padding, padding, padding)
+
+
+def test_index_maps(capi):
+    lib = capi.lib()
+    for n in (1, 2, 3, 5, 255, 257, 1000, 6000):
+        p = capi.make_plan(n)
+        src = [lib.tm_dup_source(C.byref(p), t) for t in range(p.N)]
+        assert src == list(range(n)) + list(range(p.dup))             # cat([h, h[:, :add]])  TransMIL.py:180
+        groups = [lib.tm_landmark_group(C.byref(p), r) for r in range(p.Sp)]
+        assert groups == [r // p.l for r in range(p.Sp)] and max(groups) == 255
+        assert lib.tm_padded_row(C.byref(p), 0) == p.P                # cls row sits right behind the front pad
+        y, x = C.c_int64(), C.c_int64()
+        for t in (0, p.N - 1, p.G, min(p.N - 1, p.G + 1)):
+            lib.tm_ppeg_pixel(C.byref(p), t, C.byref(y), C.byref(x))
+            assert (y.value, x.value) == (t // p.G, t % p.G)
+
+
+def test_bad_arguments_fail_loudly(capi):
+    lib = capi.lib()
+    p = capi.Plan()
+    assert lib.tm_make_plan(0, C.byref(p)) == -1
+    assert b"at least one patch" in lib.tm_last_error()
+    with pytest.raises(ValueError):
+        capi.make_plan(-5)
+    nbytes = C.c_size_t()
+    w = capi.Weights()
+    assert lib.tm_workspace_bytes(1, 100, C.byref(w), 0, C.byref(nbytes)) != 0   # empty weights struct
+    with pytest.raises((ValueError, capi.TransmilError)):
+        capi.check(lib.tm_workspace_bytes(1, 100, C.byref(w), 0, C.byref(nbytes)))
+
+
+def test_workspace_size_host_only(capi):
+    lib = capi.lib()
+    w = capi.Weights()
+    w.fc1_kind, w.in_features, w.n_classes = capi.TM_FC1_SINGLE, 1024, 2
+    for f in ("fc1_w0", "fc1_b0", "cls_token", "norm_w", "norm_b", "fc_w", "fc_b"):
+        setattr(w, f, 256)   # non-NULL dummies; nothing is dereferenced on the host
+    nbytes = C.c_size_t()
+    assert lib.tm_workspace_bytes(1, 50000, C.byref(w), 0, C.byref(nbytes)) == 0
+    p = capi.make_plan(50000)
+    assert nbytes.value > 8 * p.Sp * 512 * 4          # h x3, xn, merged, q, k, v
+    assert nbytes.value < 4 << 30

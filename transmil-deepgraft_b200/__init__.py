@@ -1,0 +1,14 @@
+"""transmil-deepgraft_b200: B200-native TransMIL bag-level hot path.
+
+Layout (only what the path needs):
+  csrc/         hand-written sm_100a CUDA kernels + the C ABI (libtransmil_b200.so)
+  capi.py       ctypes binding of include/transmil_b200.h
+  transmil.py   host-side mirror of the reference plugin interface (models.TransMIL)
+  plugin.py     the reference's "model name -> models/<name>.py class" loader
+  shard.py      bag-data-parallel / token-shard planning over torch.distributed
+  build.py      nvcc build of the shared library
+"""
+from . import capi
+from .transmil import LazyAttention, NystromAttention, PPEG, TransLayer, TransMIL, y_prob_y_hat
+
+__all__ = ["capi", "TransMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat"]

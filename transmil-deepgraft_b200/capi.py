@@ -1,0 +1,113 @@
+"""ctypes binding of libtransmil_b200.so (the C ABI in include/transmil_b200.h).
+
+The library is the product: there is no CPU path and no PyTorch fallback.  If the
+shared object is missing this module raises at import of the first symbol.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtransmil_b200.so")
+
+TM_FLAG_SIMT_ONLY = 1
+TM_FLAG_KEEP_STAGES = 2
+TM_FC1_SINGLE, TM_FC1_2048, TM_FC1_768 = 0, 1, 2
+
+_fp = C.c_void_p  # device/host float pointers travel as raw addresses
+
+
+class Plan(C.Structure):
+    _fields_ = [(k, C.c_int64) for k in ("n", "G", "N", "dup", "S", "l", "Sp", "P", "padding")]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
+class LayerWeights(C.Structure):
+    _fields_ = [(k, _fp) for k in ("norm_w", "norm_b", "qkv_w", "out_w", "out_b", "conv_w")]
+
+
+class Weights(C.Structure):
+    _fields_ = ([("fc1_kind", C.c_int32), ("in_features", C.c_int32), ("n_classes", C.c_int32), ("reserved", C.c_int32)]
+                + [(k, _fp) for k in ("fc1_w0", "fc1_b0", "fc1_ln_w", "fc1_ln_b", "fc1_w1", "fc1_b1",
+                                      "fc1_ln2_w", "fc1_ln2_b", "cls_token")]
+                + [("layer1", LayerWeights), ("layer2", LayerWeights)]
+                + [(k, _fp) for k in ("ppeg_w7", "ppeg_b7", "ppeg_w5", "ppeg_b5", "ppeg_w3", "ppeg_b3",
+                                      "norm_w", "norm_b", "fc_w", "fc_b")])
+
+
+# symbol -> (restype, argtypes); every symbol declared in include/transmil_b200.h
+_i64, _u32, _sz = C.c_int64, C.c_uint32, C.c_size_t
+_PW = C.POINTER(Weights)
+SIGNATURES = {
+    "tm_version": (C.c_char_p, []),
+    "tm_last_error": (C.c_char_p, []),
+    "tm_device_supported": (C.c_int, []),
+    "tm_launch_count": (_i64, []),
+    "tm_reset_launch_count": (None, []),
+    "tm_make_plan": (C.c_int, [_i64, C.POINTER(Plan)]),
+    "tm_dup_source": (_i64, [C.POINTER(Plan), _i64]),
+    "tm_landmark_group": (_i64, [C.POINTER(Plan), _i64]),
+    "tm_padded_row": (_i64, [C.POINTER(Plan), _i64]),
+    "tm_ppeg_pixel": (None, [C.POINTER(Plan), _i64, C.POINTER(_i64), C.POINTER(_i64)]),
+    "tm_workspace_bytes": (C.c_int, [_i64, _i64, _PW, _u32, C.POINTER(_sz)]),
+    "tm_transmil_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _sz, _u32, _fp]),
+    "tm_transmil_fwd_host": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _fp, _fp, _sz, _u32, _fp]),
+    "tm_stage_ptr": (C.c_int, [C.c_char_p, _i64, _i64, _PW, _u32, _fp, C.POINTER(C.c_void_p), C.POINTER(_i64)]),
+    "tm_fc1_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
+    "tm_ln_pad_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _fp, _fp]),
+    "tm_qkv_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _u32, _fp]),
+    "tm_landmarks_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _fp, _fp, _fp]),
+    "tm_pinv_scratch_floats": (_i64, [_i64]),
+    "tm_pinv_fwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp, _fp, _u32, _fp]),
+    "tm_attn3v_scratch_floats": (_i64, [_i64, _i64]),
+    "tm_attn3v_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
+    "tm_zw_fwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp]),
+    "tm_nystrom_out_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
+    "tm_to_out_residual_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _i64, _i64, _i64, _fp, _u32, _fp]),
+    "tm_ppeg_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _fp]),
+    "tm_head_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp]),
+    "tm_attn_rows_scratch_floats": (_i64, [_i64, _i64, _i64]),
+    "tm_attn_rows_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, C.POINTER(_i64), _i64, _fp, _fp, _fp]),
+    "tm_gemm_nt": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _u32, _fp]),
+}
+
+_lib = None
+
+
+class TransmilError(RuntimeError):
+    pass
+
+
+def lib():
+    """The loaded shared library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise TransmilError(
+                f"{LIB_PATH} is missing: build it with `python transmil-deepgraft_b200/build.py` "
+                "(there is no CPU or PyTorch fallback for this path)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+_STATUS = {-1: "bad shape", -2: "bad alignment", -3: "unsupported arch", -4: "workspace too small",
+           -5: "CUDA error", -6: "bad argument"}
+
+
+def check(status):
+    if status != 0:
+        msg = lib().tm_last_error().decode("utf-8", "replace")
+        exc = ValueError if status in (-1, -2, -6) else TransmilError
+        raise exc(f"libtransmil_b200: {_STATUS.get(status, status)}: {msg}")
+
+
+def make_plan(n):
+    p = Plan()
+    check(lib().tm_make_plan(int(n), C.byref(p)))
+    return p

@@ -1,0 +1,100 @@
+// Shared host/device helpers of libtransmil_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "transmil_b200.h"
+
+namespace tmil {
+
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+#define TM_CHECK_ARG(cond, code, ...)  \
+  do {                                 \
+    if (!(cond)) {                     \
+      tmil::set_error(__VA_ARGS__);      \
+      return (code);                   \
+    }                                  \
+  } while (0)
+
+#define TM_CUDA(expr)                                                              \
+  do {                                                                             \
+    cudaError_t _e = (expr);                                                       \
+    if (_e != cudaSuccess) {                                                       \
+      tmil::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return TM_ERR_CUDA;                                                          \
+    }                                                                              \
+  } while (0)
+
+#define TM_LAUNCH_CHECK()                                                          \
+  do {                                                                             \
+    tmil::count_launch();                                                            \
+    cudaError_t _e = cudaGetLastError();                                           \
+    if (_e != cudaSuccess) {                                                       \
+      tmil::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return TM_ERR_CUDA;                                                          \
+    }                                                                              \
+  } while (0)
+
+#define TM_PROPAGATE(expr)     \
+  do {                         \
+    int _s = (expr);           \
+    if (_s != TM_OK) return _s; \
+  } while (0)
+
+static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+__device__ __forceinline__ float gelu_erf(float x) {
+  // nn.GELU() default (approximate='none'): 0.5 x (1 + erf(x / sqrt 2))
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---- generic fp32 CUDA-core GEMM (gemm_simt.cu) ---------------------------
+enum GemmEpi : int {
+  EPI_AXPBY = 0,      // C = alpha*acc + beta*L[r,c]           (pinv steps, Z@W3)
+  EPI_BIAS_GELU = 1,  // C[map(r)] = gelu(acc + bias[c]) (+ duplicate-pad rows)   fc1
+  EPI_QKV = 2,        // head-major q(*0.125),k,v split
+  EPI_BIAS_RESID = 3, // C = acc + bias[c] + R[r,c]            to_out + residual
+};
+
+struct GemmParams {
+  const float* A; const float* Bm; float* C;
+  int M, N, K;
+  int lda, ldb, ldc;
+  int b_is_kn;                 // 0: B is [N,K] (weights, K contiguous); 1: B is [K,N]
+  int batch;                   // grid.z
+  long long strideA, strideB, strideC, strideL;
+  int epi;
+  float alpha, beta;
+  const float* L; int ldl;     // EPI_AXPBY second term / EPI_BIAS_RESID residual
+  const float* bias;
+  // row maps: logical row r in [0,M): bag = r / rows_per_bag, i = r % rows_per_bag
+  int rows_per_bag;            // 0 = identity maps
+  long long a_bag_rows; int a_row_off;   // A row  = bag*a_bag_rows + a_row_off + i
+  long long c_bag_rows; int c_row_off;   // C row  = bag*c_bag_rows + c_row_off + i
+  int dup;                     // rows i < dup are also written at c_row_off + rows_per_bag + i
+  // EPI_QKV
+  float* q; float* k; float* v; int Sp;
+};
+int gemm_simt(const GemmParams& p, cudaStream_t st);
+
+// ---- tcgen05 / TMA GEMM family (gemm_tc.cu) -------------------------------
+bool tc_available();
+int gemm_tc(const GemmParams& p, cudaStream_t st);   // same contract as gemm_simt for NT weight GEMMs
+
+}  // namespace tmil

@@ -1,0 +1,240 @@
+// Host orchestration of the TransMIL bag-level forward (TransMIL.py:167-211):
+// workspace layout, the GEMM-backed entry points (fc1, to_qkv, to_out) and the
+// whole-path calls.  Everything is launched on the caller's stream; the only
+// synchronising call is tm_transmil_fwd_host.
+#include "common.cuh"
+
+extern "C" int64_t tm_pinv_scratch_floats(int64_t B);
+
+namespace tmil {
+
+int ln_inplace(float* x, const float* gamma, const float* beta, long long rows, int width, int rpb, long long bag_rows,
+               int off, cudaStream_t st);
+
+static int gemm_auto(const GemmParams& p, uint32_t flags, cudaStream_t st) {
+  if (!(flags & TM_FLAG_SIMT_ONLY) && tc_available()) return gemm_tc(p, st);
+  return gemm_simt(p, st);
+}
+
+__global__ void cls_rows_kernel(const float* __restrict__ cls, long long bag_stride, float* __restrict__ h) {
+  // h[b, 0, :] = cls_token  (TransMIL.py:184-186)
+  reinterpret_cast<float4*>(h + (long long)blockIdx.x * bag_stride)[threadIdx.x] = __ldg(reinterpret_cast<const float4*>(cls) + threadIdx.x);
+}
+
+static int fc1_width(const tm_weights* w) {
+  switch (w->fc1_kind) {
+    case TM_FC1_SINGLE: return 0;
+    case TM_FC1_2048: return 1024;
+    case TM_FC1_768: return 768;
+    default: return -1;
+  }
+}
+
+struct Layout {
+  size_t total;  // floats
+  size_t h[4], fc1s, xn, merged, q, k, v, small[2][6], pinv_s, a3_s, packed;
+};
+enum { SM_QLM = 0, SM_KLM, SM_ATTN2, SM_Z, SM_W3, SM_M };
+
+static size_t bump(size_t& cur, size_t n) {
+  size_t at = cur;
+  cur += (n + 63) & ~(size_t)63;  // 256-byte granules
+  return at;
+}
+
+static int make_layout(int64_t B, const tm_plan& p, const tm_weights* w, uint32_t flags, Layout* L) {
+  const int f0 = fc1_width(w);
+  TM_CHECK_ARG(f0 >= 0, TM_ERR_BAD_ARGUMENT, "unknown fc1_kind %d", w->fc1_kind);
+  size_t cur = 0;
+  const size_t hs = (size_t)B * p.S * TM_DIM;
+  L->h[0] = bump(cur, hs);
+  L->h[1] = bump(cur, hs);
+  L->h[2] = bump(cur, hs);
+  L->h[3] = (flags & TM_FLAG_KEEP_STAGES) ? bump(cur, hs) : L->h[0];
+  L->fc1s = bump(cur, (size_t)B * p.n * f0);
+  const size_t ps = (size_t)B * p.Sp * TM_DIM;
+  L->xn = bump(cur, ps);
+  L->merged = bump(cur, ps);
+  L->q = bump(cur, ps);
+  L->k = bump(cur, ps);
+  L->v = bump(cur, ps);
+  const size_t lm = (size_t)B * TM_HEADS * TM_LANDMARKS * TM_DHEAD, mm = (size_t)B * TM_HEADS * 65536;
+  for (int l = 0; l < 2; ++l) {
+    L->small[l][SM_QLM] = bump(cur, lm);
+    L->small[l][SM_KLM] = bump(cur, lm);
+    L->small[l][SM_ATTN2] = bump(cur, mm);
+    L->small[l][SM_Z] = bump(cur, mm);
+    L->small[l][SM_W3] = bump(cur, lm);
+    L->small[l][SM_M] = bump(cur, lm);
+  }
+  L->pinv_s = bump(cur, (size_t)tm_pinv_scratch_floats(B));
+  L->a3_s = bump(cur, (size_t)tm_attn3v_scratch_floats(B, p.Sp));
+  L->packed = bump(cur, 50 * TM_DIM);
+  L->total = cur;
+  return TM_OK;
+}
+
+static int check_weights(const tm_weights* w) {
+  TM_CHECK_ARG(w != nullptr, TM_ERR_BAD_ARGUMENT, "weights struct is NULL");
+  TM_CHECK_ARG(w->in_features > 0 && w->in_features % 4 == 0, TM_ERR_BAD_SHAPE, "in_features must be a positive multiple of 4 (got %d)", w->in_features);
+  TM_CHECK_ARG(w->n_classes > 0, TM_ERR_BAD_SHAPE, "n_classes must be positive");
+  TM_CHECK_ARG(w->fc1_w0 && w->fc1_b0 && w->cls_token && w->norm_w && w->norm_b && w->fc_w && w->fc_b, TM_ERR_BAD_ARGUMENT, "missing parameter pointer");
+  if (w->fc1_kind == TM_FC1_2048)
+    TM_CHECK_ARG(w->in_features == 2048 && w->fc1_ln_w && w->fc1_ln_b && w->fc1_w1 && w->fc1_b1, TM_ERR_BAD_ARGUMENT, "TM_FC1_2048 needs in_features=2048 and the LN/second Linear parameters");
+  if (w->fc1_kind == TM_FC1_768)
+    TM_CHECK_ARG(w->in_features == 768 && w->fc1_ln_w && w->fc1_ln_b && w->fc1_w1 && w->fc1_b1 && w->fc1_ln2_w && w->fc1_ln2_b, TM_ERR_BAD_ARGUMENT, "TM_FC1_768 needs in_features=768 and both LayerNorms");
+  return TM_OK;
+}
+
+static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, const float* h_in, float* h_out, float* ws,
+                     const Layout& L, int li, uint32_t flags, cudaStream_t st) {
+  float* xn = ws + L.xn; float* q = ws + L.q; float* k = ws + L.k; float* v = ws + L.v;
+  float* q_lm = ws + L.small[li][SM_QLM]; float* k_lm = ws + L.small[li][SM_KLM];
+  float* attn2 = ws + L.small[li][SM_ATTN2]; float* Z = ws + L.small[li][SM_Z];
+  float* W3 = ws + L.small[li][SM_W3]; float* M = ws + L.small[li][SM_M];
+  float* merged = ws + L.merged;
+  TM_PROPAGATE(tm_ln_pad_fwd(h_in, lw.norm_w, lw.norm_b, B, p.S, p.P, xn, st));
+  TM_PROPAGATE(tm_qkv_fwd(xn, lw.qkv_w, B, p.Sp, q, k, v, flags, st));
+  TM_PROPAGATE(tm_landmarks_fwd(q, k, B, p.Sp, p.l, q_lm, k_lm, st));
+  TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, st));
+  TM_PROPAGATE(tm_attn3v_fwd(q_lm, k, v, B, p.Sp, W3, ws + L.a3_s, flags, st));
+  TM_PROPAGATE(tm_zw_fwd(Z, W3, B, M, st));
+  TM_PROPAGATE(tm_nystrom_out_fwd(q, k_lm, M, v, lw.conv_w, B, p.Sp, merged, flags, st));
+  TM_PROPAGATE(tm_to_out_residual_fwd(merged, lw.out_w, lw.out_b, h_in, B, p.S, p.P, h_out, flags, st));
+  return TM_OK;
+}
+
+}  // namespace tmil
+
+using namespace tmil;
+
+extern "C" int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n, float* h0, float* scratch,
+                          uint32_t flags, void* stream) {
+  TM_PROPAGATE(check_weights(w));
+  tm_plan p;
+  TM_PROPAGATE(tm_make_plan(n, &p));
+  TM_CHECK_ARG(B > 0 && x && h0, TM_ERR_BAD_ARGUMENT, "tm_fc1_fwd: bad arguments");
+  TM_CHECK_ARG(B * n < (1ll << 31) && B * p.Sp < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_fc1_fwd: B*n exceeds 2^31 rows");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int D = w->in_features;
+  GemmParams g;
+  memset(&g, 0, sizeof(g));
+  g.batch = 1; g.epi = EPI_BIAS_GELU;
+  const float* a2 = x; int k2 = D; const float* w2 = w->fc1_w0; const float* b2 = w->fc1_b0;
+  if (w->fc1_kind != TM_FC1_SINGLE) {
+    const int F0 = fc1_width(w);
+    TM_CHECK_ARG(scratch != nullptr, TM_ERR_BAD_ARGUMENT, "tm_fc1_fwd: scratch is required for the two-Linear stems");
+    g.A = x; g.Bm = w->fc1_w0; g.C = scratch; g.bias = w->fc1_b0;
+    g.M = (int)(B * n); g.N = F0; g.K = D; g.lda = D; g.ldb = D; g.ldc = F0;
+    TM_PROPAGATE(gemm_auto(g, flags, st));
+    TM_PROPAGATE(ln_inplace(scratch, w->fc1_ln_w, w->fc1_ln_b, B * n, F0, 0, 0, 0, st));
+    a2 = scratch; k2 = F0; w2 = w->fc1_w1; b2 = w->fc1_b1;
+  }
+  g.A = a2; g.Bm = w2; g.C = h0; g.bias = b2;
+  g.M = (int)(B * n); g.N = TM_DIM; g.K = k2; g.lda = k2; g.ldb = k2; g.ldc = TM_DIM;
+  g.rows_per_bag = (int)n; g.a_bag_rows = n; g.a_row_off = 0; g.c_bag_rows = p.S; g.c_row_off = 1; g.dup = (int)p.dup;
+  TM_PROPAGATE(gemm_auto(g, flags, st));
+  if (w->fc1_kind == TM_FC1_768)  // trailing LayerNorm(512) on every token row (row 0 is the cls token)
+    TM_PROPAGATE(ln_inplace(h0, w->fc1_ln2_w, w->fc1_ln2_b, B * p.N, TM_DIM, (int)p.N, p.S, 1, st));
+  cls_rows_kernel<<<(unsigned)B, TM_DIM / 4, 0, st>>>(w->cls_token, p.S * (long long)TM_DIM, h0);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+extern "C" int tm_qkv_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, float* q, float* k, float* v,
+                          uint32_t flags, void* stream) {
+  TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0 && B * Sp < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_qkv_fwd: bad shape B=%lld Sp=%lld", (long long)B, (long long)Sp);
+  TM_CHECK_ARG(xn && qkv_w && q && k && v, TM_ERR_BAD_ARGUMENT, "tm_qkv_fwd: NULL pointer");
+  GemmParams g;
+  memset(&g, 0, sizeof(g));
+  g.A = xn; g.Bm = qkv_w; g.C = nullptr;
+  g.M = (int)(B * Sp); g.N = 3 * TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = 3 * TM_DIM;
+  g.batch = 1; g.epi = EPI_QKV; g.q = q; g.k = k; g.v = v; g.Sp = (int)Sp;
+  return gemm_auto(g, flags, (cudaStream_t)stream);
+}
+
+extern "C" int tm_to_out_residual_fwd(const float* merged, const float* out_w, const float* out_b, const float* h_in,
+                                      int64_t B, int64_t S, int64_t P, float* h_out, uint32_t flags, void* stream) {
+  TM_CHECK_ARG(B > 0 && S > 0 && P >= 0 && B * (S + P) < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_to_out_residual_fwd: bad shape");
+  TM_CHECK_ARG(merged && out_w && out_b && h_in && h_out, TM_ERR_BAD_ARGUMENT, "tm_to_out_residual_fwd: NULL pointer");
+  GemmParams g;
+  memset(&g, 0, sizeof(g));
+  g.A = merged; g.Bm = out_w; g.C = h_out; g.bias = out_b; g.L = h_in; g.ldl = TM_DIM;
+  g.M = (int)(B * S); g.N = TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = TM_DIM;
+  g.batch = 1; g.epi = EPI_BIAS_RESID;
+  g.rows_per_bag = (int)S; g.a_bag_rows = S + P; g.a_row_off = (int)P; g.c_bag_rows = S; g.c_row_off = 0;
+  return gemm_auto(g, flags, (cudaStream_t)stream);
+}
+
+extern "C" int tm_workspace_bytes(int64_t B, int64_t n, const tm_weights* w, uint32_t flags, size_t* bytes) {
+  TM_CHECK_ARG(bytes != nullptr && B > 0, TM_ERR_BAD_ARGUMENT, "tm_workspace_bytes: bad arguments");
+  TM_PROPAGATE(check_weights(w));
+  tm_plan p;
+  TM_PROPAGATE(tm_make_plan(n, &p));
+  Layout L;
+  TM_PROPAGATE(make_layout(B, p, w, flags, &L));
+  *bytes = L.total * sizeof(float);
+  return TM_OK;
+}
+
+extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n, float* logits, void* workspace,
+                               size_t workspace_bytes, uint32_t flags, void* stream) {
+  TM_PROPAGATE(check_weights(w));
+  TM_CHECK_ARG(B > 0 && x && logits && workspace, TM_ERR_BAD_ARGUMENT, "tm_transmil_fwd: bad arguments");
+  TM_CHECK_ARG(aligned16(x) && ((uintptr_t)workspace & 255u) == 0, TM_ERR_BAD_ALIGNMENT, "tm_transmil_fwd: x must be 16-byte and workspace 256-byte aligned");
+  tm_plan p;
+  TM_PROPAGATE(tm_make_plan(n, &p));
+  Layout L;
+  TM_PROPAGATE(make_layout(B, p, w, flags, &L));
+  TM_CHECK_ARG(workspace_bytes >= L.total * sizeof(float), TM_ERR_WORKSPACE_TOO_SMALL, "tm_transmil_fwd: workspace too small (%zu < %zu bytes)", workspace_bytes, L.total * sizeof(float));
+  cudaStream_t st = (cudaStream_t)stream;
+  float* ws = (float*)workspace;
+  TM_PROPAGATE(tm_fc1_fwd(w, x, B, n, ws + L.h[0], ws + L.fc1s, flags, st));
+  TM_PROPAGATE(layer_fwd(w->layer1, p, B, ws + L.h[0], ws + L.h[1], ws, L, 0, flags, st));
+  TM_PROPAGATE(tm_ppeg_fwd(w, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
+  TM_PROPAGATE(layer_fwd(w->layer2, p, B, ws + L.h[2], ws + L.h[3], ws, L, 1, flags, st));
+  TM_PROPAGATE(tm_head_fwd(w, ws + L.h[3], B, p.S, logits, st));
+  return TM_OK;
+}
+
+extern "C" int tm_transmil_fwd_host(const tm_weights* w, const float* x_host, int64_t B, int64_t n, float* logits_host,
+                                    float* d_x, float* d_logits, void* workspace, size_t workspace_bytes, uint32_t flags,
+                                    void* stream) {
+  TM_PROPAGATE(check_weights(w));
+  TM_CHECK_ARG(x_host && logits_host && d_x && d_logits, TM_ERR_BAD_ARGUMENT, "tm_transmil_fwd_host: NULL pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  TM_CUDA(cudaMemcpyAsync(d_x, x_host, (size_t)B * n * w->in_features * sizeof(float), cudaMemcpyHostToDevice, st));
+  TM_PROPAGATE(tm_transmil_fwd(w, d_x, B, n, d_logits, workspace, workspace_bytes, flags, st));
+  TM_CUDA(cudaMemcpyAsync(logits_host, d_logits, (size_t)B * w->n_classes * sizeof(float), cudaMemcpyDeviceToHost, st));
+  TM_CUDA(cudaStreamSynchronize(st));
+  return TM_OK;
+}
+
+extern "C" int tm_stage_ptr(const char* name, int64_t B, int64_t n, const tm_weights* w, uint32_t flags, void* workspace,
+                            void** ptr, int64_t* numel) {
+  TM_CHECK_ARG(name && ptr && numel && workspace, TM_ERR_BAD_ARGUMENT, "tm_stage_ptr: bad arguments");
+  TM_PROPAGATE(check_weights(w));
+  tm_plan p;
+  TM_PROPAGATE(tm_make_plan(n, &p));
+  Layout L;
+  TM_PROPAGATE(make_layout(B, p, w, flags, &L));
+  float* ws = (float*)workspace;
+  const int64_t hs = B * p.S * TM_DIM, ps = B * p.Sp * TM_DIM;
+  const int64_t lm = B * TM_HEADS * TM_LANDMARKS * TM_DHEAD, mm = B * TM_HEADS * 65536;
+  struct { const char* nm; size_t off; int64_t ne; } tab[] = {
+      {"h0", L.h[0], hs}, {"h1", L.h[1], hs}, {"h2", L.h[2], hs}, {"h3", L.h[3], hs},
+      {"xn", L.xn, ps}, {"merged", L.merged, ps}, {"q", L.q, ps}, {"k", L.k, ps}, {"v", L.v, ps},
+      {"q_lm1", L.small[0][SM_QLM], lm}, {"k_lm1", L.small[0][SM_KLM], lm}, {"attn21", L.small[0][SM_ATTN2], mm},
+      {"Z1", L.small[0][SM_Z], mm}, {"W31", L.small[0][SM_W3], lm}, {"M1", L.small[0][SM_M], lm},
+      {"q_lm", L.small[1][SM_QLM], lm}, {"k_lm", L.small[1][SM_KLM], lm}, {"attn2", L.small[1][SM_ATTN2], mm},
+      {"Z", L.small[1][SM_Z], mm}, {"W3", L.small[1][SM_W3], lm}, {"M", L.small[1][SM_M], lm},
+  };
+  for (auto& t : tab)
+    if (strcmp(t.nm, name) == 0) {
+      *ptr = ws + t.off;
+      *numel = t.ne;
+      return TM_OK;
+    }
+  set_error("tm_stage_ptr: unknown stage '%s'", name);
+  return TM_ERR_BAD_ARGUMENT;
+}

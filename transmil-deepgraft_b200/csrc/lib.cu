@@ -1,0 +1,60 @@
+// Library plumbing: error string, launch counter, index contract (host only).
+#include <math.h>
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace tmil {
+static thread_local char g_err[512] = "";
+static thread_local int64_t g_launches = 0;
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches += n; }
+}  // namespace tmil
+
+extern "C" {
+
+const char* tm_version(void) { return "transmil_b200 0.1 (sm_100a)"; }
+const char* tm_last_error(void) { return tmil::g_err; }
+int64_t tm_launch_count(void) { return tmil::g_launches; }
+void tm_reset_launch_count(void) { tmil::g_launches = 0; }
+
+int tm_device_supported(void) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  int major = 0;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
+  return major == 10 ? 1 : 0;
+}
+
+int tm_make_plan(int64_t n, tm_plan* out) {
+  TM_CHECK_ARG(out != nullptr, TM_ERR_BAD_ARGUMENT, "tm_make_plan: out is NULL");
+  TM_CHECK_ARG(n >= 1, TM_ERR_BAD_SHAPE, "tm_make_plan: bag must hold at least one patch (n=%lld)", (long long)n);
+  // int(np.ceil(np.sqrt(H))) with a float64 sqrt  (TransMIL.py:178)
+  int64_t G = (int64_t)ceil(sqrt((double)n));
+  out->n = n;
+  out->G = G;
+  out->N = G * G;
+  out->dup = out->N - n;
+  out->S = out->N + 1;
+  int64_t rem = out->S % TM_LANDMARKS;
+  out->P = rem > 0 ? TM_LANDMARKS - rem : 0;
+  out->Sp = out->S + out->P;
+  out->l = (out->S + TM_LANDMARKS - 1) / TM_LANDMARKS;
+  out->padding = rem > 0 ? 256 - rem : 0;  // TransMIL.py:190-193
+  TM_CHECK_ARG(out->dup <= n, TM_ERR_BAD_SHAPE, "tm_make_plan: duplicate pad %lld exceeds bag %lld", (long long)out->dup, (long long)n);
+  return TM_OK;
+}
+int64_t tm_dup_source(const tm_plan* p, int64_t t) { return t < p->n ? t : t - p->n; }
+int64_t tm_landmark_group(const tm_plan* p, int64_t r) { return r / p->l; }
+int64_t tm_padded_row(const tm_plan* p, int64_t s) { return p->P + s; }
+void tm_ppeg_pixel(const tm_plan* p, int64_t t, int64_t* y, int64_t* x) {
+  *y = t / p->G;
+  *x = t % p->G;
+}
+
+}  // extern "C"

@@ -1,0 +1,140 @@
+// Row-wise kernels: LayerNorm (+ front zero pad), in-place LayerNorm for the fc1
+// stems, and the cls-row head (final LayerNorm + _fc).  All HBM-bound: one warp
+// per row, 128-bit loads, row kept in registers between the two passes.
+#include "common.cuh"
+
+namespace tmil {
+
+// One warp normalises one row of width W (multiple of 128, <= 1024).
+template <int W>
+__device__ __forceinline__ void warp_layernorm_row(const float* src, float* dst,
+                                                   const float* __restrict__ gamma, const float* __restrict__ beta, int lane) {
+  constexpr int V = W / 128;  // float4 per lane
+  float4 x[V];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    x[i] = *reinterpret_cast<const float4*>(src + (i * 32 + lane) * 4);
+    s += (x[i].x + x[i].y) + (x[i].z + x[i].w);
+  }
+  const float mean = warp_sum(s) * (1.0f / W);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    float a = x[i].x - mean, b = x[i].y - mean, c = x[i].z - mean, d = x[i].w - mean;
+    q += (a * a + b * b) + (c * c + d * d);
+  }
+  const float rstd = 1.0f / sqrtf(warp_sum(q) * (1.0f / W) + 1e-5f);  // eps of nn.LayerNorm
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int c = (i * 32 + lane) * 4;
+    float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c));
+    float4 b = __ldg(reinterpret_cast<const float4*>(beta + c));
+    float4 o;
+    o.x = (x[i].x - mean) * rstd * g.x + b.x;
+    o.y = (x[i].y - mean) * rstd * g.y + b.y;
+    o.z = (x[i].z - mean) * rstd * g.z + b.z;
+    o.w = (x[i].w - mean) * rstd * g.w + b.w;
+    *reinterpret_cast<float4*>(dst + c) = o;
+  }
+}
+
+// xn[b, t] = t < P ? 0 : LN(h[b, t - P])
+__global__ void __launch_bounds__(256) ln_pad_kernel(const float* __restrict__ h, const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, long long rows, int S, int Sp, int P,
+                                                     float* __restrict__ xn) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const long long b = row / Sp;
+  const int t = (int)(row - b * Sp);
+  float* dst = xn + row * TM_DIM;
+  if (t < P) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(dst + (i * 32 + lane) * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    return;
+  }
+  warp_layernorm_row<TM_DIM>(h + (b * S + (t - P)) * TM_DIM, dst, gamma, beta, lane);
+}
+
+// In-place LayerNorm over mapped rows: row r -> (r / rpb) * bag_rows + off + r % rpb.
+template <int W>
+__global__ void __launch_bounds__(256) ln_inplace_kernel(float* __restrict__ x, const float* __restrict__ gamma,
+                                                         const float* __restrict__ beta, long long rows, int rpb,
+                                                         long long bag_rows, int off) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  long long rr = row;
+  if (rpb > 0) {
+    long long b = row / rpb;
+    rr = b * bag_rows + off + (row - b * rpb);
+  }
+  float* p = x + rr * W;
+  warp_layernorm_row<W>(p, p, gamma, beta, lane);
+}
+
+int ln_inplace(float* x, const float* gamma, const float* beta, long long rows, int width, int rpb, long long bag_rows,
+               int off, cudaStream_t st) {
+  if (rows <= 0) return TM_OK;
+  unsigned grid = (unsigned)ceil_div(rows, 8);
+  if (width == 512)
+    ln_inplace_kernel<512><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+  else if (width == 768)
+    ln_inplace_kernel<768><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+  else if (width == 1024)
+    ln_inplace_kernel<1024><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+  else {
+    set_error("ln_inplace: unsupported width %d", width);
+    return TM_ERR_BAD_SHAPE;
+  }
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+// cls row: logits[b] = _fc(LayerNorm(h[b, 0]))
+__global__ void __launch_bounds__(128) head_kernel(const float* __restrict__ h, long long bag_stride,
+                                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                   const float* __restrict__ fc_w, const float* __restrict__ fc_b,
+                                                   int n_classes, float* __restrict__ logits) {
+  __shared__ __align__(16) float hn[TM_DIM];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.x;
+  if (warp == 0) warp_layernorm_row<TM_DIM>(h + (long long)b * bag_stride, hn, gamma, beta, lane);
+  __syncthreads();
+  for (int c = warp; c < n_classes; c += 4) {
+    const float* wr = fc_w + (long long)c * TM_DIM;
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int j = (i * 32 + lane) * 4;
+      float4 w4 = __ldg(reinterpret_cast<const float4*>(wr + j));
+      float4 x4 = *reinterpret_cast<const float4*>(hn + j);
+      s += (w4.x * x4.x + w4.y * x4.y) + (w4.z * x4.z + w4.w * x4.w);
+    }
+    s = warp_sum(s);
+    if (lane == 0) logits[(long long)b * n_classes + c] = s + fc_b[c];
+  }
+}
+
+}  // namespace tmil
+
+extern "C" int tm_ln_pad_fwd(const float* h, const float* gamma, const float* beta, int64_t B, int64_t S, int64_t P,
+                             float* xn, void* stream) {
+  TM_CHECK_ARG(B > 0 && S > 0 && P >= 0 && (S + P) % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE,
+               "tm_ln_pad_fwd: S+P must be a multiple of 256 (S=%lld P=%lld)", (long long)S, (long long)P);
+  TM_CHECK_ARG(tmil::aligned16(h) && tmil::aligned16(xn) && tmil::aligned16(gamma) && tmil::aligned16(beta), TM_ERR_BAD_ALIGNMENT,
+               "tm_ln_pad_fwd: pointers must be 16-byte aligned");
+  const long long rows = (long long)B * (S + P);
+  tmil::ln_pad_kernel<<<(unsigned)tmil::ceil_div(rows, 8), 256, 0, (cudaStream_t)stream>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+extern "C" int tm_head_fwd(const tm_weights* w, const float* h, int64_t B, int64_t S, float* logits, void* stream) {
+  TM_CHECK_ARG(w != nullptr && B > 0 && S > 0 && w->n_classes > 0, TM_ERR_BAD_ARGUMENT, "tm_head_fwd: bad arguments");
+  tmil::head_kernel<<<(unsigned)B, 128, 0, (cudaStream_t)stream>>>(h, (long long)S * TM_DIM, w->norm_w, w->norm_b, w->fc_w, w->fc_b,
+                                                                 w->n_classes, logits);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}

@@ -1,0 +1,50 @@
+"""The reference's model plugin mechanism, re-expressed without Lightning.
+
+ModelInterface.load_model / instancialize (code/models/model_interface.py:1256-1293):
+`cfg.Model.name` -> `importlib.import_module(f'models.{name}')`, class name = name
+(CamelCase if it contains '_'), constructor kwargs = intersection of the class'
+__init__ argument names with the keys of cfg.Model.  `inspect.getargspec` is gone
+in Python >= 3.11, so getfullargspec is used; behaviour is otherwise identical,
+including the ValueError text on failure (:1272-1273).
+
+`in_features` derivation from Data.feature_extractor follows code/train.py:392-397.
+"""
+import importlib
+import inspect
+import os
+import sys
+
+_CODE_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "code")
+
+FEATURE_DIMS = {"retccl": 2048, "histoencoder": 384, "ctranspath": 784}   # code/train.py:392-397
+
+
+def _ensure_models_on_path():
+    if _CODE_DIR not in sys.path:
+        sys.path.insert(0, _CODE_DIR)
+
+
+def load_model(model_cfg, **other_args):
+    """model_cfg: mapping with at least `name` (the YAML `Model:` section)."""
+    _ensure_models_on_path()
+    get = model_cfg.get if hasattr(model_cfg, "get") else (lambda k, d=None: getattr(model_cfg, k, d))
+    name = get("name")
+    camel_name = "".join(i.capitalize() for i in name.split("_")) if "_" in name else name
+    try:
+        Model = getattr(importlib.import_module(f"models.{name}"), camel_name)
+    except Exception:
+        raise ValueError("Invalid Module File Name or Invalid Class Name!")
+    class_args = inspect.getfullargspec(Model.__init__).args[1:]
+    keys = list(model_cfg.keys())
+    args = {a: model_cfg[a] for a in class_args if a in keys}
+    args.update(other_args)
+    return Model(**args)
+
+
+def model_cfg_from_yaml(cfg):
+    """Applies train.py's overrides to a parsed YAML dict and returns the `Model` section."""
+    model = dict(cfg.get("Model", {}))
+    fe = (cfg.get("Data", {}) or {}).get("feature_extractor")
+    if fe in FEATURE_DIMS:
+        model["in_features"] = FEATURE_DIMS[fe]
+    return model

@@ -1,0 +1,306 @@
+"""Drop-in `TransMIL` for the DeepGraft plugin loader (`models.TransMIL`).
+
+Mirrors /root/reference/code/models/TransMIL.py: same constructor
+`TransMIL(n_classes, in_features, out_features=512)` (TransMIL.py:79), same
+`forward(x, return_attn=False)` (TransMIL.py:167, plus the upstream `data=`
+keyword), same sub-module names and state_dict keys/shapes, sub-modules created
+in the same order so seeded initialisation is bit-identical (TransMIL.py:91-155).
+
+The sub-modules are parameter containers: the arithmetic of the whole forward
+runs in libtransmil_b200.so (hand-written sm_100a CUDA) through the C ABI in
+include/transmil_b200.h.  There is no PyTorch or CPU fallback.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import capi
+
+__all__ = ["TransMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention"]
+
+
+class NystromAttention(nn.Module):
+    """Parameter container with the layout of nystrom-attention 0.0.11
+    (constructor call at TransMIL.py:26-34): to_qkv, to_out.0, res_conv."""
+
+    def __init__(self, dim, dim_head=64, heads=8, num_landmarks=256, pinv_iterations=6,
+                 residual=True, residual_conv_kernel=33, eps=1e-8, dropout=0.0):
+        super().__init__()
+        if (dim, dim_head, heads, num_landmarks, pinv_iterations, residual, residual_conv_kernel) != (512, 64, 8, 256, 6, True, 33):
+            raise ValueError("libtransmil_b200 implements the TransMIL configuration only: dim=512, heads=8, "
+                             "dim_head=64, num_landmarks=256, pinv_iterations=6, residual conv 33")
+        inner = heads * dim_head
+        self.eps = eps
+        self.num_landmarks = num_landmarks
+        self.pinv_iterations = pinv_iterations
+        self.heads = heads
+        self.scale = dim_head ** -0.5
+        self.to_qkv = nn.Linear(dim, inner * 3, bias=False)
+        self.to_out = nn.Sequential(nn.Linear(inner, dim), nn.Dropout(dropout))
+        self.residual = residual
+        self.res_conv = nn.Conv2d(heads, heads, (residual_conv_kernel, 1), padding=(residual_conv_kernel // 2, 0),
+                                  groups=heads, bias=False)
+
+
+class TransLayer(nn.Module):
+    """TransMIL.py:19-57.  `norm` stays a real nn.LayerNorm sub-module (GradCAM hook
+    point, code/train_loop.py:87); `attn` holds the NystromAttention parameters."""
+
+    def __init__(self, norm_layer=nn.LayerNorm, dim=512):
+        super().__init__()
+        self.norm = norm_layer(dim)
+        attention_heads = 8
+        self.attn = NystromAttention(dim=dim, dim_head=dim // attention_heads, heads=attention_heads,
+                                     num_landmarks=dim // 2, pinv_iterations=6, residual=True, dropout=0.7)
+
+
+class PPEG(nn.Module):
+    """TransMIL.py:60-75: parameter container for the 7/5/3 depthwise convs."""
+
+    def __init__(self, dim=512):
+        super().__init__()
+        self.proj = nn.Conv2d(dim, dim, 7, 1, 7 // 2, groups=dim)
+        self.proj1 = nn.Conv2d(dim, dim, 5, 1, 5 // 2, groups=dim)
+        self.proj2 = nn.Conv2d(dim, dim, 3, 1, 3 // 2, groups=dim)
+
+
+def _fc1_1024_else_form():
+    """the reference's in_features==1024 branch (TransMIL.py:117-121)
+    raises at the first forward; 1024-d inputs use Sequential(Linear(1024,512), GELU())
+    (= code/models/MDMIL.py:66 = TransMIL's else branch).  Drawn from a generator seeded
+    initial_seed()+1 so the init stream of every other parameter is untouched."""
+    state = torch.random.get_rng_state()
+    seed = torch.initial_seed()
+    torch.manual_seed(seed + 1)
+    fc1 = nn.Sequential(nn.Linear(1024, 512), nn.GELU())
+    torch.manual_seed(seed)
+    torch.random.set_rng_state(state)
+    return fc1
+
+
+class TransMIL(nn.Module):
+    def __init__(self, n_classes, in_features, out_features=512):
+        super().__init__()
+        if out_features != 512:
+            raise ValueError("libtransmil_b200 implements out_features=512 (the only value the reference configs use)")
+        norm_layer = nn.LayerNorm
+        self.pos_layer = PPEG(dim=out_features)
+        if in_features == 2048:      # TransMIL.py:100-111
+            self._fc1 = nn.Sequential(
+                nn.Linear(in_features, int(in_features / 2)), nn.GELU(), norm_layer(int(in_features / 2)),
+                nn.Linear(int(in_features / 2), out_features), nn.GELU())
+            self._fc1_kind = capi.TM_FC1_2048
+        elif in_features == 1024:    # TransMIL.py:117-121 consumes RNG for two Linears, then is unusable
+            nn.Linear(in_features, in_features)
+            nn.Linear(in_features, out_features)
+            self._fc1 = _fc1_1024_else_form()
+            self._fc1_kind = capi.TM_FC1_SINGLE
+        elif in_features == 768:     # TransMIL.py:122-126
+            self._fc1 = nn.Sequential(
+                nn.Linear(in_features, int(in_features)), nn.GELU(), nn.Dropout(p=0.6), norm_layer(in_features),
+                nn.Linear(in_features, out_features), nn.GELU(), nn.Dropout(p=0.6), norm_layer(out_features))
+            self._fc1_kind = capi.TM_FC1_768
+        else:                        # TransMIL.py:128-133
+            self._fc1 = nn.Sequential(nn.Linear(in_features, out_features), nn.GELU())
+            self._fc1_kind = capi.TM_FC1_SINGLE
+        self.cls_token = nn.Parameter(torch.randn(1, 1, out_features))
+        self.n_classes = n_classes
+        self.in_features = in_features
+        self.layer1 = TransLayer(norm_layer=norm_layer, dim=out_features)
+        self.layer2 = TransLayer(norm_layer=norm_layer, dim=out_features)
+        self.norm = norm_layer(out_features)
+        self._fc = nn.Linear(out_features, self.n_classes)
+        self.flags = 0          # capi.TM_FLAG_* bits OR-ed into every call
+        self._ws = None         # cached device workspace (uint8 tensor)
+        self._stage_key = None
+
+    # ---- parameters -> C struct ------------------------------------------------
+    def _ptr(self, t, shape=None):
+        if not t.is_cuda:
+            raise capi.TransmilError("TransMIL parameters must live on a CUDA device (model.cuda()); there is no CPU path")
+        if t.dtype != torch.float32 or not t.is_contiguous():
+            raise capi.TransmilError("TransMIL parameters must be contiguous float32")
+        if shape is not None and tuple(t.shape) != tuple(shape):
+            raise ValueError(f"parameter has shape {tuple(t.shape)}, expected {tuple(shape)}")
+        return t.data_ptr()
+
+    def _weights(self):
+        w = capi.Weights()
+        w.fc1_kind, w.in_features, w.n_classes = self._fc1_kind, self.in_features, self.n_classes
+        f = self._fc1
+        D = self.in_features
+        if self._fc1_kind == capi.TM_FC1_2048:
+            w.fc1_w0, w.fc1_b0 = self._ptr(f[0].weight, (1024, D)), self._ptr(f[0].bias)
+            w.fc1_ln_w, w.fc1_ln_b = self._ptr(f[2].weight, (1024,)), self._ptr(f[2].bias)
+            w.fc1_w1, w.fc1_b1 = self._ptr(f[3].weight, (512, 1024)), self._ptr(f[3].bias)
+        elif self._fc1_kind == capi.TM_FC1_768:
+            w.fc1_w0, w.fc1_b0 = self._ptr(f[0].weight, (768, 768)), self._ptr(f[0].bias)
+            w.fc1_ln_w, w.fc1_ln_b = self._ptr(f[3].weight, (768,)), self._ptr(f[3].bias)
+            w.fc1_w1, w.fc1_b1 = self._ptr(f[4].weight, (512, 768)), self._ptr(f[4].bias)
+            w.fc1_ln2_w, w.fc1_ln2_b = self._ptr(f[7].weight, (512,)), self._ptr(f[7].bias)
+        else:
+            w.fc1_w0, w.fc1_b0 = self._ptr(f[0].weight, (512, D)), self._ptr(f[0].bias)
+        w.cls_token = self._ptr(self.cls_token, (1, 1, 512))
+        for name in ("layer1", "layer2"):
+            layer, lw = getattr(self, name), getattr(w, name)
+            lw.norm_w, lw.norm_b = self._ptr(layer.norm.weight, (512,)), self._ptr(layer.norm.bias, (512,))
+            lw.qkv_w = self._ptr(layer.attn.to_qkv.weight, (1536, 512))
+            lw.out_w, lw.out_b = self._ptr(layer.attn.to_out[0].weight, (512, 512)), self._ptr(layer.attn.to_out[0].bias)
+            lw.conv_w = self._ptr(layer.attn.res_conv.weight, (8, 1, 33, 1))
+        p = self.pos_layer
+        w.ppeg_w7, w.ppeg_b7 = self._ptr(p.proj.weight, (512, 1, 7, 7)), self._ptr(p.proj.bias)
+        w.ppeg_w5, w.ppeg_b5 = self._ptr(p.proj1.weight, (512, 1, 5, 5)), self._ptr(p.proj1.bias)
+        w.ppeg_w3, w.ppeg_b3 = self._ptr(p.proj2.weight, (512, 1, 3, 3)), self._ptr(p.proj2.bias)
+        w.norm_w, w.norm_b = self._ptr(self.norm.weight, (512,)), self._ptr(self.norm.bias, (512,))
+        w.fc_w, w.fc_b = self._ptr(self._fc.weight, (self.n_classes, 512)), self._ptr(self._fc.bias)
+        return w
+
+    def _workspace(self, nbytes, device):
+        ws = self._ws
+        if ws is None or ws.device != device or ws.numel() < nbytes:
+            self._ws = ws = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+        return ws
+
+    # ---- forward ---------------------------------------------------------------
+    def forward(self, x=None, return_attn=False, **kwargs):
+        if x is None:
+            x = kwargs.get("data")          # upstream TransMIL: forward(**kwargs) with kwargs['data']
+        if x is None:
+            raise TypeError("forward() needs the bag tensor (positional `x` or keyword `data`)")
+        if self.training and torch.is_grad_enabled():
+            raise NotImplementedError("libtransmil_b200: the backward kernels are not built yet; "
+                                      "call model.eval() / torch.no_grad() (inference path)")
+        # TransMIL.py:170-174
+        if x.dim() > 3:
+            x = x.squeeze(0)
+        elif x.dim() == 2:
+            x = x.unsqueeze(0)
+        if x.dim() != 3 or x.shape[-1] != self.in_features:
+            raise ValueError(f"expected a bag tensor [B, n, {self.in_features}], got {tuple(x.shape)}")
+        device = self.cls_token.device
+        if device.type != "cuda":
+            raise capi.TransmilError("TransMIL must be on a CUDA device (model.cuda()); there is no CPU path")
+        L = capi.lib()
+        B, n, D = (int(s) for s in x.shape)
+        flags = int(self.flags) | (capi.TM_FLAG_KEEP_STAGES if return_attn else 0)
+        with torch.cuda.device(device):
+            w = self._weights()
+            nbytes = C.c_size_t()
+            capi.check(L.tm_workspace_bytes(B, n, C.byref(w), flags, C.byref(nbytes)))
+            ws = self._workspace(nbytes.value, device)
+            logits = torch.empty((B, self.n_classes), dtype=torch.float32, device=device)
+            stream = torch.cuda.current_stream(device).cuda_stream
+            xd = x.detach()
+            if xd.dtype != torch.float32 or not xd.is_contiguous() or not xd.is_cuda:
+                # x.float() (TransMIL.py:174); host bags are copied on the current stream
+                xd = xd.to(device=device, dtype=torch.float32, non_blocking=True).contiguous()
+            capi.check(L.tm_transmil_fwd(C.byref(w), xd.data_ptr(), B, n, logits.data_ptr(), ws.data_ptr(),
+                                         ws.numel(), flags, stream))
+            self._stage_key = (B, n, flags)
+        if return_attn:
+            plan = capi.make_plan(n)
+            attn = LazyAttention(self, ws, w, B, n, flags, plan)
+            self._ws = None   # the lazy view owns this workspace now
+            return logits, (attn, int(plan.padding))
+        return logits
+
+    def stage(self, name):
+        """Per-stage buffer of the last forward (needs flags |= TM_FLAG_KEEP_STAGES); parity tests only."""
+        if self._ws is None or self._stage_key is None:
+            raise capi.TransmilError("no forward has been run")
+        B, n, flags = self._stage_key
+        return _stage_tensor(self, self._ws, self._weights(), name, B, n, flags)
+
+
+_STAGE_SHAPES = {
+    "h": lambda B, p: (B, p.S, 512), "p": lambda B, p: (B, p.Sp, 512), "q": lambda B, p: (B, 8, p.Sp, 64),
+    "l": lambda B, p: (B, 8, 256, 64), "m": lambda B, p: (B, 8, 256, 256)}
+_STAGE_KIND = {"h0": "h", "h1": "h", "h2": "h", "h3": "h", "xn": "p", "merged": "p", "q": "q", "k": "q", "v": "q",
+               "q_lm": "l", "k_lm": "l", "W3": "l", "M": "l", "attn2": "m", "Z": "m",
+               "q_lm1": "l", "k_lm1": "l", "W31": "l", "M1": "l", "attn21": "m", "Z1": "m"}
+
+
+def _stage_tensor(model, ws, w, name, B, n, flags):
+    ptr, numel = C.c_void_p(), C.c_int64()
+    capi.check(capi.lib().tm_stage_ptr(name.encode(), B, n, C.byref(w), flags, ws.data_ptr(), C.byref(ptr), C.byref(numel)))
+    off = ptr.value - ws.data_ptr()
+    plan = capi.make_plan(n)
+    shape = _STAGE_SHAPES[_STAGE_KIND[name]](B, plan)
+    return ws[off:off + 4 * numel.value].view(torch.float32).view(shape)
+
+
+class LazyAttention:
+    """Stands in for the dense `attn1 @ attn2_inv @ attn3` [B,8,Sp,Sp] tensor the
+    reference returns with return_attn=True (TransMIL.py:47,209-210).  Consumers read
+    single rows (`attn[0, :, padding+1, padding+1:padding+1+H]`, code/visualize_mil.py:581);
+    rows are computed on demand by tm_attn_rows_fwd from layer 2's q, k, landmarks and Z."""
+
+    MAX_DENSE_BYTES = 8 << 30
+
+    def __init__(self, model, ws, w, B, n, flags, plan):
+        self._ws, self._w, self._B, self._n, self._flags = ws, w, B, n, flags
+        self._model = model
+        self.Sp = int(plan.Sp)
+        self.shape = (B, 8, self.Sp, self.Sp)
+        self.device = ws.device
+        self.dtype = torch.float32
+
+    def size(self, dim=None):
+        return self.shape if dim is None else self.shape[dim]
+
+    def dim(self):
+        return 4
+
+    def rows(self, rows):
+        """[B, 8, len(rows), Sp] for the given padded row indices."""
+        rows = [int(r) % self.Sp for r in rows]
+        L = capi.lib()
+        st = {k: _stage_tensor(self._model, self._ws, self._w, k, self._B, self._n, self._flags)
+              for k in ("q", "k", "q_lm", "k_lm", "Z")}
+        out = torch.empty((self._B, 8, len(rows), self.Sp), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            for i0 in range(0, len(rows), 16):
+                chunk = rows[i0:i0 + 16]
+                nr = len(chunk)
+                scratch = torch.empty(int(L.tm_attn_rows_scratch_floats(self._B, self.Sp, nr)), dtype=torch.float32,
+                                      device=self.device)
+                tmp = torch.empty((self._B, 8, nr, self.Sp), dtype=torch.float32, device=self.device)
+                arr = (C.c_int64 * nr)(*chunk)
+                capi.check(L.tm_attn_rows_fwd(st["q"].data_ptr(), st["k"].data_ptr(), st["q_lm"].data_ptr(),
+                                              st["k_lm"].data_ptr(), st["Z"].data_ptr(), self._B, self.Sp, arr, nr,
+                                              tmp.data_ptr(), scratch.data_ptr(), stream))
+                out[:, :, i0:i0 + nr] = tmp
+        return out
+
+    def __getitem__(self, idx):
+        if not isinstance(idx, tuple):
+            idx = (idx,)
+        idx = idx + (slice(None),) * (4 - len(idx))
+        b, h, r, c = idx
+        if isinstance(r, slice):
+            rr = list(range(*r.indices(self.Sp)))
+            squeeze = False
+        elif isinstance(r, (list, tuple)):
+            rr, squeeze = list(r), False
+        else:
+            rr, squeeze = [int(r)], True
+        full = self.rows(rr)                      # [B,8,len,Sp]
+        full = full[b, h] if not (isinstance(b, slice) and isinstance(h, slice)) else full
+        # after indexing b,h the row axis moved left by the number of integer indices among (b,h)
+        lead = sum(1 for t in (b, h) if isinstance(t, slice))
+        sel = (slice(None),) * lead + ((0,) if squeeze else (slice(None),)) + (c,)
+        return full[sel]
+
+    def dense(self):
+        nbytes = self._B * 8 * self.Sp * self.Sp * 4
+        if nbytes > self.MAX_DENSE_BYTES:
+            raise MemoryError(f"dense attention would need {nbytes / 2**30:.1f} GiB; index rows instead")
+        return self.rows(range(self.Sp))
+
+
+def y_prob_y_hat(logits):
+    """ModelInterface.step post-processing (code/models/model_interface.py:323-324)."""
+    return torch.softmax(logits, dim=1), torch.argmax(logits, dim=1)
