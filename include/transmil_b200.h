@@ -107,6 +107,14 @@ int tm_device_supported(void);
 int64_t tm_launch_count(void);
 void tm_reset_launch_count(void);
 
+/* Per-stage CUDA-event profiler: while enabled, tm_transmil_fwd records an event on the
+ * launch stream at every stage boundary; tm_profile_read synchronises them and returns,
+ * per stage, the accumulated milliseconds and the number of intervals since the last read. */
+int tm_profile_enable(int on);
+int tm_profile_stage_count(void);
+const char* tm_profile_stage_name(int i);
+int tm_profile_read(double* ms_per_stage, int64_t* counts, int n_stages);
+
 /* ---- index contract (host only) --------------------------------------- */
 /* TransMIL.py:177-179 (G, N, dup), :184-186 (S), :190-193 (padding);
  * nystrom-attention forward (l, Sp, P). */

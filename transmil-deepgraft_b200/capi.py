@@ -45,6 +45,10 @@ SIGNATURES = {
     "tm_device_supported": (C.c_int, []),
     "tm_launch_count": (_i64, []),
     "tm_reset_launch_count": (None, []),
+    "tm_profile_enable": (C.c_int, [C.c_int]),
+    "tm_profile_stage_count": (C.c_int, []),
+    "tm_profile_stage_name": (C.c_char_p, [C.c_int]),
+    "tm_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(_i64), C.c_int]),
     "tm_make_plan": (C.c_int, [_i64, C.POINTER(Plan)]),
     "tm_dup_source": (_i64, [C.POINTER(Plan), _i64]),
     "tm_landmark_group": (_i64, [C.POINTER(Plan), _i64]),
@@ -111,3 +115,13 @@ def make_plan(n):
     p = Plan()
     check(lib().tm_make_plan(int(n), C.byref(p)))
     return p
+
+
+def profile_read():
+    """{stage: (total_ms, intervals)} since the last read (see tm_profile_enable)."""
+    L = lib()
+    n = L.tm_profile_stage_count()
+    ms = (C.c_double * n)()
+    cnt = (C.c_int64 * n)()
+    check(L.tm_profile_read(ms, cnt, n))
+    return {L.tm_profile_stage_name(i).decode(): (ms[i], int(cnt[i])) for i in range(n) if cnt[i] > 0}

@@ -12,6 +12,10 @@ namespace tmil {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 
+enum Stage : int { ST_FC1_GEMM0 = 0, ST_FC1_LN, ST_FC1_GEMM1, ST_FC1_TAIL, ST_LN_PAD, ST_QKV, ST_LANDMARKS, ST_PINV, ST_ATTN3V,
+                   ST_ZW, ST_NYSTROM_OUT, ST_TO_OUT, ST_PPEG, ST_HEAD, ST_END, ST_COUNT };
+void prof_mark(int stage, cudaStream_t st);
+
 #define TM_CHECK_ARG(cond, code, ...)  \
   do {                                 \
     if (!(cond)) {                     \

@@ -93,13 +93,21 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
   float* attn2 = ws + L.small[li][SM_ATTN2]; float* Z = ws + L.small[li][SM_Z];
   float* W3 = ws + L.small[li][SM_W3]; float* M = ws + L.small[li][SM_M];
   float* merged = ws + L.merged;
+  prof_mark(ST_LN_PAD, st);
   TM_PROPAGATE(tm_ln_pad_fwd(h_in, lw.norm_w, lw.norm_b, B, p.S, p.P, xn, st));
+  prof_mark(ST_QKV, st);
   TM_PROPAGATE(tm_qkv_fwd(xn, lw.qkv_w, B, p.Sp, q, k, v, flags, st));
+  prof_mark(ST_LANDMARKS, st);
   TM_PROPAGATE(tm_landmarks_fwd(q, k, B, p.Sp, p.l, q_lm, k_lm, st));
+  prof_mark(ST_PINV, st);
   TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, st));
+  prof_mark(ST_ATTN3V, st);
   TM_PROPAGATE(tm_attn3v_fwd(q_lm, k, v, B, p.Sp, W3, ws + L.a3_s, flags, st));
+  prof_mark(ST_ZW, st);
   TM_PROPAGATE(tm_zw_fwd(Z, W3, B, M, st));
+  prof_mark(ST_NYSTROM_OUT, st);
   TM_PROPAGATE(tm_nystrom_out_fwd(q, k_lm, M, v, lw.conv_w, B, p.Sp, merged, flags, st));
+  prof_mark(ST_TO_OUT, st);
   TM_PROPAGATE(tm_to_out_residual_fwd(merged, lw.out_w, lw.out_b, h_in, B, p.S, p.P, h_out, flags, st));
   return TM_OK;
 }
@@ -126,14 +134,18 @@ extern "C" int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_
     TM_CHECK_ARG(scratch != nullptr, TM_ERR_BAD_ARGUMENT, "tm_fc1_fwd: scratch is required for the two-Linear stems");
     g.A = x; g.Bm = w->fc1_w0; g.C = scratch; g.bias = w->fc1_b0;
     g.M = (int)(B * n); g.N = F0; g.K = D; g.lda = D; g.ldb = D; g.ldc = F0;
+    prof_mark(ST_FC1_GEMM0, st);
     TM_PROPAGATE(gemm_auto(g, flags, st));
+    prof_mark(ST_FC1_LN, st);
     TM_PROPAGATE(ln_inplace(scratch, w->fc1_ln_w, w->fc1_ln_b, B * n, F0, 0, 0, 0, st));
     a2 = scratch; k2 = F0; w2 = w->fc1_w1; b2 = w->fc1_b1;
   }
   g.A = a2; g.Bm = w2; g.C = h0; g.bias = b2;
   g.M = (int)(B * n); g.N = TM_DIM; g.K = k2; g.lda = k2; g.ldb = k2; g.ldc = TM_DIM;
   g.rows_per_bag = (int)n; g.a_bag_rows = n; g.a_row_off = 0; g.c_bag_rows = p.S; g.c_row_off = 1; g.dup = (int)p.dup;
+  prof_mark(ST_FC1_GEMM1, st);
   TM_PROPAGATE(gemm_auto(g, flags, st));
+  prof_mark(ST_FC1_TAIL, st);
   if (w->fc1_kind == TM_FC1_768)  // trailing LayerNorm(512) on every token row (row 0 is the cls token)
     TM_PROPAGATE(ln_inplace(h0, w->fc1_ln2_w, w->fc1_ln2_b, B * p.N, TM_DIM, (int)p.N, p.S, 1, st));
   cls_rows_kernel<<<(unsigned)B, TM_DIM / 4, 0, st>>>(w->cls_token, p.S * (long long)TM_DIM, h0);
@@ -191,9 +203,12 @@ extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, i
   float* ws = (float*)workspace;
   TM_PROPAGATE(tm_fc1_fwd(w, x, B, n, ws + L.h[0], ws + L.fc1s, flags, st));
   TM_PROPAGATE(layer_fwd(w->layer1, p, B, ws + L.h[0], ws + L.h[1], ws, L, 0, flags, st));
+  prof_mark(ST_PPEG, st);
   TM_PROPAGATE(tm_ppeg_fwd(w, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
   TM_PROPAGATE(layer_fwd(w->layer2, p, B, ws + L.h[2], ws + L.h[3], ws, L, 1, flags, st));
+  prof_mark(ST_HEAD, st);
   TM_PROPAGATE(tm_head_fwd(w, ws + L.h[3], B, p.S, logits, st));
+  prof_mark(ST_END, st);
   return TM_OK;
 }
 

@@ -2,6 +2,9 @@
 #include <math.h>
 #include <stdarg.h>
 
+#include <utility>
+#include <vector>
+
 #include "common.cuh"
 
 namespace tmil {
@@ -14,6 +17,21 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 void count_launch(int n) { g_launches += n; }
+
+// ---- per-stage CUDA-event profiler (bench.py's roofline numbers) -----------
+static const char* kStageNames[ST_COUNT] = {"fc1_gemm0", "fc1_ln", "fc1_gemm1", "fc1_tail", "ln_pad", "qkv", "landmarks",
+                                            "pinv", "attn3v", "zw", "nystrom_out", "to_out", "ppeg", "head", "end"};
+static bool g_prof_on = false;
+static std::vector<std::pair<int, cudaEvent_t>> g_marks;
+static std::vector<cudaEvent_t> g_pool;
+void prof_mark(int stage, cudaStream_t st) {
+  if (!g_prof_on) return;
+  cudaEvent_t ev;
+  if (!g_pool.empty()) { ev = g_pool.back(); g_pool.pop_back(); }
+  else if (cudaEventCreate(&ev) != cudaSuccess) return;
+  cudaEventRecord(ev, st);
+  g_marks.emplace_back(stage, ev);
+}
 }  // namespace tmil
 
 extern "C" {
@@ -22,6 +40,29 @@ const char* tm_version(void) { return "transmil_b200 0.1 (sm_100a)"; }
 const char* tm_last_error(void) { return tmil::g_err; }
 int64_t tm_launch_count(void) { return tmil::g_launches; }
 void tm_reset_launch_count(void) { tmil::g_launches = 0; }
+
+int tm_profile_enable(int on) {
+  tmil::g_prof_on = on != 0;
+  return TM_OK;
+}
+int tm_profile_stage_count(void) { return tmil::ST_COUNT - 1; }
+const char* tm_profile_stage_name(int i) { return (i >= 0 && i < tmil::ST_COUNT) ? tmil::kStageNames[i] : ""; }
+int tm_profile_read(double* ms, int64_t* counts, int n) {
+  // Synchronises the recorded events; accumulates the time from each mark to the next one into the mark's stage.
+  using namespace tmil;
+  for (int i = 0; i < n; ++i) { ms[i] = 0.0; counts[i] = 0; }
+  for (size_t i = 0; i + 1 < g_marks.size(); ++i) {
+    const int stg = g_marks[i].first;
+    if (stg == ST_END) continue;
+    float t = 0.f;
+    cudaEventSynchronize(g_marks[i + 1].second);
+    if (cudaEventElapsedTime(&t, g_marks[i].second, g_marks[i + 1].second) != cudaSuccess) continue;
+    if (stg < n) { ms[stg] += t; counts[stg] += 1; }
+  }
+  for (auto& m : g_marks) g_pool.push_back(m.second);
+  g_marks.clear();
+  return TM_OK;
+}
 
 int tm_device_supported(void) {
   int dev = 0;
