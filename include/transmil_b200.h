@@ -51,6 +51,9 @@ typedef enum tm_fc1_kind {
 /* Flags for tm_transmil_fwd / tm_workspace_bytes. */
 #define TM_FLAG_SIMT_ONLY 1u     /* force the fp32 CUDA-core kernels (on-device cross-check of the tensor-core path) */
 #define TM_FLAG_KEEP_STAGES 2u   /* keep per-stage buffers addressable through tm_stage_ptr */
+#define TM_FLAG_TF32_OPERANDS 4u /* producers round (cvt.rna) the tensors that feed tensor-core contractions to tf32, so the
+                                    MMA's operand truncation is exact; set internally by tm_transmil_fwd when the tcgen05
+                                    engine runs.  Callers of the per-kernel entry points pass it themselves. */
 
 /* Index contract of one bag (TransMIL.py:177-179,184-186,190-193 and the
  * nystrom-attention 0.0.11 front pad / landmark grouping).  Pure host code. */
@@ -167,7 +170,7 @@ int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n, float*
 /* K3: TransLayer.norm (TransMIL.py:23,47) + the FRONT zero pad of
  * NystromAttention.forward.  h [B,S,512] -> xn [B,Sp,512] (rows < P zero). */
 int tm_ln_pad_fwd(const float* h, const float* gamma, const float* beta, int64_t B, int64_t S,
-                  int64_t P, float* xn, void* stream);
+                  int64_t P, float* xn, uint32_t flags, void* stream);
 
 /* K4: to_qkv (no bias), head split 'b n (h d) -> b h n d', q *= 64^-0.5.
  * xn [B,Sp,512] -> q,k,v [B,8,Sp,64]. */
@@ -223,6 +226,9 @@ int tm_attn_rows_fwd(const float* q, const float* k, const float* q_lm, const fl
                      const float* Z, int64_t B, int64_t Sp, const int64_t* rows_host,
                      int64_t n_rows, float* out, float* scratch, void* stream);
 int64_t tm_attn_rows_scratch_floats(int64_t B, int64_t Sp, int64_t n_rows);
+
+/* dst[i] = tf32-rounded (round to nearest, ties away: cvt.rna.tf32.f32) src[i]; dst may alias src. */
+int tm_round_tf32(const float* src, float* dst, int64_t n, void* stream);
 
 /* Generic fp32 GEMM of the library (C[M,N] = A[M,K] W[N,K]^T), exposed for tests. */
 int tm_gemm_nt(const float* A, const float* W, float* C, int64_t M, int64_t N, int64_t K,

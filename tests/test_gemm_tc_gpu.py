@@ -1,0 +1,48 @@
+"""GPU suite: the tcgen05/TMA GEMM against torch fp32 matmul and the CUDA-core engine."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _tf32(x):
+    xi = x.contiguous().view(torch.int32)
+    r = ((xi >> 13) & 1) + 0xFFF
+    return ((xi + r) & ~0x1FFF).view(torch.float32)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 32), (128, 256, 64), (256, 512, 512), (1000, 512, 1024), (5000, 1536, 512),
+                                   (130, 768, 768), (4099, 1024, 2048), (777, 512, 384), (300, 512, 784)])
+def test_gemm_tc_matches_fp32(built_lib, M, N, K):
+    import transmil_b200 as T
+    L = T.capi.lib()
+    g = torch.Generator().manual_seed(M * 7 + N + K)
+    A = _tf32(torch.randn(M, K, generator=g)).cuda()
+    W = _tf32(torch.randn(N, K, generator=g) * 0.05).cuda()
+    C_tc = torch.full((M, N), float("nan"), device="cuda")
+    C_simt = torch.empty((M, N), device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    T.capi.check(L.tm_gemm_nt(A.data_ptr(), W.data_ptr(), C_tc.data_ptr(), M, N, K, 0, st))
+    T.capi.check(L.tm_gemm_nt(A.data_ptr(), W.data_ptr(), C_simt.data_ptr(), M, N, K, T.capi.TM_FLAG_SIMT_ONLY, st))
+    torch.cuda.synchronize()
+    ref = (A.double() @ W.double().T)
+    scale = ref.abs().max().item()
+    assert torch.isfinite(C_tc).all()
+    e_simt = (C_simt.double() - ref).abs().max().item() / scale
+    e_tc = (C_tc.double() - ref).abs().max().item() / scale
+    assert e_simt < 2e-6, e_simt
+    assert e_tc < 2e-6, f"tcgen05 GEMM error {e_tc:.3e} (operands are tf32-exact, accumulation is fp32)"
+
+
+def test_gemm_tc_truncates_unrounded_operands(built_lib):
+    """Unrounded fp32 operands are truncated to tf32 by the tensor core: error ~2^-10 relative, not garbage."""
+    import transmil_b200 as T
+    L = T.capi.lib()
+    g = torch.Generator().manual_seed(1)
+    A = torch.rand(512, 1024, generator=g).cuda()
+    W = (torch.randn(512, 1024, generator=g) * 0.03).cuda()
+    C = torch.empty(512, 512, device="cuda")
+    T.capi.check(L.tm_gemm_nt(A.data_ptr(), W.data_ptr(), C.data_ptr(), 512, 512, 1024, 0, torch.cuda.current_stream().cuda_stream))
+    ref = A.double() @ W.double().T
+    rel = (C.double() - ref).abs().max().item() / ref.abs().max().item()
+    assert rel < 5e-3

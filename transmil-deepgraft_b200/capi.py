@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libtransmil_b200.so")
 
 TM_FLAG_SIMT_ONLY = 1
 TM_FLAG_KEEP_STAGES = 2
+TM_FLAG_TF32_OPERANDS = 4
 TM_FC1_SINGLE, TM_FC1_2048, TM_FC1_768 = 0, 1, 2
 
 _fp = C.c_void_p  # device/host float pointers travel as raw addresses
@@ -59,7 +60,8 @@ SIGNATURES = {
     "tm_transmil_fwd_host": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _fp, _fp, _sz, _u32, _fp]),
     "tm_stage_ptr": (C.c_int, [C.c_char_p, _i64, _i64, _PW, _u32, _fp, C.POINTER(C.c_void_p), C.POINTER(_i64)]),
     "tm_fc1_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
-    "tm_ln_pad_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _fp, _fp]),
+    "tm_ln_pad_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _fp, _u32, _fp]),
+    "tm_round_tf32": (C.c_int, [_fp, _fp, _i64, _fp]),
     "tm_qkv_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _u32, _fp]),
     "tm_landmarks_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _fp, _fp, _fp]),
     "tm_pinv_scratch_floats": (_i64, [_i64]),

@@ -87,11 +87,12 @@ struct GemmParams {
   float alpha, beta;
   const float* L; int ldl;     // EPI_AXPBY second term / EPI_BIAS_RESID residual
   const float* bias;
-  // row maps: logical row r in [0,M): bag = r / rows_per_bag, i = r % rows_per_bag
-  int rows_per_bag;            // 0 = identity maps
-  long long a_bag_rows; int a_row_off;   // A row  = bag*a_bag_rows + a_row_off + i
-  long long c_bag_rows; int c_row_off;   // C row  = bag*c_bag_rows + c_row_off + i
-  int dup;                     // rows i < dup are also written at c_row_off + rows_per_bag + i
+  // C row map: logical row r in [0,M): bag = r / rows_per_bag, i = r % rows_per_bag;
+  // rows with i < c_skip are not stored; C row = bag*c_bag_rows + c_row_off + (i - c_skip)
+  int rows_per_bag;            // 0 = identity
+  long long c_bag_rows; int c_row_off; int c_skip;
+  int dup;                     // EPI_BIAS_GELU: rows i < dup are also written rows_per_bag rows further down
+  int round_out;               // round stored values to tf32 (consumer is a tensor-core contraction)
   // EPI_QKV
   float* q; float* k; float* v; int Sp;
 };

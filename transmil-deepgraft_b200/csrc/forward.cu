@@ -9,10 +9,12 @@ extern "C" int64_t tm_pinv_scratch_floats(int64_t B);
 namespace tmil {
 
 int ln_inplace(float* x, const float* gamma, const float* beta, long long rows, int width, int rpb, long long bag_rows,
-               int off, cudaStream_t st);
+               int off, bool round, cudaStream_t st);
+
+static bool use_tc(uint32_t flags) { return !(flags & TM_FLAG_SIMT_ONLY) && tc_available(); }
 
 static int gemm_auto(const GemmParams& p, uint32_t flags, cudaStream_t st) {
-  if (!(flags & TM_FLAG_SIMT_ONLY) && tc_available()) return gemm_tc(p, st);
+  if (use_tc(flags)) return gemm_tc(p, st);
   return gemm_simt(p, st);
 }
 
@@ -33,6 +35,7 @@ static int fc1_width(const tm_weights* w) {
 struct Layout {
   size_t total;  // floats
   size_t h[4], fc1s, xn, merged, q, k, v, small[2][6], pinv_s, a3_s, packed;
+  size_t wr_fc1_0, wr_fc1_1, wr_qkv[2], wr_out[2];   // tf32-rounded copies of the GEMM weights
 };
 enum { SM_QLM = 0, SM_KLM, SM_ATTN2, SM_Z, SM_W3, SM_M };
 
@@ -70,6 +73,12 @@ static int make_layout(int64_t B, const tm_plan& p, const tm_weights* w, uint32_
   L->pinv_s = bump(cur, (size_t)tm_pinv_scratch_floats(B));
   L->a3_s = bump(cur, (size_t)tm_attn3v_scratch_floats(B, p.Sp));
   L->packed = bump(cur, 50 * TM_DIM);
+  L->wr_fc1_0 = bump(cur, (size_t)(f0 ? f0 : TM_DIM) * w->in_features);
+  L->wr_fc1_1 = bump(cur, (size_t)TM_DIM * f0);
+  for (int l = 0; l < 2; ++l) {
+    L->wr_qkv[l] = bump(cur, (size_t)3 * TM_DIM * TM_DIM);
+    L->wr_out[l] = bump(cur, (size_t)TM_DIM * TM_DIM);
+  }
   L->total = cur;
   return TM_OK;
 }
@@ -94,7 +103,7 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
   float* W3 = ws + L.small[li][SM_W3]; float* M = ws + L.small[li][SM_M];
   float* merged = ws + L.merged;
   prof_mark(ST_LN_PAD, st);
-  TM_PROPAGATE(tm_ln_pad_fwd(h_in, lw.norm_w, lw.norm_b, B, p.S, p.P, xn, st));
+  TM_PROPAGATE(tm_ln_pad_fwd(h_in, lw.norm_w, lw.norm_b, B, p.S, p.P, xn, flags, st));
   prof_mark(ST_QKV, st);
   TM_PROPAGATE(tm_qkv_fwd(xn, lw.qkv_w, B, p.Sp, q, k, v, flags, st));
   prof_mark(ST_LANDMARKS, st);
@@ -137,17 +146,17 @@ extern "C" int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_
     prof_mark(ST_FC1_GEMM0, st);
     TM_PROPAGATE(gemm_auto(g, flags, st));
     prof_mark(ST_FC1_LN, st);
-    TM_PROPAGATE(ln_inplace(scratch, w->fc1_ln_w, w->fc1_ln_b, B * n, F0, 0, 0, 0, st));
+    TM_PROPAGATE(ln_inplace(scratch, w->fc1_ln_w, w->fc1_ln_b, B * n, F0, 0, 0, 0, (flags & TM_FLAG_TF32_OPERANDS) != 0, st));
     a2 = scratch; k2 = F0; w2 = w->fc1_w1; b2 = w->fc1_b1;
   }
   g.A = a2; g.Bm = w2; g.C = h0; g.bias = b2;
   g.M = (int)(B * n); g.N = TM_DIM; g.K = k2; g.lda = k2; g.ldb = k2; g.ldc = TM_DIM;
-  g.rows_per_bag = (int)n; g.a_bag_rows = n; g.a_row_off = 0; g.c_bag_rows = p.S; g.c_row_off = 1; g.dup = (int)p.dup;
+  g.rows_per_bag = (int)n; g.c_bag_rows = p.S; g.c_row_off = 1; g.c_skip = 0; g.dup = (int)p.dup;
   prof_mark(ST_FC1_GEMM1, st);
   TM_PROPAGATE(gemm_auto(g, flags, st));
   prof_mark(ST_FC1_TAIL, st);
   if (w->fc1_kind == TM_FC1_768)  // trailing LayerNorm(512) on every token row (row 0 is the cls token)
-    TM_PROPAGATE(ln_inplace(h0, w->fc1_ln2_w, w->fc1_ln2_b, B * p.N, TM_DIM, (int)p.N, p.S, 1, st));
+    TM_PROPAGATE(ln_inplace(h0, w->fc1_ln2_w, w->fc1_ln2_b, B * p.N, TM_DIM, (int)p.N, p.S, 1, false, st));
   cls_rows_kernel<<<(unsigned)B, TM_DIM / 4, 0, st>>>(w->cls_token, p.S * (long long)TM_DIM, h0);
   TM_LAUNCH_CHECK();
   return TM_OK;
@@ -162,6 +171,7 @@ extern "C" int tm_qkv_fwd(const float* xn, const float* qkv_w, int64_t B, int64_
   g.A = xn; g.Bm = qkv_w; g.C = nullptr;
   g.M = (int)(B * Sp); g.N = 3 * TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = 3 * TM_DIM;
   g.batch = 1; g.epi = EPI_QKV; g.q = q; g.k = k; g.v = v; g.Sp = (int)Sp;
+  g.round_out = (flags & TM_FLAG_TF32_OPERANDS) ? 1 : 0;
   return gemm_auto(g, flags, (cudaStream_t)stream);
 }
 
@@ -172,9 +182,10 @@ extern "C" int tm_to_out_residual_fwd(const float* merged, const float* out_w, c
   GemmParams g;
   memset(&g, 0, sizeof(g));
   g.A = merged; g.Bm = out_w; g.C = h_out; g.bias = out_b; g.L = h_in; g.ldl = TM_DIM;
-  g.M = (int)(B * S); g.N = TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = TM_DIM;
+  // all Sp padded rows go through the GEMM (identity A rows, TMA friendly); the epilogue drops the P front-pad rows
+  g.M = (int)(B * (S + P)); g.N = TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = TM_DIM;
   g.batch = 1; g.epi = EPI_BIAS_RESID;
-  g.rows_per_bag = (int)S; g.a_bag_rows = S + P; g.a_row_off = (int)P; g.c_bag_rows = S; g.c_row_off = 0;
+  g.rows_per_bag = (int)(S + P); g.c_bag_rows = S; g.c_row_off = 0; g.c_skip = (int)P;
   return gemm_auto(g, flags, (cudaStream_t)stream);
 }
 
@@ -201,13 +212,33 @@ extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, i
   TM_CHECK_ARG(workspace_bytes >= L.total * sizeof(float), TM_ERR_WORKSPACE_TOO_SMALL, "tm_transmil_fwd: workspace too small (%zu < %zu bytes)", workspace_bytes, L.total * sizeof(float));
   cudaStream_t st = (cudaStream_t)stream;
   float* ws = (float*)workspace;
-  TM_PROPAGATE(tm_fc1_fwd(w, x, B, n, ws + L.h[0], ws + L.fc1s, flags, st));
-  TM_PROPAGATE(layer_fwd(w->layer1, p, B, ws + L.h[0], ws + L.h[1], ws, L, 0, flags, st));
+  tm_weights wl = *w;
+  if (use_tc(flags)) {
+    // tensor-core engine: every tensor that feeds a tf32 contraction is rounded by its producer; the (static) GEMM
+    // weights are rounded here into the workspace.  The user's bag x is read as is (operand truncation by the MMA).
+    flags |= TM_FLAG_TF32_OPERANDS;
+    const int f0 = fc1_width(w);
+    TM_PROPAGATE(tm_round_tf32(w->fc1_w0, ws + L.wr_fc1_0, (int64_t)(f0 ? f0 : TM_DIM) * w->in_features, st));
+    wl.fc1_w0 = ws + L.wr_fc1_0;
+    if (f0) {
+      TM_PROPAGATE(tm_round_tf32(w->fc1_w1, ws + L.wr_fc1_1, (int64_t)TM_DIM * f0, st));
+      wl.fc1_w1 = ws + L.wr_fc1_1;
+    }
+    tm_layer_weights* lws[2] = {&wl.layer1, &wl.layer2};
+    for (int l = 0; l < 2; ++l) {
+      TM_PROPAGATE(tm_round_tf32(lws[l]->qkv_w, ws + L.wr_qkv[l], (int64_t)3 * TM_DIM * TM_DIM, st));
+      TM_PROPAGATE(tm_round_tf32(lws[l]->out_w, ws + L.wr_out[l], (int64_t)TM_DIM * TM_DIM, st));
+      lws[l]->qkv_w = ws + L.wr_qkv[l];
+      lws[l]->out_w = ws + L.wr_out[l];
+    }
+  }
+  TM_PROPAGATE(tm_fc1_fwd(&wl, x, B, n, ws + L.h[0], ws + L.fc1s, flags, st));
+  TM_PROPAGATE(layer_fwd(wl.layer1, p, B, ws + L.h[0], ws + L.h[1], ws, L, 0, flags, st));
   prof_mark(ST_PPEG, st);
-  TM_PROPAGATE(tm_ppeg_fwd(w, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
-  TM_PROPAGATE(layer_fwd(w->layer2, p, B, ws + L.h[2], ws + L.h[3], ws, L, 1, flags, st));
+  TM_PROPAGATE(tm_ppeg_fwd(&wl, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
+  TM_PROPAGATE(layer_fwd(wl.layer2, p, B, ws + L.h[2], ws + L.h[3], ws, L, 1, flags, st));
   prof_mark(ST_HEAD, st);
-  TM_PROPAGATE(tm_head_fwd(w, ws + L.h[3], B, p.S, logits, st));
+  TM_PROPAGATE(tm_head_fwd(&wl, ws + L.h[3], B, p.S, logits, st));
   prof_mark(ST_END, st);
   return TM_OK;
 }

@@ -5,64 +5,11 @@
 // tcgen05/TMA GEMMs in gemm_tc.cu (TM_FLAG_SIMT_ONLY).  128x128x16 CTA tile,
 // 256 threads, 8x8 register micro-tile, register-staged double buffering.
 #include "common.cuh"
+#include "gemm_epilogue.cuh"
 
 namespace tmil {
 
 constexpr int BM = 128, BN = 128, BK = 16, NT = 256;
-
-__device__ __forceinline__ long long map_row(int r, int rows_per_bag, long long bag_rows, int off) {
-  if (rows_per_bag <= 0) return r;
-  int bag = r / rows_per_bag;
-  int i = r - bag * rows_per_bag;
-  return (long long)bag * bag_rows + off + i;
-}
-
-__device__ __forceinline__ void epilogue_store4(const GemmParams& p, int r, int c, float4 acc,
-                                                const float* __restrict__ Lb, float* __restrict__ Cb) {
-  // r, c: logical row / first of 4 consecutive columns (c % 4 == 0, c + 3 < N guaranteed by caller)
-  switch (p.epi) {
-    case EPI_AXPBY: {
-      float4 o = make_float4(p.alpha * acc.x, p.alpha * acc.y, p.alpha * acc.z, p.alpha * acc.w);
-      if (Lb != nullptr) {
-        float4 l = *reinterpret_cast<const float4*>(Lb + (long long)r * p.ldl + c);
-        o.x = fmaf(p.beta, l.x, o.x); o.y = fmaf(p.beta, l.y, o.y);
-        o.z = fmaf(p.beta, l.z, o.z); o.w = fmaf(p.beta, l.w, o.w);
-      }
-      *reinterpret_cast<float4*>(Cb + (long long)r * p.ldc + c) = o;
-      break;
-    }
-    case EPI_BIAS_GELU: {
-      float4 b = *reinterpret_cast<const float4*>(p.bias + c);
-      float4 o = make_float4(gelu_erf(acc.x + b.x), gelu_erf(acc.y + b.y), gelu_erf(acc.z + b.z), gelu_erf(acc.w + b.w));
-      long long cr = map_row(r, p.rows_per_bag, p.c_bag_rows, p.c_row_off);
-      *reinterpret_cast<float4*>(Cb + cr * p.ldc + c) = o;
-      if (p.dup > 0) {
-        int i = r % p.rows_per_bag;
-        if (i < p.dup) *reinterpret_cast<float4*>(Cb + (cr + p.rows_per_bag) * p.ldc + c) = o;
-      }
-      break;
-    }
-    case EPI_QKV: {
-      int which = c / TM_DIM;
-      int cc = c - which * TM_DIM;
-      int hh = cc / TM_DHEAD, d = cc % TM_DHEAD;
-      int bag = r / p.Sp, t = r - bag * p.Sp;
-      float* base = which == 0 ? p.q : (which == 1 ? p.k : p.v);
-      float s = which == 0 ? 0.125f : 1.0f;  // q * dim_head^-0.5
-      float4 o = make_float4(acc.x * s, acc.y * s, acc.z * s, acc.w * s);
-      *reinterpret_cast<float4*>(base + (((long long)bag * TM_HEADS + hh) * p.Sp + t) * TM_DHEAD + d) = o;
-      break;
-    }
-    case EPI_BIAS_RESID: {
-      float4 b = *reinterpret_cast<const float4*>(p.bias + c);
-      long long cr = map_row(r, p.rows_per_bag, p.c_bag_rows, p.c_row_off);
-      float4 l = *reinterpret_cast<const float4*>(p.L + cr * p.ldl + c);
-      float4 o = make_float4(l.x + (acc.x + b.x), l.y + (acc.y + b.y), l.z + (acc.z + b.z), l.w + (acc.w + b.w));
-      *reinterpret_cast<float4*>(Cb + cr * p.ldc + c) = o;
-      break;
-    }
-  }
-}
 
 template <bool B_IS_KN>
 __global__ void __launch_bounds__(NT, 2) gemm_simt_kernel(const GemmParams p) {
@@ -84,8 +31,7 @@ __global__ void __launch_bounds__(NT, 2) gemm_simt_kernel(const GemmParams p) {
     a_r[i] = idx >> 2; a_k[i] = (idx & 3) * 4;
     int gr = m0 + a_r[i];
     a_ok[i] = gr < p.M;
-    long long ar = a_ok[i] ? map_row(gr, p.rows_per_bag, p.a_bag_rows, p.a_row_off) : 0;
-    a_ptr[i] = Ab + ar * p.lda + a_k[i];
+    a_ptr[i] = Ab + (long long)(a_ok[i] ? gr : 0) * p.lda + a_k[i];
   }
   const float* b_ptr[2]; bool b_ok[2]; int b_r[2], b_c[2];
 #pragma unroll

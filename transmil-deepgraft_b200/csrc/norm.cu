@@ -2,11 +2,12 @@
 // stems, and the cls-row head (final LayerNorm + _fc).  All HBM-bound: one warp
 // per row, 128-bit loads, row kept in registers between the two passes.
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace tmil {
 
 // One warp normalises one row of width W (multiple of 128, <= 1024).
-template <int W>
+template <int W, bool ROUND = false>
 __device__ __forceinline__ void warp_layernorm_row(const float* src, float* dst,
                                                    const float* __restrict__ gamma, const float* __restrict__ beta, int lane) {
   constexpr int V = W / 128;  // float4 per lane
@@ -35,11 +36,13 @@ __device__ __forceinline__ void warp_layernorm_row(const float* src, float* dst,
     o.y = (x[i].y - mean) * rstd * g.y + b.y;
     o.z = (x[i].z - mean) * rstd * g.z + b.z;
     o.w = (x[i].w - mean) * rstd * g.w + b.w;
+    if (ROUND) { o.x = round_tf32(o.x); o.y = round_tf32(o.y); o.z = round_tf32(o.z); o.w = round_tf32(o.w); }
     *reinterpret_cast<float4*>(dst + c) = o;
   }
 }
 
 // xn[b, t] = t < P ? 0 : LN(h[b, t - P])
+template <bool ROUND>
 __global__ void __launch_bounds__(256) ln_pad_kernel(const float* __restrict__ h, const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, long long rows, int S, int Sp, int P,
                                                      float* __restrict__ xn) {
@@ -54,11 +57,11 @@ __global__ void __launch_bounds__(256) ln_pad_kernel(const float* __restrict__ h
     for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(dst + (i * 32 + lane) * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
     return;
   }
-  warp_layernorm_row<TM_DIM>(h + (b * S + (t - P)) * TM_DIM, dst, gamma, beta, lane);
+  warp_layernorm_row<TM_DIM, ROUND>(h + (b * S + (t - P)) * TM_DIM, dst, gamma, beta, lane);
 }
 
 // In-place LayerNorm over mapped rows: row r -> (r / rpb) * bag_rows + off + r % rpb.
-template <int W>
+template <int W, bool ROUND>
 __global__ void __launch_bounds__(256) ln_inplace_kernel(float* __restrict__ x, const float* __restrict__ gamma,
                                                          const float* __restrict__ beta, long long rows, int rpb,
                                                          long long bag_rows, int off) {
@@ -71,25 +74,36 @@ __global__ void __launch_bounds__(256) ln_inplace_kernel(float* __restrict__ x, 
     rr = b * bag_rows + off + (row - b * rpb);
   }
   float* p = x + rr * W;
-  warp_layernorm_row<W>(p, p, gamma, beta, lane);
+  warp_layernorm_row<W, ROUND>(p, p, gamma, beta, lane);
 }
 
 int ln_inplace(float* x, const float* gamma, const float* beta, long long rows, int width, int rpb, long long bag_rows,
-               int off, cudaStream_t st) {
+               int off, bool round, cudaStream_t st) {
   if (rows <= 0) return TM_OK;
   unsigned grid = (unsigned)ceil_div(rows, 8);
-  if (width == 512)
-    ln_inplace_kernel<512><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
-  else if (width == 768)
-    ln_inplace_kernel<768><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
-  else if (width == 1024)
-    ln_inplace_kernel<1024><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+  if (width == 512 && !round)
+    ln_inplace_kernel<512, false><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+  else if (width == 768 && !round)
+    ln_inplace_kernel<768, false><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+  else if (width == 1024 && !round)
+    ln_inplace_kernel<1024, false><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+  else if (width == 768 && round)
+    ln_inplace_kernel<768, true><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+  else if (width == 1024 && round)
+    ln_inplace_kernel<1024, true><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
   else {
     set_error("ln_inplace: unsupported width %d", width);
     return TM_ERR_BAD_SHAPE;
   }
   TM_LAUNCH_CHECK();
   return TM_OK;
+}
+
+__global__ void __launch_bounds__(256) round_tf32_kernel(const float* __restrict__ src, float* __restrict__ dst, long long n4) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    float4 v = reinterpret_cast<const float4*>(src)[i];
+    reinterpret_cast<float4*>(dst)[i] = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+  }
 }
 
 // cls row: logits[b] = _fc(LayerNorm(h[b, 0]))
@@ -119,14 +133,28 @@ __global__ void __launch_bounds__(128) head_kernel(const float* __restrict__ h, 
 
 }  // namespace tmil
 
+extern "C" int tm_round_tf32(const float* src, float* dst, int64_t n, void* stream) {
+  TM_CHECK_ARG(src && dst && n >= 0 && n % 4 == 0 && tmil::aligned16(src) && tmil::aligned16(dst), TM_ERR_BAD_ALIGNMENT,
+               "tm_round_tf32: n must be a multiple of 4 and the pointers 16-byte aligned");
+  if (n == 0) return TM_OK;
+  long long blocks = tmil::ceil_div(n / 4, 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  tmil::round_tf32_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, n / 4);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
 extern "C" int tm_ln_pad_fwd(const float* h, const float* gamma, const float* beta, int64_t B, int64_t S, int64_t P,
-                             float* xn, void* stream) {
+                             float* xn, uint32_t flags, void* stream) {
   TM_CHECK_ARG(B > 0 && S > 0 && P >= 0 && (S + P) % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE,
                "tm_ln_pad_fwd: S+P must be a multiple of 256 (S=%lld P=%lld)", (long long)S, (long long)P);
   TM_CHECK_ARG(tmil::aligned16(h) && tmil::aligned16(xn) && tmil::aligned16(gamma) && tmil::aligned16(beta), TM_ERR_BAD_ALIGNMENT,
                "tm_ln_pad_fwd: pointers must be 16-byte aligned");
   const long long rows = (long long)B * (S + P);
-  tmil::ln_pad_kernel<<<(unsigned)tmil::ceil_div(rows, 8), 256, 0, (cudaStream_t)stream>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+  if (flags & TM_FLAG_TF32_OPERANDS)
+    tmil::ln_pad_kernel<true><<<(unsigned)tmil::ceil_div(rows, 8), 256, 0, (cudaStream_t)stream>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+  else
+    tmil::ln_pad_kernel<false><<<(unsigned)tmil::ceil_div(rows, 8), 256, 0, (cudaStream_t)stream>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -7,12 +7,14 @@
 // v1 engine: fp32 CUDA cores, one token per thread with online softmax over the
 // 256 landmarks; conv from a shared-memory halo tile; coalesced head-merged store.
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace tmil {
 
 constexpr int NO_TOK = 256;                 // tokens per CTA
 constexpr int NO_HALO = TM_CONV_TAPS / 2;   // 16
 
+template <bool ROUND>
 __global__ void __launch_bounds__(256, 1) nystrom_out_kernel(const float* __restrict__ q, const float* __restrict__ k_lm,
                                                              const float* __restrict__ M, const float* __restrict__ v,
                                                              const float* __restrict__ conv_w, int Sp,
@@ -108,6 +110,7 @@ __global__ void __launch_bounds__(256, 1) nystrom_out_kernel(const float* __rest
       const float4 x = vr[tau * 16];
       acc.x = fmaf(w, x.x, acc.x); acc.y = fmaf(w, x.y, acc.y); acc.z = fmaf(w, x.z, acc.z); acc.w = fmaf(w, x.w, acc.w);
     }
+    if (ROUND) { acc.x = round_tf32(acc.x); acc.y = round_tf32(acc.y); acc.z = round_tf32(acc.z); acc.w = round_tf32(acc.w); }
     *reinterpret_cast<float4*>(outb + (long long)tt * TM_DIM) = acc;
   }
 }
@@ -117,17 +120,20 @@ __global__ void __launch_bounds__(256, 1) nystrom_out_kernel(const float* __rest
 extern "C" int tm_nystrom_out_fwd(const float* q, const float* k_lm, const float* M, const float* v, const float* conv_w,
                                   int64_t B, int64_t Sp, float* merged, uint32_t flags, void* stream) {
   using namespace tmil;
-  (void)flags;
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE, "tm_nystrom_out_fwd: Sp must be a multiple of 256 (Sp=%lld)", (long long)Sp);
   TM_CHECK_ARG(q && k_lm && M && v && conv_w && merged, TM_ERR_BAD_ARGUMENT, "tm_nystrom_out_fwd: NULL pointer");
   const size_t smem = (size_t)(2 * TM_LANDMARKS * TM_DHEAD + (NO_TOK + 2 * NO_HALO) * TM_DHEAD) * sizeof(float);
   static bool attr_done = false;
   if (!attr_done) {
-    TM_CUDA(cudaFuncSetAttribute(nystrom_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TM_CUDA(cudaFuncSetAttribute(nystrom_out_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TM_CUDA(cudaFuncSetAttribute(nystrom_out_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done = true;
   }
   dim3 grid((unsigned)(Sp / NO_TOK), (unsigned)(B * TM_HEADS));
-  nystrom_out_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(q, k_lm, M, v, conv_w, (int)Sp, merged);
+  if (flags & TM_FLAG_TF32_OPERANDS)
+    nystrom_out_kernel<true><<<grid, 256, smem, (cudaStream_t)stream>>>(q, k_lm, M, v, conv_w, (int)Sp, merged);
+  else
+    nystrom_out_kernel<false><<<grid, 256, smem, (cudaStream_t)stream>>>(q, k_lm, M, v, conv_w, (int)Sp, merged);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
