@@ -203,6 +203,20 @@ int tm_nystrom_out_fwd(const float* q, const float* k_lm, const float* M, const 
                        const float* conv_w, int64_t B, int64_t Sp, float* merged,
                        uint32_t flags, void* stream);
 
+/* ---- fp16 tensor-core engine of the attention core (tcgen05 / TMEM / TMA) ----------
+ * q16,k16,v16 [B,8,Sp,64], qlm16,klm16 [B,8,256,64], mt16 [B,8,64,256] are IEEE fp16 (device); all
+ * contractions accumulate in fp32.  tm_transmil_fwd routes through these unless TM_FLAG_SIMT_ONLY. */
+/* mt16[b,h,d,j] = half(M[b,h,j,d])  (K-major B operand of attn1 @ M). */
+int tm_mt16_fwd(const float* M, void* mt16, int64_t B, void* stream);
+/* K9+K10+K11, same contract as tm_nystrom_out_fwd (nystrom-attention 0.0.11 forward: attn1, (attn1 @ Z) @ W3, res_conv). */
+int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const void* mt16, const void* v16,
+                          const float* conv_w, int64_t B, int64_t Sp, float* merged, uint32_t flags,
+                          void* stream);
+/* K8, same contract as tm_attn3v_fwd (attn3 @ v, flash style with lazy rescaling). */
+int64_t tm_attn3v_tc_scratch_floats(int64_t B, int64_t Sp);
+int tm_attn3v_tc_fwd(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp,
+                     float* W3, float* scratch, uint32_t flags, void* stream);
+
 /* K12: to_out Linear(512,512)+bias on rows [P,Sp) of merged (the `[:, -S:]` slice),
  * plus the TransLayer residual (TransMIL.py:53).  h_out may alias h_in. */
 int tm_to_out_residual_fwd(const float* merged, const float* out_w, const float* out_b,

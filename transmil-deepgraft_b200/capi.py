@@ -70,6 +70,10 @@ SIGNATURES = {
     "tm_attn3v_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
     "tm_zw_fwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp]),
     "tm_nystrom_out_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
+    "tm_mt16_fwd": (C.c_int, [_fp, _fp, _i64, _fp]),
+    "tm_nystrom_out_tc_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
+    "tm_attn3v_tc_scratch_floats": (_i64, [_i64, _i64]),
+    "tm_attn3v_tc_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
     "tm_to_out_residual_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _i64, _i64, _i64, _fp, _u32, _fp]),
     "tm_ppeg_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _fp]),
     "tm_head_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp]),

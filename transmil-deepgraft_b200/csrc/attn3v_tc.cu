@@ -1,0 +1,262 @@
+// K8 on the 5th-gen tensor cores (fp16 operands, fp32 accumulate), flash style:
+//   W3 = softmax_t(q_lm k^T) v   over ALL Sp padded tokens (zero-score front-pad rows included, like the reference)
+// The [256, Sp] score/probability matrix never reaches HBM.  One CTA owns one (bag, head) and a contiguous chunk of
+// 128-token tiles; it keeps the 256 landmark queries in smem and streams K/V tiles through a 4-stage TMA ring.  Per tile
+// and per landmark half (rows 0-127 / 128-255):
+//   MMA  S[128 lm,128 tok] = Q_lm[128,64] . K_tile[128,64]^T      smem x smem -> TMEM
+//   online softmax along the token axis out of TMEM (one thread per landmark row): running max with LAZY rescaling
+//   (the accumulator is only rescaled when the max grows by more than TAU; P <= e^TAU stays well inside fp16), P written
+//   back in place as packed fp16
+//   MMA  O[128,64] += P[128,128] . V_tile[128,64]                  TMEM x smem (V is the MN-major B operand) -> TMEM
+// The chunk emits (max, sum, numerator) partials; attn3v_combine_kernel (attn3v.cu) merges them in a fixed order.  The same
+// triple is what token-sharded ranks exchange.
+// Warp roles: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 softmax of landmark half a, warps 6-9 of half b.
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace tmil {
+
+int attn_chunks(int64_t nbh, int64_t tiles_per_bh);   // nystrom_out_tc.cu
+
+constexpr int A3_TOK = 128;
+constexpr int A3_STAGES = 4;
+constexpr int A3_QLM_BYTES = 256 * 128;
+constexpr int A3_K_BYTES = 128 * 128;
+constexpr int A3_STAGE_BYTES = 2 * A3_K_BYTES;   // K tile + V tile
+constexpr int A3_OFF_STAGE = A3_QLM_BYTES;
+constexpr int A3_OFF_BAR = A3_OFF_STAGE + A3_STAGES * A3_STAGE_BYTES;
+constexpr size_t A3_SMEM = 1024 + A3_OFF_BAR + 256;
+constexpr int A3_THREADS = 320;
+constexpr float A3_LOG2E = 1.4426950408889634f;
+constexpr float A3_TAU = 5.0f;   // lazy-rescale threshold (natural-log units): P <= e^5 ~ 148
+
+__device__ __forceinline__ void tmem_st_32x32_u(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+      "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]),
+      "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]),
+      "r"(v[31])
+      : "memory");
+}
+
+__global__ void __launch_bounds__(A3_THREADS, 1)
+attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV, int tiles_per_chunk, int tiles_per_bh, int nchunks,
+                 float* __restrict__ pm, float* __restrict__ ps, float* __restrict__ pO) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sQ = smem;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A3_OFF_BAR);
+  uint64_t* kv_full = bars;                    // [4] TMA -> MMA
+  uint64_t* kv_empty = bars + A3_STAGES;       // [4] MMA -> TMA
+  uint64_t* s_full = bars + 2 * A3_STAGES;     // [2] MMA -> softmax half
+  uint64_t* p_full = s_full + 2;               // [2] softmax half -> MMA, 4 arrivals
+  uint64_t* o_full = p_full + 2;               // [2] last PV of the half retired
+  uint64_t* c_full = o_full + 2;               // landmark queries landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bh = blockIdx.y, chunk = blockIdx.x;
+  const int tile0 = chunk * tiles_per_chunk;
+  const int ntile = min(tiles_per_chunk, tiles_per_bh - tile0);
+
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmQlm); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < A3_STAGES; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); }
+    mbar_init(c_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(c_full, A3_QLM_BYTES);
+      tma_load_3d(sQ, &tmQlm, c_full, 0, 0, bh);
+      for (int j = 0; j < ntile; ++j) {
+        const int st = j % A3_STAGES;
+        const uint32_t par = (j / A3_STAGES) & 1;
+        mbar_wait(&kv_empty[st], par ^ 1);
+        uint8_t* sK = smem + A3_OFF_STAGE + st * A3_STAGE_BYTES;
+        mbar_arrive_expect_tx(&kv_full[st], A3_STAGE_BYTES);
+        tma_load_3d(sK, &tmK, &kv_full[st], 0, (tile0 + j) * A3_TOK, bh);
+        tma_load_3d(sK + A3_K_BYTES, &tmV, &kv_full[st], 0, (tile0 + j) * A3_TOK, bh);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && ntile > 0) {
+      constexpr uint32_t idesc_s = umma_idesc_f16(128, 128);
+      constexpr uint32_t idesc_o = umma_idesc_f16(128, 64, 0, 1);   // B = V tile, MN-major (d contiguous)
+      mbar_wait(c_full, 0);
+      auto issue_s = [&](int j, int hf) {
+        const int st = j % A3_STAGES;
+        const uint64_t dQ = umma_desc_k_sw128(smem_u32(sQ + hf * (128 * 128)));
+        const uint64_t dK = umma_desc_k_sw128(smem_u32(smem + A3_OFF_STAGE + st * A3_STAGE_BYTES));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_base + hf * 128, dQ + 2 * k, dK + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(&s_full[hf]);
+      };
+      mbar_wait(&kv_full[0], 0);
+      tc_fence_after();
+      issue_s(0, 0);
+      issue_s(0, 1);
+      for (int j = 0; j < ntile; ++j) {
+        const int st = j % A3_STAGES;
+        const uint32_t sV = smem_u32(smem + A3_OFF_STAGE + st * A3_STAGE_BYTES + A3_K_BYTES);
+        for (int hf = 0; hf < 2; ++hf) {
+          mbar_wait(&p_full[hf], j & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t dV = umma_desc_mn_sw128(sV + ks * 2048, A3_K_BYTES, 1024);
+            umma_f16_ts(tmem_base + 256 + hf * 64, tmem_base + hf * 128 + 8 * ks, dV, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
+          }
+          if (hf == 1) umma_commit(&kv_empty[st]);   // K_j and V_j have no reader left
+          if (j + 1 < ntile) {
+            if (hf == 0) {
+              mbar_wait(&kv_full[(j + 1) % A3_STAGES], ((j + 1) / A3_STAGES) & 1);
+              tc_fence_after();
+            }
+            issue_s(j + 1, hf);
+          } else {
+            umma_commit(&o_full[hf]);
+          }
+        }
+      }
+    }
+  } else {
+    const int hf = (warp - 2) >> 2;     // landmark half
+    const int qd = warp & 3;            // TMEM lane quarter
+    const uint32_t lane_base = (uint32_t)(qd * 32) << 16;
+    const uint32_t tS = tmem_base + lane_base + hf * 128;
+    const uint32_t tO = tmem_base + lane_base + 256 + hf * 64;
+    float m_used = -INFINITY, sum = 0.f;
+    for (int j = 0; j < ntile; ++j) {
+      mbar_wait(&s_full[hf], j & 1);
+      tc_fence_after();
+      float tmax = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; c += 2) {
+        uint32_t r0[32], r1[32];
+        tmem_ld_32x32_nowait(tS + c * 32, r0);
+        tmem_ld_32x32_nowait(tS + c * 32 + 32, r1);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 32; ++e) tmax = fmaxf(tmax, fmaxf(__uint_as_float(r0[e]), __uint_as_float(r1[e])));
+      }
+      if (j == 0) {
+        m_used = tmax;
+      } else {
+        const bool need = tmax > m_used + A3_TAU;
+        if (__any_sync(0xffffffffu, need)) {
+          // the accumulator is quiescent here: s_full(j) was committed after PV(j-1)
+          const float f = need ? ex2_approx((m_used - tmax) * A3_LOG2E) : 1.0f;
+          if (need) { m_used = tmax; sum *= f; }
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t o[32];
+            tmem_ld_32x32_nowait(tO + c * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * f);
+            tmem_st_32x32_u(tO + c * 32, o);
+          }
+        }
+      }
+      const float ml = m_used * A3_LOG2E;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32], pk[16];
+        tmem_ld_32x32_nowait(tS + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * e]), A3_LOG2E, -ml));
+          const float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * e + 1]), A3_LOG2E, -ml));
+          sum += p0 + p1;
+          pk[e] = pack_f16x2(p0, p1);
+        }
+        tmem_st_32x16(tS + c * 16, pk);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[hf]);
+    }
+    if (ntile > 0) {
+      mbar_wait(&o_full[hf], 0);
+      tc_fence_after();
+      const int row = hf * 128 + qd * 32 + lane;
+      const long long pi = ((long long)bh * nchunks + chunk) * TM_LANDMARKS + row;
+      pm[pi] = m_used;
+      ps[pi] = sum;
+      float4* od = reinterpret_cast<float4*>(pO + pi * TM_DHEAD);
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32_nowait(tO + c * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 32; e += 4)
+          od[c * 8 + (e >> 2)] = make_float4(__uint_as_float(o[e]), __uint_as_float(o[e + 1]), __uint_as_float(o[e + 2]), __uint_as_float(o[e + 3]));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+__global__ void attn3v_combine_kernel(const float* __restrict__ pm, const float* __restrict__ ps, const float* __restrict__ pO,
+                                      int nchunks, float* __restrict__ W3);   // attn3v.cu
+
+}  // namespace tmil
+
+extern "C" int64_t tm_attn3v_tc_scratch_floats(int64_t B, int64_t Sp) {
+  const int64_t nbh = B * TM_HEADS;
+  return nbh * tmil::attn_chunks(nbh, Sp / tmil::A3_TOK) * TM_LANDMARKS * (TM_DHEAD + 2);
+}
+
+extern "C" int tm_attn3v_tc_fwd(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3,
+                                float* scratch, uint32_t flags, void* stream) {
+  using namespace tmil;
+  (void)flags;
+  TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE, "tm_attn3v_tc_fwd: Sp must be a multiple of 256 (Sp=%lld)", (long long)Sp);
+  TM_CHECK_ARG(qlm16 && k16 && v16 && W3 && scratch, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_fwd: NULL pointer");
+  TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "tm_attn3v_tc_fwd needs an sm_100 device");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t nbh = B * TM_HEADS;
+  CUtensorMap tmQ, tmK, tmV;
+  TM_PROPAGATE(make_tmap_3d_f16(&tmQ, qlm16, nbh, TM_LANDMARKS, TM_DHEAD, TM_LANDMARKS * TM_DHEAD, TM_DHEAD, TM_LANDMARKS, TM_DHEAD));
+  TM_PROPAGATE(make_tmap_3d_f16(&tmK, k16, nbh, Sp, TM_DHEAD, Sp * TM_DHEAD, TM_DHEAD, A3_TOK, TM_DHEAD));
+  TM_PROPAGATE(make_tmap_3d_f16(&tmV, v16, nbh, Sp, TM_DHEAD, Sp * TM_DHEAD, TM_DHEAD, A3_TOK, TM_DHEAD));
+  static bool attr_done = false;
+  if (!attr_done) {
+    TM_CUDA(cudaFuncSetAttribute(attn3v_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A3_SMEM));
+    attr_done = true;
+  }
+  const int tiles_per_bh = (int)(Sp / A3_TOK);
+  const int chunks = attn_chunks(nbh, tiles_per_bh);
+  const int tpc = (int)ceil_div(tiles_per_bh, chunks);
+  const int used = (int)ceil_div(tiles_per_bh, tpc);
+  float* pm = scratch;
+  float* ps = pm + nbh * used * TM_LANDMARKS;
+  float* pO = ps + nbh * used * TM_LANDMARKS;
+  attn3v_tc_kernel<<<dim3((unsigned)used, (unsigned)nbh), A3_THREADS, A3_SMEM, st>>>(tmQ, tmK, tmV, tpc, tiles_per_bh, used, pm, ps, pO);
+  TM_LAUNCH_CHECK();
+  attn3v_combine_kernel<<<dim3(16, (unsigned)nbh), 256, 0, st>>>(pm, ps, pO, used, W3);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}

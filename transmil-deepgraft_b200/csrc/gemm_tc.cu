@@ -69,6 +69,23 @@ int make_tmap_3d(CUtensorMap* out, const float* base, uint64_t batch, uint64_t r
   return TM_OK;
 }
 
+int make_tmap_3d_f16(CUtensorMap* out, const void* base, uint64_t batch, uint64_t rows, uint64_t cols, uint64_t batch_stride, uint64_t ld,
+                     uint32_t box_rows, uint32_t box_cols) {
+  TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "TMA tensor maps need an sm_100 device and driver");
+  TM_CHECK_ARG(aligned16(base) && (ld * 2) % 16 == 0 && (batch_stride * 2) % 16 == 0 && box_cols * 2 == 128 && box_rows <= 256,
+               TM_ERR_BAD_ALIGNMENT, "fp16 TMA operand: 16-byte aligned, 16-byte pitches, 128-byte box rows, <= 256 box rows");
+  cuuint64_t dims[3] = {cols, rows, batch};
+  cuuint64_t strides[2] = {ld * 2, batch_stride * 2};
+  cuuint32_t box[3] = {box_cols, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TM_CHECK_ARG(r == CUDA_SUCCESS, TM_ERR_CUDA, "cuTensorMapEncodeTiled(3d f16) failed with %d (batch=%llu rows=%llu cols=%llu)", (int)r,
+               (unsigned long long)batch, (unsigned long long)rows, (unsigned long long)cols);
+  return TM_OK;
+}
+
 // ---- kernel ------------------------------------------------------------------------------------------------
 constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32, TC_STAGES = 4;
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;   // 16 KB
