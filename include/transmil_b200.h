@@ -159,6 +159,8 @@ int tm_transmil_fwd_host(const tm_weights* w, const float* x_host, int64_t B, in
  * (stages of the LAST layer executed unless suffixed "1", e.g. "Z1", "q_lm1"). */
 int tm_stage_ptr(const char* name, int64_t B, int64_t n, const tm_weights* w, uint32_t flags,
                  void* workspace, void** ptr, int64_t* numel);
+/* 1 when that stage buffer holds fp16 elements under `flags` on this device ("q","k","v" of the tensor-core engine). */
+int tm_stage_is_f16(const char* name, uint32_t flags);
 
 /* ---- per-kernel entry points (all device pointers) -------------------- */
 /* K1+K2: _fc1 (TransMIL.py:175) fused with the duplicate pad (:177-180) and the
@@ -206,6 +208,12 @@ int tm_nystrom_out_fwd(const float* q, const float* k_lm, const float* M, const 
 /* ---- fp16 tensor-core engine of the attention core (tcgen05 / TMEM / TMA) ----------
  * q16,k16,v16 [B,8,Sp,64], qlm16,klm16 [B,8,256,64], mt16 [B,8,64,256] are IEEE fp16 (device); all
  * contractions accumulate in fp32.  tm_transmil_fwd routes through these unless TM_FLAG_SIMT_ONLY. */
+/* K4 with fp16 head-major outputs (saturating round-to-nearest): xn [B,Sp,512] fp32 -> q16 (x 64^-0.5), k16, v16. */
+int tm_qkv16_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16,
+                 void* v16, uint32_t flags, void* stream);
+/* K5 on fp16 q/k: fp32 landmark means (fp32 accumulation) plus their fp16 copies. */
+int tm_landmarks16_fwd(const void* q16, const void* k16, int64_t B, int64_t Sp, int64_t l, float* q_lm,
+                       float* k_lm, void* qlm16, void* klm16, void* stream);
 /* mt16[b,h,d,j] = half(M[b,h,j,d])  (K-major B operand of attn1 @ M). */
 int tm_mt16_fwd(const float* M, void* mt16, int64_t B, void* stream);
 /* K9+K10+K11, same contract as tm_nystrom_out_fwd (nystrom-attention 0.0.11 forward: attn1, (attn1 @ Z) @ W3, res_conv). */

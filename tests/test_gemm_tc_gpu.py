@@ -30,7 +30,7 @@ def test_gemm_tc_matches_fp32(built_lib, M, N, K):
     assert torch.isfinite(C_tc).all()
     e_simt = (C_simt.double() - ref).abs().max().item() / scale
     e_tc = (C_tc.double() - ref).abs().max().item() / scale
-    assert e_simt < 2e-6, e_simt
+    assert e_simt < 1e-5, e_simt
     assert e_tc < 1e-5, f"tcgen05 GEMM error {e_tc:.3e} (operands are tf32-exact, accumulation is fp32)"
 
 

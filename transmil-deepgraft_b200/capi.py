@@ -70,6 +70,9 @@ SIGNATURES = {
     "tm_attn3v_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
     "tm_zw_fwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp]),
     "tm_nystrom_out_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
+    "tm_qkv16_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _u32, _fp]),
+    "tm_landmarks16_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _fp, _fp, _fp, _fp, _fp]),
+    "tm_stage_is_f16": (C.c_int, [C.c_char_p, _u32]),
     "tm_mt16_fwd": (C.c_int, [_fp, _fp, _i64, _fp]),
     "tm_nystrom_out_tc_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
     "tm_attn3v_tc_scratch_floats": (_i64, [_i64, _i64]),

@@ -74,6 +74,7 @@ enum GemmEpi : int {
   EPI_BIAS_GELU = 1,  // C[map(r)] = gelu(acc + bias[c]) (+ duplicate-pad rows)   fc1
   EPI_QKV = 2,        // head-major q(*0.125),k,v split
   EPI_BIAS_RESID = 3, // C = acc + bias[c] + R[r,c]            to_out + residual
+  EPI_QKV16 = 4,      // head-major q(*0.125),k,v split stored as fp16 (p.q/k/v point at __half arrays)
 };
 
 struct GemmParams {

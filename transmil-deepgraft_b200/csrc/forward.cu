@@ -5,6 +5,8 @@
 #include "common.cuh"
 
 extern "C" int64_t tm_pinv_scratch_floats(int64_t B);
+extern "C" int tm_qkv16_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
+                            uint32_t flags, void* stream);
 
 namespace tmil {
 
@@ -36,6 +38,7 @@ struct Layout {
   size_t total;  // floats
   size_t h[4], fc1s, xn, merged, q, k, v, small[2][6], pinv_s, a3_s, packed;
   size_t wr_fc1_0, wr_fc1_1, wr_qkv[2], wr_out[2];   // tf32-rounded copies of the GEMM weights
+  size_t qlm16, klm16, mt16;                         // fp16 operands of the tensor-core attention kernels
 };
 enum { SM_QLM = 0, SM_KLM, SM_ATTN2, SM_Z, SM_W3, SM_M };
 
@@ -71,7 +74,13 @@ static int make_layout(int64_t B, const tm_plan& p, const tm_weights* w, uint32_
     L->small[l][SM_M] = bump(cur, lm);
   }
   L->pinv_s = bump(cur, (size_t)tm_pinv_scratch_floats(B));
-  L->a3_s = bump(cur, (size_t)tm_attn3v_scratch_floats(B, p.Sp));
+  {
+    const size_t a = (size_t)tm_attn3v_scratch_floats(B, p.Sp), t = (size_t)tm_attn3v_tc_scratch_floats(B, p.Sp);
+    L->a3_s = bump(cur, a > t ? a : t);
+  }
+  L->qlm16 = bump(cur, lm / 2);
+  L->klm16 = bump(cur, lm / 2);
+  L->mt16 = bump(cur, lm / 2);
   L->packed = bump(cur, 50 * TM_DIM);
   L->wr_fc1_0 = bump(cur, (size_t)(f0 ? f0 : TM_DIM) * w->in_features);
   L->wr_fc1_1 = bump(cur, (size_t)TM_DIM * f0);
@@ -104,6 +113,24 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
   float* merged = ws + L.merged;
   prof_mark(ST_LN_PAD, st);
   TM_PROPAGATE(tm_ln_pad_fwd(h_in, lw.norm_w, lw.norm_b, B, p.S, p.P, xn, flags, st));
+  if (use_tc(flags)) {
+    // tensor-core engine: q, k, v live as fp16 (head-major) in the q/k/v regions; all contractions accumulate in fp32
+    void* q16 = q; void* k16 = k; void* v16 = v;
+    void* qlm16 = ws + L.qlm16; void* klm16 = ws + L.klm16; void* mt16 = ws + L.mt16;
+    prof_mark(ST_QKV, st);
+    TM_PROPAGATE(tm_qkv16_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, flags, st));
+    prof_mark(ST_LANDMARKS, st);
+    TM_PROPAGATE(tm_landmarks16_fwd(q16, k16, B, p.Sp, p.l, q_lm, k_lm, qlm16, klm16, st));
+    prof_mark(ST_PINV, st);
+    TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, st));
+    prof_mark(ST_ATTN3V, st);
+    TM_PROPAGATE(tm_attn3v_tc_fwd(qlm16, k16, v16, B, p.Sp, W3, ws + L.a3_s, flags, st));
+    prof_mark(ST_ZW, st);
+    TM_PROPAGATE(tm_zw_fwd(Z, W3, B, M, st));
+    TM_PROPAGATE(tm_mt16_fwd(M, mt16, B, st));
+    prof_mark(ST_NYSTROM_OUT, st);
+    TM_PROPAGATE(tm_nystrom_out_tc_fwd(q16, klm16, mt16, v16, lw.conv_w, B, p.Sp, merged, flags, st));
+  } else {
   prof_mark(ST_QKV, st);
   TM_PROPAGATE(tm_qkv_fwd(xn, lw.qkv_w, B, p.Sp, q, k, v, flags, st));
   prof_mark(ST_LANDMARKS, st);
@@ -116,6 +143,7 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
   TM_PROPAGATE(tm_zw_fwd(Z, W3, B, M, st));
   prof_mark(ST_NYSTROM_OUT, st);
   TM_PROPAGATE(tm_nystrom_out_fwd(q, k_lm, M, v, lw.conv_w, B, p.Sp, merged, flags, st));
+  }
   prof_mark(ST_TO_OUT, st);
   TM_PROPAGATE(tm_to_out_residual_fwd(merged, lw.out_w, lw.out_b, h_in, B, p.S, p.P, h_out, flags, st));
   return TM_OK;
@@ -172,6 +200,18 @@ extern "C" int tm_qkv_fwd(const float* xn, const float* qkv_w, int64_t B, int64_
   g.M = (int)(B * Sp); g.N = 3 * TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = 3 * TM_DIM;
   g.batch = 1; g.epi = EPI_QKV; g.q = q; g.k = k; g.v = v; g.Sp = (int)Sp;
   g.round_out = (flags & TM_FLAG_TF32_OPERANDS) ? 1 : 0;
+  return gemm_auto(g, flags, (cudaStream_t)stream);
+}
+
+extern "C" int tm_qkv16_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
+                            uint32_t flags, void* stream) {
+  TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0 && B * Sp < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_qkv16_fwd: bad shape B=%lld Sp=%lld", (long long)B, (long long)Sp);
+  TM_CHECK_ARG(xn && qkv_w && q16 && k16 && v16, TM_ERR_BAD_ARGUMENT, "tm_qkv16_fwd: NULL pointer");
+  GemmParams g;
+  memset(&g, 0, sizeof(g));
+  g.A = xn; g.Bm = qkv_w; g.C = nullptr;
+  g.M = (int)(B * Sp); g.N = 3 * TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = 3 * TM_DIM;
+  g.batch = 1; g.epi = EPI_QKV16; g.q = (float*)q16; g.k = (float*)k16; g.v = (float*)v16; g.Sp = (int)Sp;
   return gemm_auto(g, flags, (cudaStream_t)stream);
 }
 
@@ -283,4 +323,10 @@ extern "C" int tm_stage_ptr(const char* name, int64_t B, int64_t n, const tm_wei
     }
   set_error("tm_stage_ptr: unknown stage '%s'", name);
   return TM_ERR_BAD_ARGUMENT;
+}
+
+// 1 when the named stage buffer holds fp16 under `flags` on this device (q, k, v of the tensor-core engine).
+extern "C" int tm_stage_is_f16(const char* name, uint32_t flags) {
+  if (!name || !use_tc(flags)) return 0;
+  return (strcmp(name, "q") == 0 || strcmp(name, "k") == 0 || strcmp(name, "v") == 0) ? 1 : 0;
 }

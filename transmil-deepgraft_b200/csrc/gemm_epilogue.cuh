@@ -3,6 +3,8 @@
 // columns of one logical row.
 #pragma once
 #include "common.cuh"
+#include <cuda_fp16.h>
+
 #include "tc_common.cuh"
 
 namespace tmil {
@@ -50,6 +52,19 @@ __device__ __forceinline__ void epilogue_store4(const GemmParams& p, int r, int 
       float4 o = make_float4(acc.x * s, acc.y * s, acc.z * s, acc.w * s);
       if (p.round_out) { o.x = round_tf32(o.x); o.y = round_tf32(o.y); o.z = round_tf32(o.z); o.w = round_tf32(o.w); }
       *reinterpret_cast<float4*>(base + (((long long)bag * TM_HEADS + hh) * p.Sp + t) * TM_DHEAD + d) = o;
+      break;
+    }
+    case EPI_QKV16: {
+      const int which = c / TM_DIM;
+      const int cc = c - which * TM_DIM;
+      const int hh = cc / TM_DHEAD, d = cc % TM_DHEAD;
+      const int bag = r / p.Sp, t = r - bag * p.Sp;
+      __half* base = reinterpret_cast<__half*>(which == 0 ? p.q : (which == 1 ? p.k : p.v));
+      const float s = which == 0 ? 0.125f : 1.0f;  // q * dim_head^-0.5 (exact in fp16: power of two)
+      uint2 o;
+      o.x = pack_f16x2(acc.x * s, acc.y * s);
+      o.y = pack_f16x2(acc.z * s, acc.w * s);
+      *reinterpret_cast<uint2*>(base + (((long long)bag * TM_HEADS + hh) * p.Sp + t) * TM_DHEAD + d) = o;
       break;
     }
     case EPI_BIAS_RESID: {

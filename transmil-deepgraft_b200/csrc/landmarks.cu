@@ -1,7 +1,10 @@
 // K5: landmark means.  q_lm[b,h,g,:] = (sum_{j<l} q[b,h,g*l+j,:]) / l over the PADDED
 // token axis (nystrom-attention 0.0.11: reduce('... (n l) d -> ... n d', 'sum') / l).
 // HBM-bound: q and k are each read exactly once, 16 lanes x float4 per 64-wide row.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace tmil {
 
@@ -36,6 +39,48 @@ __global__ void __launch_bounds__(256) landmarks_kernel(const float* __restrict_
   reinterpret_cast<float4*>((is_k ? k_lm : q_lm) + g * TM_DHEAD)[lane16] = acc;
 }
 
+// fp16 q/k (tensor-core engine): same means accumulated in fp32; emits the fp32 landmarks (sim2 / pinv run in fp32)
+// and fp16 copies (operands of the tensor-core contractions).  8 lanes x 16 bytes per 64-wide fp16 row.
+__global__ void __launch_bounds__(256) landmarks16_kernel(const __half* __restrict__ q, const __half* __restrict__ k,
+                                                          long long groups_per_tensor, int l, float* __restrict__ q_lm,
+                                                          float* __restrict__ k_lm, __half* __restrict__ qlm16,
+                                                          __half* __restrict__ klm16) {
+  const long long gid = (long long)blockIdx.x * 32 + (threadIdx.x >> 3);
+  if (gid >= 2 * groups_per_tensor) return;
+  const int lane8 = threadIdx.x & 7;
+  const bool is_k = gid >= groups_per_tensor;
+  const long long g = is_k ? gid - groups_per_tensor : gid;
+  const uint4* src = reinterpret_cast<const uint4*>((is_k ? k : q) + g * (long long)l * TM_DHEAD) + lane8;
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  auto add = [&](uint4 u) {
+    const __half2* h2 = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __half22float2(h2[e]);
+      acc[2 * e] += f.x; acc[2 * e + 1] += f.y;
+    }
+  };
+  int j = 0;
+  for (; j + 4 <= l; j += 4) {
+    const uint4 a = __ldg(src + (long long)(j + 0) * 8), b = __ldg(src + (long long)(j + 1) * 8);
+    const uint4 c = __ldg(src + (long long)(j + 2) * 8), d = __ldg(src + (long long)(j + 3) * 8);
+    add(a); add(b); add(c); add(d);
+  }
+  for (; j < l; ++j) add(__ldg(src + (long long)j * 8));
+  const float fl = (float)l;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] /= fl;
+  float4* dst = reinterpret_cast<float4*>((is_k ? k_lm : q_lm) + g * TM_DHEAD) + lane8 * 2;
+  dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  uint4 o;
+  o.x = pack_f16x2(acc[0], acc[1]); o.y = pack_f16x2(acc[2], acc[3]);
+  o.z = pack_f16x2(acc[4], acc[5]); o.w = pack_f16x2(acc[6], acc[7]);
+  reinterpret_cast<uint4*>((is_k ? klm16 : qlm16) + g * TM_DHEAD)[lane8] = o;
+}
+
 }  // namespace tmil
 
 extern "C" int tm_landmarks_fwd(const float* q, const float* k, int64_t B, int64_t Sp, int64_t l, float* q_lm,
@@ -46,6 +91,20 @@ extern "C" int tm_landmarks_fwd(const float* q, const float* k, int64_t B, int64
                "tm_landmarks_fwd: pointers must be 16-byte aligned");
   const long long groups = (long long)B * TM_HEADS * TM_LANDMARKS;
   tmil::landmarks_kernel<<<(unsigned)tmil::ceil_div(2 * groups, 16), 256, 0, (cudaStream_t)stream>>>(q, k, groups, (int)l, q_lm, k_lm);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+extern "C" int tm_landmarks16_fwd(const void* q16, const void* k16, int64_t B, int64_t Sp, int64_t l, float* q_lm, float* k_lm,
+                                  void* qlm16, void* klm16, void* stream) {
+  TM_CHECK_ARG(B > 0 && l > 0 && Sp == l * TM_LANDMARKS, TM_ERR_BAD_SHAPE,
+               "tm_landmarks16_fwd: Sp must equal 256*l (Sp=%lld l=%lld)", (long long)Sp, (long long)l);
+  TM_CHECK_ARG(tmil::aligned16(q16) && tmil::aligned16(k16) && tmil::aligned16(q_lm) && tmil::aligned16(k_lm) &&
+                   tmil::aligned16(qlm16) && tmil::aligned16(klm16), TM_ERR_BAD_ALIGNMENT,
+               "tm_landmarks16_fwd: pointers must be 16-byte aligned");
+  const long long groups = (long long)B * TM_HEADS * TM_LANDMARKS;
+  tmil::landmarks16_kernel<<<(unsigned)tmil::ceil_div(2 * groups, 32), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)q16, (const __half*)k16, groups, (int)l, q_lm, k_lm, (__half*)qlm16, (__half*)klm16);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -228,6 +228,8 @@ def _stage_tensor(model, ws, w, name, B, n, flags):
     off = ptr.value - ws.data_ptr()
     plan = capi.make_plan(n)
     shape = _STAGE_SHAPES[_STAGE_KIND[name]](B, plan)
+    if capi.lib().tm_stage_is_f16(name.encode(), flags):   # q, k, v of the tensor-core engine: returned as an fp32 copy
+        return ws[off:off + 2 * numel.value].view(torch.float16).view(shape).float()
     return ws[off:off + 4 * numel.value].view(torch.float32).view(shape)
 
 
