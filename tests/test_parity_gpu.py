@@ -193,7 +193,7 @@ def test_full_size_properties(T, n, D):
     assert float(q[:, :, :p["P"]].abs().max()) == 0.0
     ref_lm = q.double().reshape(1, 8, 256, p["l"], 64).mean(3)
     _close(q_lm, ref_lm, 1e-5)
-    _close(attn2.sum(-1), torch.ones(1, 8, 256), 1e-5)
+    _close(attn2.sum(-1), torch.ones(1, 8, 256), 2e-4)   # attn2 is stored tf32-rounded (operand of the tensor-core pinv chain)
     A = attn2.double()
     res = ((A @ Z.double() @ A - A).norm() / A.norm()).item()
     assert 1e-6 < res < 0.2

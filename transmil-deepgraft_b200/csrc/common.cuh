@@ -74,6 +74,8 @@ enum GemmEpi : int {
   EPI_BIAS_GELU = 1,  // C[map(r)] = gelu(acc + bias[c]) (+ duplicate-pad rows)   fc1
   EPI_QKV = 2,        // head-major q(*0.125),k,v split
   EPI_BIAS_RESID = 3, // C = acc + bias[c] + R[r,c]            to_out + residual
+  EPI_AXPBY_T = 5,    // o = alpha*acc + beta*LT[c,r]; stores C[r,c] (if C) and CT[c,r] (if CT): the pinv chain keeps every
+                      // iterate in both orientations so each product is an NT GEMM (B operand = transposed copy)
   EPI_QKV16 = 4,      // head-major q(*0.125),k,v split stored as fp16 (p.q/k/v point at __half arrays)
 };
 
@@ -86,7 +88,8 @@ struct GemmParams {
   long long strideA, strideB, strideC, strideL;
   int epi;
   float alpha, beta;
-  const float* L; int ldl;     // EPI_AXPBY second term / EPI_BIAS_RESID residual
+  const float* L; int ldl;     // EPI_AXPBY second term / EPI_BIAS_RESID residual / EPI_AXPBY_T transposed second term
+  float* CT;                   // EPI_AXPBY_T transposed output (same ldc / strideC as C)
   const float* bias;
   // C row map: logical row r in [0,M): bag = r / rows_per_bag, i = r % rows_per_bag;
   // rows with i < c_skip are not stored; C row = bag*c_bag_rows + c_row_off + (i - c_skip)
@@ -94,6 +97,8 @@ struct GemmParams {
   long long c_bag_rows; int c_row_off; int c_skip;
   int dup;                     // EPI_BIAS_GELU: rows i < dup are also written rows_per_bag rows further down
   int round_out;               // round stored values to tf32 (consumer is a tensor-core contraction)
+  int f16_in;                  // A and Bm point at fp16 operands (tensor-core engine only)
+  int bn128;                   // tensor-core engine: use the 128-wide N tile (small batched problems)
   // EPI_QKV
   float* q; float* k; float* v; int Sp;
 };

@@ -33,6 +33,10 @@ __device__ __forceinline__ void epilogue_store4(const GemmParams& p, int r, int 
       *reinterpret_cast<float4*>(Cb + (long long)r * p.ldc + c) = o;
       break;
     }
+    case EPI_AXPBY_T: {   // the value was finished (scaled, second term, rounding) in the accumulator layout; plain store
+      if (Cb != nullptr) *reinterpret_cast<float4*>(Cb + (long long)r * p.ldc + c) = acc;
+      break;
+    }
     case EPI_BIAS_GELU: {
       float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + c));
       float4 o = make_float4(gelu_erf(acc.x + b.x), gelu_erf(acc.y + b.y), gelu_erf(acc.z + b.z), gelu_erf(acc.w + b.w));

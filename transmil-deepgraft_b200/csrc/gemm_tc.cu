@@ -10,6 +10,8 @@
 #include <mutex>
 
 #include "common.cuh"
+#include <cuda_fp16.h>
+
 #include "gemm_epilogue.cuh"
 #include "tc_common.cuh"
 
@@ -87,27 +89,38 @@ int make_tmap_3d_f16(CUtensorMap* out, const void* base, uint64_t batch, uint64_
 }
 
 // ---- kernel ------------------------------------------------------------------------------------------------
-constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 32, TC_STAGES = 4;
-constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;   // 16 KB
-constexpr int TC_B_BYTES = TC_BN * TC_BK * 4;   // 32 KB
+// Template parameters: BN = N tile (256: big weight GEMMs, 128: the batched 256^3 products of the pinv chain),
+// F16 = operand type (false: tf32 in fp32 storage, BK = 32; true: fp16, BK = 64).  Either way a k-block row is 128 bytes
+// (one SWIZZLE_128B atom row) and holds 4 UMMA K-steps of 32 bytes.
+constexpr int TC_BM = 128;
+constexpr int TC_A_BYTES = TC_BM * 128;         // 16 KB per stage
 constexpr int TC_STG_LD = 36;                   // floats per staged row (32 + 4: conflict-free 128-bit access)
 constexpr int TC_STG_BYTES = 32 * TC_STG_LD * 4;
 constexpr int TC_THREADS = 192;
-constexpr size_t TC_SMEM = 1024 + TC_STAGES * (TC_A_BYTES + TC_B_BYTES) + 4 * TC_STG_BYTES + 256;
 
+template <int BN> struct TcCfg {
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int STAGES = BN == 256 ? 4 : 6;
+  static constexpr size_t SMEM = 1024 + STAGES * (TC_A_BYTES + B_BYTES) + 4 * TC_STG_BYTES + 256;
+};
+
+template <int BN, bool F16>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p, int m_tiles,
-               int n_tiles, int k_blocks) {
+               int n_tiles, int k_blocks, int total) {
+  constexpr int STAGES = TcCfg<BN>::STAGES;
+  constexpr int B_BYTES = TcCfg<BN>::B_BYTES;
+  constexpr int BK = F16 ? 64 : 32;             // elements per k-block
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
-  uint8_t* sB = sA + TC_STAGES * TC_A_BYTES;
-  float* stg = reinterpret_cast<float*>(sB + TC_STAGES * TC_B_BYTES);
+  uint8_t* sB = sA + STAGES * TC_A_BYTES;
+  float* stg = reinterpret_cast<float*>(sB + STAGES * B_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stg) + 4 * TC_STG_BYTES);
-  uint64_t* full = bars;                 // [TC_STAGES]  TMA -> MMA
-  uint64_t* empty = bars + TC_STAGES;    // [TC_STAGES]  MMA -> TMA
-  uint64_t* tfull = bars + 2 * TC_STAGES;   // [2]       MMA -> epilogue
-  uint64_t* tempty = tfull + 2;             // [2]       epilogue -> MMA
+  uint64_t* full = bars;                 // [STAGES]  TMA -> MMA
+  uint64_t* empty = bars + STAGES;       // [STAGES]  MMA -> TMA
+  uint64_t* tfull = bars + 2 * STAGES;   // [2]       MMA -> epilogue
+  uint64_t* tempty = tfull + 2;          // [2]       epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -116,34 +129,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tma_prefetch_desc(&tmB);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < TC_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  if (warp == 2) tmem_alloc(tmem_slot, 2 * BN);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int total = m_tiles * n_tiles;
+  const int tiles_per_z = m_tiles * n_tiles;
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const int m_blk = tile / n_tiles, n_blk = tile - m_blk * n_tiles;
+        const int z = tile / tiles_per_z, rem = tile - z * tiles_per_z;
+        const int m_blk = rem / n_tiles, n_blk = rem - m_blk * n_tiles;
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full[stage], TC_A_BYTES + TC_B_BYTES);
-          tma_load_2d(sA + stage * TC_A_BYTES, &tmA, &full[stage], kb * TC_BK, m_blk * TC_BM);
-          tma_load_2d(sB + stage * TC_B_BYTES, &tmB, &full[stage], kb * TC_BK, n_blk * TC_BN);
-          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+          mbar_arrive_expect_tx(&full[stage], TC_A_BYTES + B_BYTES);
+          tma_load_3d(sA + stage * TC_A_BYTES, &tmA, &full[stage], kb * BK, m_blk * TC_BM, z);
+          tma_load_3d(sB + stage * B_BYTES, &tmB, &full[stage], kb * BK, n_blk * BN, z);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_tf32(TC_BM, TC_BN);
+      constexpr uint32_t idesc = F16 ? umma_idesc_f16(TC_BM, BN) : umma_idesc_tf32(TC_BM, BN);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int tile = blockIdx.x; tile < total; tile += gridDim.x, ++it) {
@@ -151,53 +165,185 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&tempty[as], aphase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * TC_BN;
+        const uint32_t d_tmem = tmem_base + as * BN;
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint64_t a_desc = umma_desc_k_sw128(smem_u32(sA + stage * TC_A_BYTES));
-          const uint64_t b_desc = umma_desc_k_sw128(smem_u32(sB + stage * TC_B_BYTES));
+          const uint64_t b_desc = umma_desc_k_sw128(smem_u32(sB + stage * B_BYTES));
 #pragma unroll
-          for (int k = 0; k < TC_BK / 8; ++k)  // 8 tf32 = 32 bytes per MMA: advance the start address inside the swizzle atom
-            umma_tf32_ss(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < 4; ++k) {  // 32 bytes of K per MMA: advance the start address inside the swizzle atom
+            if (F16) umma_f16_ss(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+            else umma_tf32_ss(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+          }
           umma_commit(&empty[stage]);
-          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         umma_commit(&tfull[as]);
       }
     }
   } else {
+    // ---- epilogue warps: TMEM -> registers -> per-warp smem transpose -> coalesced 128-bit global accesses ----
     const int q = warp & 3;   // TMEM lane quarter this warp may access
     float* my_stg = stg + (warp - 2) * (32 * TC_STG_LD);
-    const float* Lb = (p.L != nullptr && p.epi == EPI_AXPBY) ? p.L : nullptr;
+    const int sub = lane >> 3, cl = (lane & 7) * 4;   // store phase: lane covers rows sub, sub+4, ... and 4 columns at cl
     int it = 0;
     for (int tile = blockIdx.x; tile < total; tile += gridDim.x, ++it) {
-      const int m_blk = tile / n_tiles, n_blk = tile - m_blk * n_tiles;
+      const int z = tile / tiles_per_z, rem = tile - z * tiles_per_z;
+      const int m_blk = rem / n_tiles, n_blk = rem - m_blk * n_tiles;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
+      // row bookkeeping of the store phase, once per tile (the integer divisions stay out of the column loop)
+      long long crow[8];
+      int irow[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = m_blk * TC_BM + q * 32 + i * 4 + sub;
+        irow[i] = 0;
+        if (r >= p.M) { crow[i] = -1; continue; }
+        switch (p.epi) {
+          case EPI_BIAS_GELU:
+          case EPI_BIAS_RESID: crow[i] = map_c_row(p, r, &irow[i]); break;
+          case EPI_QKV:
+          case EPI_QKV16: {
+            const int bag = r / p.Sp;
+            crow[i] = (long long)bag * TM_HEADS * p.Sp + (r - bag * p.Sp);   // row inside head 0 of the bag
+            break;
+          }
+          default: crow[i] = r; break;
+        }
+      }
+      const float* Lz = p.L != nullptr ? p.L + (long long)z * p.strideL : nullptr;
+      float* Cz = p.C != nullptr ? p.C + (long long)z * p.strideC : nullptr;
+      float* CTz = (p.epi == EPI_AXPBY_T && p.CT != nullptr) ? p.CT + (long long)z * p.strideC : nullptr;
       mbar_wait(&tfull[as], aphase);
       tc_fence_after();
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * TC_BN;
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
 #pragma unroll 1
-      for (int chunk = 0; chunk < TC_BN / 32; ++chunk) {
+      for (int chunk = 0; chunk < BN / 32; ++chunk) {
         float v[32];
         tmem_ld_32x32(t_row + chunk * 32, v);
-        if (chunk == TC_BN / 32 - 1) {   // accumulator fully read: hand the TMEM buffer back to the MMA warp
+        if (chunk == BN / 32 - 1) {   // accumulator fully read: hand the TMEM buffer back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[as]);
+        }
+        const int c0 = n_blk * BN + chunk * 32;
+        if (p.epi == EPI_AXPBY_T) {
+          // accumulator layout: this lane owns row r_own, columns c0..c0+31 -> the transposed accesses are coalesced
+          const int r_own = m_blk * TC_BM + q * 32 + lane;
+          const bool ok = r_own < p.M;
+          if (Lz != nullptr) {   // all 32 second-term loads in flight before the first store (CT may alias nothing, but the
+                                 // compiler cannot know): one L2 round trip per chunk instead of 32
+            float lv[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) lv[e] = (ok && (c0 + e) < p.N) ? Lz[(long long)(c0 + e) * p.ldl + r_own] : 0.f;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[e] = fmaf(p.beta, lv[e], p.alpha * v[e]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[e] = p.alpha * v[e];
+          }
+          if (p.round_out) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[e] = round_tf32(v[e]);
+          }
+          if (CTz != nullptr) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (ok && (c0 + e) < p.N) CTz[(long long)(c0 + e) * p.ldc + r_own] = v[e];
+          }
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i)
           *reinterpret_cast<float4*>(my_stg + lane * TC_STG_LD + i * 4) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         __syncwarp();
+        const int c = c0 + cl;
+        if (c < p.N) {
+          float4 acc[8];
 #pragma unroll
-        for (int rr = 0; rr < 32; rr += 4) {
-          const int rl = rr + (lane >> 3), cl = (lane & 7) * 4;
-          const float4 acc = *reinterpret_cast<const float4*>(my_stg + rl * TC_STG_LD + cl);
-          const int r = m_blk * TC_BM + q * 32 + rl;
-          const int c = n_blk * TC_BN + chunk * 32 + cl;
-          if (r < p.M && c < p.N) epilogue_store4(p, r, c, acc, Lb, p.C);
+          for (int i = 0; i < 8; ++i) acc[i] = *reinterpret_cast<const float4*>(my_stg + (i * 4 + sub) * TC_STG_LD + cl);
+          switch (p.epi) {
+            case EPI_AXPBY: {
+              float4 l[8];
+              if (Lz != nullptr) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                  l[i] = crow[i] >= 0 ? *reinterpret_cast<const float4*>(Lz + crow[i] * p.ldl + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+              }
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                if (crow[i] < 0) continue;
+                float4 o = make_float4(p.alpha * acc[i].x, p.alpha * acc[i].y, p.alpha * acc[i].z, p.alpha * acc[i].w);
+                if (Lz != nullptr) {
+                  o.x = fmaf(p.beta, l[i].x, o.x); o.y = fmaf(p.beta, l[i].y, o.y);
+                  o.z = fmaf(p.beta, l[i].z, o.z); o.w = fmaf(p.beta, l[i].w, o.w);
+                }
+                if (p.round_out) { o.x = round_tf32(o.x); o.y = round_tf32(o.y); o.z = round_tf32(o.z); o.w = round_tf32(o.w); }
+                *reinterpret_cast<float4*>(Cz + crow[i] * p.ldc + c) = o;
+              }
+              break;
+            }
+            case EPI_AXPBY_T: {
+              if (Cz != nullptr) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                  if (crow[i] >= 0) *reinterpret_cast<float4*>(Cz + crow[i] * p.ldc + c) = acc[i];
+              }
+              break;
+            }
+            case EPI_BIAS_GELU: {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                if (crow[i] < 0) continue;
+                float4 o = make_float4(gelu_erf(acc[i].x + b.x), gelu_erf(acc[i].y + b.y), gelu_erf(acc[i].z + b.z), gelu_erf(acc[i].w + b.w));
+                if (p.round_out) { o.x = round_tf32(o.x); o.y = round_tf32(o.y); o.z = round_tf32(o.z); o.w = round_tf32(o.w); }
+                *reinterpret_cast<float4*>(Cz + crow[i] * p.ldc + c) = o;
+                if (irow[i] < p.dup) *reinterpret_cast<float4*>(Cz + (crow[i] + p.rows_per_bag) * p.ldc + c) = o;  // TransMIL.py:180
+              }
+              break;
+            }
+            case EPI_QKV:
+            case EPI_QKV16: {
+              const int which = c / TM_DIM;               // uniform over the 32-column chunk
+              const int cc = c - which * TM_DIM;
+              const int hh = cc / TM_DHEAD, d = cc % TM_DHEAD;
+              const float s = which == 0 ? 0.125f : 1.0f;  // q * dim_head^-0.5
+              float* base = which == 0 ? p.q : (which == 1 ? p.k : p.v);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                if (crow[i] < 0) continue;
+                const long long off = (crow[i] + (long long)hh * p.Sp) * TM_DHEAD + d;
+                if (p.epi == EPI_QKV16) {
+                  uint2 o;
+                  o.x = pack_f16x2(acc[i].x * s, acc[i].y * s);
+                  o.y = pack_f16x2(acc[i].z * s, acc[i].w * s);
+                  *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(base) + off) = o;
+                } else {
+                  float4 o = make_float4(acc[i].x * s, acc[i].y * s, acc[i].z * s, acc[i].w * s);
+                  if (p.round_out) { o.x = round_tf32(o.x); o.y = round_tf32(o.y); o.z = round_tf32(o.z); o.w = round_tf32(o.w); }
+                  *reinterpret_cast<float4*>(base + off) = o;
+                }
+              }
+              break;
+            }
+            case EPI_BIAS_RESID: {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+              float4 l[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i)   // all residual loads in flight before the first store (h_out may alias h_in)
+                l[i] = crow[i] >= 0 ? *reinterpret_cast<const float4*>(p.L + crow[i] * p.ldl + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                if (crow[i] < 0) continue;
+                const float4 o = make_float4(l[i].x + (acc[i].x + b.x), l[i].y + (acc[i].y + b.y), l[i].z + (acc[i].z + b.z),
+                                             l[i].w + (acc[i].w + b.w));
+                *reinterpret_cast<float4*>(Cz + crow[i] * p.ldc + c) = o;
+              }
+              break;
+            }
+          }
         }
         __syncwarp();
       }
@@ -207,32 +353,55 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    tmem_dealloc(tmem_base, 2 * BN);
   }
 }
 
-int gemm_tc(const GemmParams& p, cudaStream_t st) {
-  TM_CHECK_ARG(p.M > 0 && p.N > 0 && p.K > 0, TM_ERR_BAD_SHAPE, "gemm_tc: empty problem");
-  TM_CHECK_ARG(!p.b_is_kn && (p.batch <= 1), TM_ERR_BAD_ARGUMENT, "gemm_tc: only single NT GEMMs (weights [N,K]) are supported");
-  TM_CHECK_ARG(p.N % 4 == 0 && p.K % 4 == 0, TM_ERR_BAD_ALIGNMENT, "gemm_tc: N and K must be multiples of 4");
-  CUtensorMap tmA, tmB;
-  TM_PROPAGATE(make_tmap_2d(&tmA, p.A, (uint64_t)p.M, (uint64_t)p.K, (uint64_t)p.lda, TC_BM, TC_BK));
-  TM_PROPAGATE(make_tmap_2d(&tmB, p.Bm, (uint64_t)p.N, (uint64_t)p.K, (uint64_t)p.ldb, TC_BN, TC_BK));
+template <int BN, bool F16>
+static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int batch, cudaStream_t st) {
   static int sms = 0;
   static bool attr_done = false;
   if (!attr_done) {
     int dev = 0;
     TM_CUDA(cudaGetDevice(&dev));
     TM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    TM_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM));
+    TM_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TcCfg<BN>::SMEM));
     attr_done = true;
   }
-  const int m_tiles = (int)ceil_div(p.M, TC_BM), n_tiles = (int)ceil_div(p.N, TC_BN), k_blocks = (int)ceil_div(p.K, TC_BK);
-  const int total = m_tiles * n_tiles;
-  const int grid = total < sms ? total : sms;
-  gemm_tc_kernel<<<grid, TC_THREADS, TC_SMEM, st>>>(tmA, tmB, p, m_tiles, n_tiles, k_blocks);
+  const int BK = F16 ? 64 : 32;
+  const int m_tiles = (int)ceil_div(p.M, TC_BM), n_tiles = (int)ceil_div(p.N, BN), k_blocks = (int)ceil_div(p.K, BK);
+  const long long total = (long long)m_tiles * n_tiles * batch;
+  TM_CHECK_ARG(total < (1ll << 31), TM_ERR_BAD_SHAPE, "gemm_tc: too many tiles");
+  const int grid = total < sms ? (int)total : sms;
+  gemm_tc_kernel<BN, F16><<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(tmA, tmB, p, m_tiles, n_tiles, k_blocks, (int)total);
   TM_LAUNCH_CHECK();
   return TM_OK;
+}
+
+int gemm_tc(const GemmParams& p, cudaStream_t st) {
+  TM_CHECK_ARG(p.M > 0 && p.N > 0 && p.K > 0, TM_ERR_BAD_SHAPE, "gemm_tc: empty problem");
+  TM_CHECK_ARG(!p.b_is_kn, TM_ERR_BAD_ARGUMENT, "gemm_tc: only NT GEMMs (B operand stored [N,K]) are supported");
+  TM_CHECK_ARG(p.N % 4 == 0 && p.K % 4 == 0, TM_ERR_BAD_ALIGNMENT, "gemm_tc: N and K must be multiples of 4");
+  const int batch = p.batch > 0 ? p.batch : 1;
+  const uint64_t sA = batch > 1 ? (uint64_t)p.strideA : (uint64_t)p.M * p.lda;
+  const uint64_t sB = batch > 1 ? (uint64_t)p.strideB : (uint64_t)p.N * p.ldb;
+  CUtensorMap tmA, tmB;
+  if (p.f16_in) {
+    TM_PROPAGATE(make_tmap_3d_f16(&tmA, p.A, batch, (uint64_t)p.M, (uint64_t)p.K, sA, (uint64_t)p.lda, TC_BM, 64));
+    if (p.bn128) {
+      TM_PROPAGATE(make_tmap_3d_f16(&tmB, p.Bm, batch, (uint64_t)p.N, (uint64_t)p.K, sB, (uint64_t)p.ldb, 128, 64));
+      return launch_tc<128, true>(tmA, tmB, p, batch, st);
+    }
+    TM_PROPAGATE(make_tmap_3d_f16(&tmB, p.Bm, batch, (uint64_t)p.N, (uint64_t)p.K, sB, (uint64_t)p.ldb, 256, 64));
+    return launch_tc<256, true>(tmA, tmB, p, batch, st);
+  }
+  TM_PROPAGATE(make_tmap_3d(&tmA, p.A, batch, (uint64_t)p.M, (uint64_t)p.K, sA, (uint64_t)p.lda, TC_BM, 32));
+  if (p.bn128) {
+    TM_PROPAGATE(make_tmap_3d(&tmB, p.Bm, batch, (uint64_t)p.N, (uint64_t)p.K, sB, (uint64_t)p.ldb, 128, 32));
+    return launch_tc<128, false>(tmA, tmB, p, batch, st);
+  }
+  TM_PROPAGATE(make_tmap_3d(&tmB, p.Bm, batch, (uint64_t)p.N, (uint64_t)p.K, sB, (uint64_t)p.ldb, 256, 32));
+  return launch_tc<256, false>(tmA, tmB, p, batch, st);
 }
 
 }  // namespace tmil

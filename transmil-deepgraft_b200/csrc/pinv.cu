@@ -8,6 +8,7 @@
 //   XZ = A Z;  T1 = 7 XZ - XZ XZ;  T2 = 15 XZ - XZ T1;  Z' = 3.25 Z - 0.25 Z T2
 // which equals 1/4 Z (13 I - XZ (15 I - XZ (7 I - XZ))) in exact arithmetic.
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace tmil {
 
@@ -16,6 +17,7 @@ constexpr int ROWS = 32;           // rows of attn2 per CTA
 constexpr int KLD = 68;            // padded row stride of k_lm in smem (floats)
 
 // grid (LM/ROWS, B*8).  smem: k_lm [256][68] + q rows [32][68] + P tile [32][257]
+template <bool ROUND>
 __global__ void __launch_bounds__(256) attn2_kernel(const float* __restrict__ q_lm, const float* __restrict__ k_lm,
                                                     float* __restrict__ attn2, float* __restrict__ rowsum,
                                                     float* __restrict__ colpart) {
@@ -74,7 +76,7 @@ __global__ void __launch_bounds__(256) attn2_kernel(const float* __restrict__ q_
 #pragma unroll 8
   for (int rr = 0; rr < ROWS; ++rr) {
     float p = ps[rr * 257 + tid];
-    ag[rr * LM + tid] = p;
+    ag[rr * LM + tid] = ROUND ? round_tf32(p) : p;
     cs += p;
   }
   colpart[((long long)bh * (LM / ROWS) + tile) * LM + tid] = cs;     // partial |x|.sum(-2)
@@ -103,15 +105,21 @@ __global__ void __launch_bounds__(1024) pinv_scale_kernel(const float* __restric
 }
 
 // Z0 = A^T / scale, 32x32 smem transpose tiles.  grid (8, 8, B*8), block (32, 8)
+template <bool TC>
 __global__ void __launch_bounds__(256) pinv_z0_kernel(const float* __restrict__ A, const float* __restrict__ scale,
-                                                      float* __restrict__ Z) {
+                                                      float* __restrict__ Z, float* __restrict__ ZT) {
   __shared__ float t[32][33];
   const long long base = (long long)blockIdx.z * LM * LM;
   const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 32;
   for (int i = threadIdx.y; i < 32; i += 8) t[i][threadIdx.x] = A[base + (long long)(y0 + i) * LM + x0 + threadIdx.x];
   __syncthreads();
   const float sc = scale[0];
-  for (int i = threadIdx.y; i < 32; i += 8) Z[base + (long long)(x0 + i) * LM + y0 + threadIdx.x] = t[threadIdx.x][i] / sc;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const float z = t[threadIdx.x][i] / sc;
+    Z[base + (long long)(x0 + i) * LM + y0 + threadIdx.x] = TC ? round_tf32(z) : z;
+  }
+  if (TC)   // Z0^T = A / scale: the B operand of the first A @ Z product
+    for (int i = threadIdx.y; i < 32; i += 8) ZT[base + (long long)(y0 + i) * LM + x0 + threadIdx.x] = round_tf32(t[i][threadIdx.x] / sc);
 }
 
 static int pinv_gemm(const float* L, const float* R, float* C, float alpha, float beta, const float* addL, int nbh,
@@ -126,39 +134,76 @@ static int pinv_gemm(const float* L, const float* R, float* C, float alpha, floa
   return gemm_simt(p, st);
 }
 
+// One product of the chain on the tensor cores: every iterate is kept in both orientations, so X @ Y is the NT GEMM
+// X . (Y^T)^T with tf32 operands (all stored iterates are tf32-rounded by their producer) and fp32 accumulation;
+// out = alpha * X@Y + beta * L, with L supplied transposed (LT) and the result written as C and/or C^T.
+static int pinv_gemm_tc(const float* X, const float* YT, float alpha, float beta, const float* LT, float* C, float* CT, bool round,
+                        int nbh, cudaStream_t st) {
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.A = X; p.Bm = YT; p.C = C; p.CT = CT;
+  p.M = p.N = p.K = LM; p.lda = p.ldb = p.ldc = p.ldl = LM;
+  p.batch = nbh; p.bn128 = 1;
+  p.strideA = p.strideB = p.strideC = p.strideL = (long long)LM * LM;
+  p.epi = EPI_AXPBY_T; p.alpha = alpha; p.beta = beta; p.L = LT; p.round_out = round ? 1 : 0;
+  return gemm_tc(p, st);
+}
+
 }  // namespace tmil
 
 extern "C" int64_t tm_pinv_scratch_floats(int64_t B) {
   const int64_t nbh = B * TM_HEADS;
-  return 3 * nbh * 65536 + nbh * 256 * 9 + 64;
+  return 7 * nbh * 65536 + nbh * 256 * 9 + 64;   // tensor-core chain: XZ, XZ^T, T1^T, T2^T, Z', Z^T, Z'^T
 }
 
 extern "C" int tm_pinv_fwd(const float* q_lm, const float* k_lm, int64_t B, float* attn2, float* Z, float* scratch,
                            uint32_t flags, void* stream) {
   using namespace tmil;
-  (void)flags;
   TM_CHECK_ARG(B > 0 && q_lm && k_lm && attn2 && Z && scratch, TM_ERR_BAD_ARGUMENT, "tm_pinv_fwd: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   const int nbh = (int)(B * TM_HEADS);
   const long long mat = 65536;
+  const bool tc = !(flags & TM_FLAG_SIMT_ONLY) && tc_available();
   float* XZ = scratch;
   float* T1 = XZ + nbh * mat;
   float* T2 = T1 + nbh * mat;
-  float* rowsum = T2 + nbh * mat;
+  float* XZT = T2 + nbh * mat;
+  float* Zb = XZT + nbh * mat;
+  float* ZTa = Zb + nbh * mat;
+  float* ZTb = ZTa + nbh * mat;
+  float* rowsum = ZTb + nbh * mat;
   float* colpart = rowsum + (long long)nbh * LM;
   float* scale = colpart + (long long)nbh * LM * (LM / ROWS);
 
   static bool attr_done = false;
   const size_t smem = (size_t)(LM * KLD + ROWS * KLD + ROWS * 257) * sizeof(float);
   if (!attr_done) {
-    TM_CUDA(cudaFuncSetAttribute(attn2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TM_CUDA(cudaFuncSetAttribute(attn2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TM_CUDA(cudaFuncSetAttribute(attn2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done = true;
   }
-  attn2_kernel<<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
+  if (tc) attn2_kernel<true><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
+  else attn2_kernel<false><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
   TM_LAUNCH_CHECK();
   pinv_scale_kernel<<<1, 1024, 0, st>>>(rowsum, colpart, nbh, scale);
   TM_LAUNCH_CHECK();
-  pinv_z0_kernel<<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, scale, Z);
+  if (tc) {
+    pinv_z0_kernel<true><<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, scale, Z, ZTa);
+    TM_LAUNCH_CHECK();
+    float* Zc = Z; float* Zn = Zb; float* ZTc = ZTa; float* ZTn = ZTb;
+    float* T1T = T1; float* T2T = T2;
+    for (int it = 0; it < TM_PINV_ITERS; ++it) {
+      const bool last = it == TM_PINV_ITERS - 1;
+      TM_PROPAGATE(pinv_gemm_tc(attn2, ZTc, 1.f, 0.f, nullptr, XZ, XZT, true, nbh, st));          // XZ = A Z (+ XZ^T)
+      TM_PROPAGATE(pinv_gemm_tc(XZ, XZT, -1.f, 7.f, XZT, nullptr, T1T, true, nbh, st));           // T1^T,  T1 = 7 XZ - XZ XZ
+      TM_PROPAGATE(pinv_gemm_tc(XZ, T1T, -1.f, 15.f, XZT, nullptr, T2T, true, nbh, st));          // T2^T,  T2 = 15 XZ - XZ T1
+      TM_PROPAGATE(pinv_gemm_tc(Zc, T2T, -0.25f, 3.25f, ZTc, Zn, last ? nullptr : ZTn, !last, nbh, st));  // Z' = 3.25 Z - 0.25 Z T2
+      float* t = Zc; Zc = Zn; Zn = t;
+      t = ZTc; ZTc = ZTn; ZTn = t;
+    }
+    return TM_OK;   // 6 swaps: the final iterate is back in the caller's Z
+  }
+  pinv_z0_kernel<false><<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, scale, Z, nullptr);
   TM_LAUNCH_CHECK();
   float* Zc = Z;      // current iterate
   float* Zn = T1;     // T1's storage is free again when Z' is formed
