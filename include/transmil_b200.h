@@ -55,6 +55,9 @@ typedef enum tm_fc1_kind {
                                     MMA's operand truncation is exact; set internally by tm_transmil_fwd when the tcgen05
                                     engine runs.  Callers of the per-kernel entry points pass it themselves. */
 
+#define TM_FLAG_PINV_GEMM_CHAIN 8u /* run the pinv chain as 24 batched tcgen05 GEMM launches (tf32 operands) instead of the
+                                    single 4-CTA-cluster kernel (fp16 operands); kept for cross-checking */
+
 /* Index contract of one bag (TransMIL.py:177-179,184-186,190-193 and the
  * nystrom-attention 0.0.11 front pad / landmark grouping).  Pure host code. */
 typedef struct tm_plan {
@@ -214,6 +217,8 @@ int tm_qkv16_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, voi
 /* K5 on fp16 q/k: fp32 landmark means (fp32 accumulation) plus their fp16 copies. */
 int tm_landmarks16_fwd(const void* q16, const void* k16, int64_t B, int64_t Sp, int64_t l, float* q_lm,
                        float* k_lm, void* qlm16, void* klm16, void* stream);
+/* M = Z @ W3 in fp32 with both layouts written at once: M [B,8,256,64] fp32 and mt16 [B,8,64,256] fp16. */
+int tm_zw16_fwd(const float* Z, const float* W3, int64_t B, float* M, void* mt16, void* stream);
 /* mt16[b,h,d,j] = half(M[b,h,j,d])  (K-major B operand of attn1 @ M). */
 int tm_mt16_fwd(const float* M, void* mt16, int64_t B, void* stream);
 /* K9+K10+K11, same contract as tm_nystrom_out_fwd (nystrom-attention 0.0.11 forward: attn1, (attn1 @ Z) @ W3, res_conv). */

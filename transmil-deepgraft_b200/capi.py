@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libtransmil_b200.so")
 TM_FLAG_SIMT_ONLY = 1
 TM_FLAG_KEEP_STAGES = 2
 TM_FLAG_TF32_OPERANDS = 4
+TM_FLAG_PINV_GEMM_CHAIN = 8
 TM_FC1_SINGLE, TM_FC1_2048, TM_FC1_768 = 0, 1, 2
 
 _fp = C.c_void_p  # device/host float pointers travel as raw addresses
@@ -73,6 +74,7 @@ SIGNATURES = {
     "tm_qkv16_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _u32, _fp]),
     "tm_landmarks16_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _fp, _fp, _fp, _fp, _fp]),
     "tm_stage_is_f16": (C.c_int, [C.c_char_p, _u32]),
+    "tm_zw16_fwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp, _fp]),
     "tm_mt16_fwd": (C.c_int, [_fp, _fp, _i64, _fp]),
     "tm_nystrom_out_tc_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
     "tm_attn3v_tc_scratch_floats": (_i64, [_i64, _i64]),

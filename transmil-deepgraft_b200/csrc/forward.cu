@@ -126,8 +126,7 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
     prof_mark(ST_ATTN3V, st);
     TM_PROPAGATE(tm_attn3v_tc_fwd(qlm16, k16, v16, B, p.Sp, W3, ws + L.a3_s, flags, st));
     prof_mark(ST_ZW, st);
-    TM_PROPAGATE(tm_zw_fwd(Z, W3, B, M, st));
-    TM_PROPAGATE(tm_mt16_fwd(M, mt16, B, st));
+    TM_PROPAGATE(tm_zw16_fwd(Z, W3, B, M, mt16, st));
     prof_mark(ST_NYSTROM_OUT, st);
     TM_PROPAGATE(tm_nystrom_out_tc_fwd(q16, klm16, mt16, v16, lw.conv_w, B, p.Sp, merged, flags, st));
   } else {

@@ -40,14 +40,16 @@ __global__ void __launch_bounds__(256) landmarks_kernel(const float* __restrict_
 }
 
 // fp16 q/k (tensor-core engine): same means accumulated in fp32; emits the fp32 landmarks (sim2 / pinv run in fp32)
-// and fp16 copies (operands of the tensor-core contractions).  8 lanes x 16 bytes per 64-wide fp16 row.
+// and fp16 copies (operands of the tensor-core contractions).  One WARP per landmark group so that a 50k-token bag
+// (4096 groups of ~200 rows) keeps enough loads in flight to reach HBM speed: lane = (row phase 0..3, 16-byte column
+// chunk 0..7); the four phases are reduced with shuffles in a fixed order.
 __global__ void __launch_bounds__(256) landmarks16_kernel(const __half* __restrict__ q, const __half* __restrict__ k,
                                                           long long groups_per_tensor, int l, float* __restrict__ q_lm,
                                                           float* __restrict__ k_lm, __half* __restrict__ qlm16,
                                                           __half* __restrict__ klm16) {
-  const long long gid = (long long)blockIdx.x * 32 + (threadIdx.x >> 3);
+  const long long gid = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (gid >= 2 * groups_per_tensor) return;
-  const int lane8 = threadIdx.x & 7;
+  const int lane = threadIdx.x & 31, lane8 = lane & 7, phase = lane >> 3;
   const bool is_k = gid >= groups_per_tensor;
   const long long g = is_k ? gid - groups_per_tensor : gid;
   const uint4* src = reinterpret_cast<const uint4*>((is_k ? k : q) + g * (long long)l * TM_DHEAD) + lane8;
@@ -62,13 +64,19 @@ __global__ void __launch_bounds__(256) landmarks16_kernel(const __half* __restri
       acc[2 * e] += f.x; acc[2 * e + 1] += f.y;
     }
   };
-  int j = 0;
-  for (; j + 4 <= l; j += 4) {
-    const uint4 a = __ldg(src + (long long)(j + 0) * 8), b = __ldg(src + (long long)(j + 1) * 8);
-    const uint4 c = __ldg(src + (long long)(j + 2) * 8), d = __ldg(src + (long long)(j + 3) * 8);
+  int j = phase;
+  for (; j + 12 < l; j += 16) {
+    const uint4 a = __ldg(src + (long long)(j + 0) * 8), b = __ldg(src + (long long)(j + 4) * 8);
+    const uint4 c = __ldg(src + (long long)(j + 8) * 8), d = __ldg(src + (long long)(j + 12) * 8);
     add(a); add(b); add(c); add(d);
   }
-  for (; j < l; ++j) add(__ldg(src + (long long)j * 8));
+  for (; j < l; j += 4) add(__ldg(src + (long long)j * 8));
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
+    acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
+  }
+  if (phase != 0) return;
   const float fl = (float)l;
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] /= fl;
@@ -103,7 +111,7 @@ extern "C" int tm_landmarks16_fwd(const void* q16, const void* k16, int64_t B, i
                    tmil::aligned16(qlm16) && tmil::aligned16(klm16), TM_ERR_BAD_ALIGNMENT,
                "tm_landmarks16_fwd: pointers must be 16-byte aligned");
   const long long groups = (long long)B * TM_HEADS * TM_LANDMARKS;
-  tmil::landmarks16_kernel<<<(unsigned)tmil::ceil_div(2 * groups, 32), 256, 0, (cudaStream_t)stream>>>(
+  tmil::landmarks16_kernel<<<(unsigned)tmil::ceil_div(2 * groups, 8), 256, 0, (cudaStream_t)stream>>>(
       (const __half*)q16, (const __half*)k16, groups, (int)l, q_lm, k_lm, (__half*)qlm16, (__half*)klm16);
   TM_LAUNCH_CHECK();
   return TM_OK;

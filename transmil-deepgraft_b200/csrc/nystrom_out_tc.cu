@@ -246,6 +246,36 @@ __global__ void __launch_bounds__(256) mt16_kernel(const float* __restrict__ M, 
   }
 }
 
+// M = Z @ W3 in exact fp32 (256x256 @ 256x64 per head) with both consumers' layouts written at once:
+// M [bh][j][d] fp32 (stage buffer) and mt16 [bh][d][j] fp16 (K-major B operand of attn1 @ M).
+// grid (16, B*8): 16 rows per CTA; thread = (row, 4 columns); Z rows staged in smem, W3 streamed through L1/L2.
+__global__ void __launch_bounds__(256) zw16_kernel(const float* __restrict__ Z, const float* __restrict__ W3, float* __restrict__ M,
+                                                   __half* __restrict__ mt16) {
+  __shared__ __align__(16) float zs[16][TM_LANDMARKS];
+  const int bh = blockIdx.y, r0 = blockIdx.x * 16, tid = threadIdx.x;
+  const float4* zg = reinterpret_cast<const float4*>(Z + ((long long)bh * TM_LANDMARKS + r0) * TM_LANDMARKS);
+  for (int i = tid; i < 16 * 64; i += 256) reinterpret_cast<float4*>(&zs[0][0])[i] = __ldg(zg + i);
+  __syncthreads();
+  const int ry = tid >> 4, cx = tid & 15;
+  const float4* wg = reinterpret_cast<const float4*>(W3 + (long long)bh * TM_LANDMARKS * TM_DHEAD) + cx;
+  float4 acc0 = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc0;
+#pragma unroll 4
+  for (int k = 0; k < TM_LANDMARKS; k += 2) {
+    const float4 w0 = __ldg(wg + (long long)k * 16), w1 = __ldg(wg + (long long)(k + 1) * 16);
+    const float z0 = zs[ry][k], z1 = zs[ry][k + 1];
+    acc0.x = fmaf(z0, w0.x, acc0.x); acc0.y = fmaf(z0, w0.y, acc0.y); acc0.z = fmaf(z0, w0.z, acc0.z); acc0.w = fmaf(z0, w0.w, acc0.w);
+    acc1.x = fmaf(z1, w1.x, acc1.x); acc1.y = fmaf(z1, w1.y, acc1.y); acc1.z = fmaf(z1, w1.z, acc1.z); acc1.w = fmaf(z1, w1.w, acc1.w);
+  }
+  const float4 o = make_float4(acc0.x + acc1.x, acc0.y + acc1.y, acc0.z + acc1.z, acc0.w + acc1.w);
+  const int r = r0 + ry;
+  reinterpret_cast<float4*>(M + ((long long)bh * TM_LANDMARKS + r) * TM_DHEAD)[cx] = o;
+  __half* mt = mt16 + ((long long)bh * TM_DHEAD + cx * 4) * TM_LANDMARKS + r;
+  mt[0] = __float2half_rn(o.x);
+  mt[TM_LANDMARKS] = __float2half_rn(o.y);
+  mt[2 * TM_LANDMARKS] = __float2half_rn(o.z);
+  mt[3 * TM_LANDMARKS] = __float2half_rn(o.w);
+}
+
 int attn_chunks(int64_t nbh, int64_t tiles_per_bh) {
   int64_t c = (148 + nbh / 2) / nbh;   // about one CTA per SM in total
   if (c < 1) c = 1;
@@ -259,6 +289,14 @@ extern "C" int tm_mt16_fwd(const float* M, void* mt16, int64_t B, void* stream) 
   using namespace tmil;
   TM_CHECK_ARG(M && mt16 && B > 0, TM_ERR_BAD_ARGUMENT, "tm_mt16_fwd: bad arguments");
   mt16_kernel<<<dim3(4, (unsigned)(B * TM_HEADS)), 256, 0, (cudaStream_t)stream>>>(M, (__half*)mt16);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+extern "C" int tm_zw16_fwd(const float* Z, const float* W3, int64_t B, float* M, void* mt16, void* stream) {
+  using namespace tmil;
+  TM_CHECK_ARG(Z && W3 && M && mt16 && B > 0, TM_ERR_BAD_ARGUMENT, "tm_zw16_fwd: bad arguments");
+  zw16_kernel<<<dim3(16, (unsigned)(B * TM_HEADS)), 256, 0, (cudaStream_t)stream>>>(Z, W3, M, (__half*)mt16);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -137,6 +137,8 @@ static int pinv_gemm(const float* L, const float* R, float* C, float alpha, floa
 // One product of the chain on the tensor cores: every iterate is kept in both orientations, so X @ Y is the NT GEMM
 // X . (Y^T)^T with tf32 operands (all stored iterates are tf32-rounded by their producer) and fp32 accumulation;
 // out = alpha * X@Y + beta * L, with L supplied transposed (LT) and the result written as C and/or C^T.
+int pinv_cluster_run(const float* attn2, const float* scale, int nbh, void* scratch16, float* Z, cudaStream_t st);   // pinv_cluster.cu
+
 static int pinv_gemm_tc(const float* X, const float* YT, float alpha, float beta, const float* LT, float* C, float* CT, bool round,
                         int nbh, cudaStream_t st) {
   GemmParams p;
@@ -182,11 +184,14 @@ extern "C" int tm_pinv_fwd(const float* q_lm, const float* k_lm, int64_t B, floa
     TM_CUDA(cudaFuncSetAttribute(attn2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done = true;
   }
-  if (tc) attn2_kernel<true><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
+  const bool cluster = tc && !(flags & TM_FLAG_PINV_GEMM_CHAIN);
+  if (tc && !cluster) attn2_kernel<true><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
   else attn2_kernel<false><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
   TM_LAUNCH_CHECK();
   pinv_scale_kernel<<<1, 1024, 0, st>>>(rowsum, colpart, nbh, scale);
   TM_LAUNCH_CHECK();
+  if (cluster)   // one 4-CTA-cluster kernel for the whole chain (fp16 operands); attn2 stays exact fp32
+    return pinv_cluster_run(attn2, scale, nbh, XZ, Z, st);
   if (tc) {
     pinv_z0_kernel<true><<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, scale, Z, ZTa);
     TM_LAUNCH_CHECK();

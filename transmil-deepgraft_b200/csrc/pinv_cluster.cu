@@ -1,0 +1,250 @@
+// K7 as ONE kernel: the 6 Moore-Penrose iterations (24 dependent 256^3 products) of every (bag, head) run inside a
+// 4-CTA thread-block cluster, fp16 operands / fp32 accumulation on the tensor cores.
+//
+//   Z <- 1/4 Z (13 I - XZ (15 I - XZ (7 I - XZ))),  XZ = A Z        (nystrom-attention 0.0.11 moore_penrose_iter_pinv)
+//   evaluated as  XZ = A Z;  T1 = 7 XZ - XZ XZ;  T2 = 15 XZ - XZ T1;  Z' = 3.25 Z - 0.25 Z T2   (same as pinv.cu)
+//
+// CTA (mi, ni) of the cluster owns the 128x128 output block (rows 128 mi.., columns 128 ni..) of every product X @ Y:
+//   A operand = X[128 mi .. +128, :]   K-major   (4 k-blocks of [128 rows][64 k])
+//   B operand = Y[:, 128 ni .. +128]   MN-major  (2 column groups of [256 k rows][64 n]) -- the row-major iterate serves both
+//   roles, so every iterate is stored once, row-major fp16, in global memory (L2 resident: 128 KB each).
+// A product needs blocks written by the other CTAs of the cluster: one hardware cluster barrier per product orders the
+// global stores of step s before the TMA loads of step s+1 (release/acquire + proxy fence); there is no host round trip and
+// no relaunch.  The second term of each update (XZ, Z) is the CTA's own previous output block: it stays in registers as
+// packed fp16.  Operand loads that do not depend on the step in flight (A rows, Z rows) are prefetched behind the barrier.
+// Warp roles: warp 0 TMA, warp 1 MMA issue, warps 2-5 epilogue (one thread per output row).
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace tmil {
+
+constexpr int PC_THREADS = 192;
+constexpr int PC_OP_BYTES = 65536;                       // one operand tile: 128 x 256 (A) or 256 x 128 (B) fp16
+constexpr size_t PC_SMEM = 1024 + 2 * PC_OP_BYTES + 256;
+constexpr int PC_STEPS = 4 * TM_PINV_ITERS;
+
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+struct PinvMaps {
+  CUtensorMap A, Za, Zb, XZ, T1, T2;   // [nbh][256][256] fp16, box [1][64][64]
+};
+
+__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(PC_THREADS, 1)
+pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ Za, __half* __restrict__ Zb,
+                    __half* __restrict__ XZ, __half* __restrict__ T1, __half* __restrict__ T2, float* __restrict__ Zout) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + PC_OP_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * PC_OP_BYTES);
+  uint64_t* fullA = bars;         // [4] per k-block of the A operand
+  uint64_t* fullB = bars + 4;     // [4] per 64-row k-chunk of the B operand
+  uint64_t* mma_done = bars + 8;  // accumulator of the step complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = blockIdx.x;          // cluster spans gridDim.x = 4
+  const int mi = rank >> 1, ni = rank & 1;
+  const int bh = blockIdx.y;
+  const long long mat = (long long)bh * TM_LANDMARKS * TM_LANDMARKS;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&maps.A); tma_prefetch_desc(&maps.Za); tma_prefetch_desc(&maps.Zb);
+    tma_prefetch_desc(&maps.XZ); tma_prefetch_desc(&maps.T1); tma_prefetch_desc(&maps.T2);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < 4; ++i) { mbar_init(&fullA[i], 1); mbar_init(&fullB[i], 1); }
+    mbar_init(mma_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 128);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ---- TMA producer ------------------------------------------------------------------------------------------
+    auto loadA = [&](const CUtensorMap* m) {   // rows 128 mi .. +128 of a row-major iterate, K-major k-blocks
+#pragma unroll
+      for (int kb = 0; kb < 4; ++kb) {
+        mbar_arrive_expect_tx(&fullA[kb], 16384);
+        tma_load_3d(sA + kb * 16384, m, &fullA[kb], kb * 64, 128 * mi, bh);
+        tma_load_3d(sA + kb * 16384 + 8192, m, &fullA[kb], kb * 64, 128 * mi + 64, bh);
+      }
+    };
+    auto loadB = [&](const CUtensorMap* m) {   // columns 128 ni .. +128, MN-major: 2 groups of [256 k rows][64 n]
+#pragma unroll
+      for (int kc = 0; kc < 4; ++kc) {
+        mbar_arrive_expect_tx(&fullB[kc], 16384);
+        tma_load_3d(sB + kc * 8192, m, &fullB[kc], 128 * ni, kc * 64, bh);
+        tma_load_3d(sB + 32768 + kc * 8192, m, &fullB[kc], 128 * ni + 64, kc * 64, bh);
+      }
+    };
+    if (lane == 0) loadA(&maps.A);
+    __syncwarp();
+    for (int s = 0; s < PC_STEPS; ++s) {
+      cluster_sync_all();
+      if (lane == 0) {
+        fence_proxy_async_all();
+        const int it = s >> 2, g = s & 3;
+        const CUtensorMap* zc = (it & 1) ? &maps.Zb : &maps.Za;
+        if (g == 1) loadA(&maps.XZ);
+        loadB(g == 0 ? zc : (g == 1 ? &maps.XZ : (g == 2 ? &maps.T1 : &maps.T2)));
+        if (g == 2) {                       // next A operand = Z rows: independent of the step in flight
+          mbar_wait(mma_done, s & 1);
+          loadA(zc);
+        } else if (g == 3 && s + 1 < PC_STEPS) {
+          mbar_wait(mma_done, s & 1);
+          loadA(&maps.A);
+        }
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ---- MMA issuer --------------------------------------------------------------------------------------------
+    constexpr uint32_t idesc = umma_idesc_f16(128, 64, 0, 1);   // A K-major, B MN-major
+    uint32_t nA = 0;
+    for (int s = 0; s < PC_STEPS; ++s) {
+      cluster_sync_all();
+      if (lane == 0) {
+        tc_fence_after();
+        const bool newA = (s & 3) != 2;
+#pragma unroll
+        for (int kc = 0; kc < 4; ++kc) {
+          if (newA) mbar_wait(&fullA[kc], nA & 1);
+          mbar_wait(&fullB[kc], s & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4) {
+            const int ks = kc * 4 + k4;
+            const uint64_t dA = umma_desc_k_sw128(smem_u32(sA + kc * 16384)) + 2 * k4;
+#pragma unroll
+            for (int gg = 0; gg < 2; ++gg) {
+              const uint64_t dB = umma_desc_mn_sw128(smem_u32(sB + gg * 32768 + ks * 2048), 32768, 1024);
+              umma_f16_ss(tmem_base + gg * 64, dA, dB, idesc, ks > 0 ? 1u : 0u);
+            }
+          }
+        }
+        umma_commit(mma_done);
+        if (newA) ++nA;
+      }
+      __syncwarp();
+    }
+  } else {
+    // ---- epilogue: one thread per row of the 128x128 block ---------------------------------------------------------
+    const int qd = warp & 3;
+    const int r = qd * 32 + lane;
+    const uint32_t t_row = tmem_base + ((uint32_t)(qd * 32) << 16);
+    const long long row_off = mat + (long long)(128 * mi + r) * TM_LANDMARKS + 128 * ni;
+    uint32_t xz[64], zs[64];   // own XZ block row / own Z block row, packed fp16 (the second terms of the updates)
+    {
+      const uint4* z0 = reinterpret_cast<const uint4*>(Za + row_off);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const uint4 u = __ldcg(z0 + i);
+        zs[4 * i] = u.x; zs[4 * i + 1] = u.y; zs[4 * i + 2] = u.z; zs[4 * i + 3] = u.w;
+      }
+    }
+    for (int s = 0; s < PC_STEPS; ++s) {
+      cluster_sync_all();
+      const int it = s >> 2, g = s & 3;
+      const bool last = s == PC_STEPS - 1;
+      __half* dst = g == 0 ? XZ : (g == 1 ? T1 : (g == 2 ? T2 : ((it & 1) ? Za : Zb)));
+      mbar_wait(mma_done, s & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) {
+        float v[32];
+        tmem_ld_32x32(t_row + ch * 32, v);
+        uint32_t pk[16];
+        if (g == 0) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) { pk[e] = pack_f16x2(v[2 * e], v[2 * e + 1]); xz[ch * 16 + e] = pk[e]; }
+        } else if (g == 3) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const float2 z = __half22float2(*reinterpret_cast<const __half2*>(&zs[ch * 16 + e]));
+            v[2 * e] = fmaf(3.25f, z.x, -0.25f * v[2 * e]);
+            v[2 * e + 1] = fmaf(3.25f, z.y, -0.25f * v[2 * e + 1]);
+            pk[e] = pack_f16x2(v[2 * e], v[2 * e + 1]);
+            zs[ch * 16 + e] = pk[e];
+          }
+        } else {
+          const float c = g == 1 ? 7.0f : 15.0f;
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&xz[ch * 16 + e]));
+            pk[e] = pack_f16x2(fmaf(c, x.x, -v[2 * e]), fmaf(c, x.y, -v[2 * e + 1]));
+          }
+        }
+        if (last) {   // final iterate: fp32, unrounded, straight into the caller's Z
+          float4* zo = reinterpret_cast<float4*>(Zout + row_off + ch * 32);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) zo[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+        } else {
+          uint4* d4 = reinterpret_cast<uint4*>(dst + row_off + ch * 32);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) d4[e] = make_uint4(pk[4 * e], pk[4 * e + 1], pk[4 * e + 2], pk[4 * e + 3]);
+        }
+      }
+      tc_fence_before();           // TMEM reads retire before the next step's MMA overwrites the accumulator
+      fence_proxy_async_all();     // generic-proxy global stores -> visible to the peers' TMA (async proxy) loads
+    }
+  }
+  cluster_sync_all();
+  tc_fence_after();
+  if (warp == 2) tmem_dealloc(tmem_base, 128);
+}
+
+// A16 = half(attn2);  Z0 = half(attn2^T / scale)      grid (8, 8, B*8), block (32, 8)
+__global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restrict__ A, const float* __restrict__ scale,
+                                                          __half* __restrict__ A16, __half* __restrict__ Z16) {
+  __shared__ float t[32][33];
+  const long long base = (long long)blockIdx.z * TM_LANDMARKS * TM_LANDMARKS;
+  const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const long long o = base + (long long)(y0 + i) * TM_LANDMARKS + x0 + threadIdx.x;
+    const float a = A[o];
+    t[i][threadIdx.x] = a;
+    A16[o] = __float2half_rn(a);
+  }
+  __syncthreads();
+  const float sc = scale[0];
+  for (int i = threadIdx.y; i < 32; i += 8)
+    Z16[base + (long long)(x0 + i) * TM_LANDMARKS + y0 + threadIdx.x] = __float2half_rn(t[threadIdx.x][i] / sc);
+}
+
+// scratch16: 6 fp16 matrices per (bag, head): A16, Za, Zb, XZ, T1, T2
+int pinv_cluster_run(const float* attn2, const float* scale, int nbh, void* scratch16, float* Z, cudaStream_t st) {
+  TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "pinv_cluster_run needs an sm_100 device");
+  const long long mat = (long long)TM_LANDMARKS * TM_LANDMARKS;
+  __half* A16 = (__half*)scratch16;
+  __half* Za = A16 + nbh * mat;
+  __half* Zb = Za + nbh * mat;
+  __half* XZ = Zb + nbh * mat;
+  __half* T1 = XZ + nbh * mat;
+  __half* T2 = T1 + nbh * mat;
+  pinv_prep16_kernel<<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, scale, A16, Za);
+  TM_LAUNCH_CHECK();
+  PinvMaps maps;
+  __half* ptrs[6] = {A16, Za, Zb, XZ, T1, T2};
+  CUtensorMap* ms[6] = {&maps.A, &maps.Za, &maps.Zb, &maps.XZ, &maps.T1, &maps.T2};
+  for (int i = 0; i < 6; ++i)
+    TM_PROPAGATE(make_tmap_3d_f16(ms[i], ptrs[i], nbh, TM_LANDMARKS, TM_LANDMARKS, mat, TM_LANDMARKS, 64, 64));
+  static bool attr_done = false;
+  if (!attr_done) {
+    TM_CUDA(cudaFuncSetAttribute(pinv_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PC_SMEM));
+    attr_done = true;
+  }
+  pinv_cluster_kernel<<<dim3(4, nbh), PC_THREADS, PC_SMEM, st>>>(maps, Za, Zb, XZ, T1, T2, Z);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+}  // namespace tmil
