@@ -55,6 +55,8 @@ typedef enum tm_fc1_kind {
                                     MMA's operand truncation is exact; set internally by tm_transmil_fwd when the tcgen05
                                     engine runs.  Callers of the per-kernel entry points pass it themselves. */
 
+#define TM_FLAG_F16_ACT 16u       /* per-kernel entry points of the tensor-core engine: the activation that feeds the next fp16
+                                    contraction (xn, merged) is read / written as fp16; set internally by tm_transmil_fwd */
 #define TM_FLAG_PINV_GEMM_CHAIN 8u /* run the pinv chain as 24 batched tcgen05 GEMM launches (tf32 operands) instead of the
                                     single 4-CTA-cluster kernel (fp16 operands); kept for cross-checking */
 
@@ -173,7 +175,7 @@ int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n, float*
                float* scratch, uint32_t flags, void* stream);
 
 /* K3: TransLayer.norm (TransMIL.py:23,47) + the FRONT zero pad of
- * NystromAttention.forward.  h [B,S,512] -> xn [B,Sp,512] (rows < P zero). */
+ * NystromAttention.forward.  h [B,S,512] -> xn [B,Sp,512] (rows < P zero); xn is fp16 with TM_FLAG_F16_ACT. */
 int tm_ln_pad_fwd(const float* h, const float* gamma, const float* beta, int64_t B, int64_t S,
                   int64_t P, float* xn, uint32_t flags, void* stream);
 
@@ -211,8 +213,9 @@ int tm_nystrom_out_fwd(const float* q, const float* k_lm, const float* M, const 
 /* ---- fp16 tensor-core engine of the attention core (tcgen05 / TMEM / TMA) ----------
  * q16,k16,v16 [B,8,Sp,64], qlm16,klm16 [B,8,256,64], mt16 [B,8,64,256] are IEEE fp16 (device); all
  * contractions accumulate in fp32.  tm_transmil_fwd routes through these unless TM_FLAG_SIMT_ONLY. */
-/* K4 with fp16 head-major outputs (saturating round-to-nearest): xn [B,Sp,512] fp32 -> q16 (x 64^-0.5), k16, v16. */
-int tm_qkv16_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16,
+/* K4 with fp16 head-major outputs (saturating round-to-nearest): xn [B,Sp,512] -> q16 (x 64^-0.5), k16, v16.
+ * xn and qkv_w are fp32 (tf32 contraction) or, with TM_FLAG_F16_ACT, fp16 (fp16 contraction, fp32 accumulate). */
+int tm_qkv16_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16,
                  void* v16, uint32_t flags, void* stream);
 /* K5 on fp16 q/k: fp32 landmark means (fp32 accumulation) plus their fp16 copies. */
 int tm_landmarks16_fwd(const void* q16, const void* k16, int64_t B, int64_t Sp, int64_t l, float* q_lm,
@@ -223,15 +226,16 @@ int tm_zw16_fwd(const float* Z, const float* W3, int64_t B, float* M, void* mt16
 int tm_mt16_fwd(const float* M, void* mt16, int64_t B, void* stream);
 /* K9+K10+K11, same contract as tm_nystrom_out_fwd (nystrom-attention 0.0.11 forward: attn1, (attn1 @ Z) @ W3, res_conv). */
 int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const void* mt16, const void* v16,
-                          const float* conv_w, int64_t B, int64_t Sp, float* merged, uint32_t flags,
-                          void* stream);
+                          const float* conv_w, int64_t B, int64_t Sp, void* merged, uint32_t flags,
+                          void* stream);   /* merged: fp32 [B,Sp,512], or fp16 with TM_FLAG_F16_ACT */
 /* K8, same contract as tm_attn3v_fwd (attn3 @ v, flash style with lazy rescaling). */
 int64_t tm_attn3v_tc_scratch_floats(int64_t B, int64_t Sp);
 int tm_attn3v_tc_fwd(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp,
                      float* W3, float* scratch, uint32_t flags, void* stream);
 
 /* K12: to_out Linear(512,512)+bias on rows [P,Sp) of merged (the `[:, -S:]` slice),
- * plus the TransLayer residual (TransMIL.py:53).  h_out may alias h_in. */
+ * plus the TransLayer residual (TransMIL.py:53).  h_out may alias h_in.  With TM_FLAG_F16_ACT merged and out_w point
+ * at fp16 data (tensor-core engine); h_in / h_out / out_b stay fp32. */
 int tm_to_out_residual_fwd(const float* merged, const float* out_w, const float* out_b,
                            const float* h_in, int64_t B, int64_t S, int64_t P, float* h_out,
                            uint32_t flags, void* stream);
@@ -253,6 +257,9 @@ int tm_attn_rows_fwd(const float* q, const float* k, const float* q_lm, const fl
                      const float* Z, int64_t B, int64_t Sp, const int64_t* rows_host,
                      int64_t n_rows, float* out, float* scratch, void* stream);
 int64_t tm_attn_rows_scratch_floats(int64_t B, int64_t Sp, int64_t n_rows);
+
+/* dst[i] = half(src[i]) (round to nearest, saturating): fp16 operand copies of the GEMM weights. */
+int tm_cvt_f16(const float* src, void* dst, int64_t n, void* stream);
 
 /* dst[i] = tf32-rounded (round to nearest, ties away: cvt.rna.tf32.f32) src[i]; dst may alias src. */
 int tm_round_tf32(const float* src, float* dst, int64_t n, void* stream);

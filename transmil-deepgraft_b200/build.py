@@ -20,7 +20,7 @@ FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default",
     "-I", os.path.join(ROOT, "include"), "-I", CSRC,
-]
+] + os.environ.get("TM_EXTRA_NVCC_FLAGS", "").split()   # e.g. -DTM_TIMELINE (per-tile clock64 trace of attn3v_tc, debug only)
 
 
 def _sources():

@@ -13,6 +13,7 @@ TM_FLAG_SIMT_ONLY = 1
 TM_FLAG_KEEP_STAGES = 2
 TM_FLAG_TF32_OPERANDS = 4
 TM_FLAG_PINV_GEMM_CHAIN = 8
+TM_FLAG_F16_ACT = 16
 TM_FC1_SINGLE, TM_FC1_2048, TM_FC1_768 = 0, 1, 2
 
 _fp = C.c_void_p  # device/host float pointers travel as raw addresses
@@ -62,6 +63,7 @@ SIGNATURES = {
     "tm_stage_ptr": (C.c_int, [C.c_char_p, _i64, _i64, _PW, _u32, _fp, C.POINTER(C.c_void_p), C.POINTER(_i64)]),
     "tm_fc1_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
     "tm_ln_pad_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _fp, _u32, _fp]),
+    "tm_cvt_f16": (C.c_int, [_fp, _fp, _i64, _fp]),
     "tm_round_tf32": (C.c_int, [_fp, _fp, _i64, _fp]),
     "tm_qkv_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _u32, _fp]),
     "tm_landmarks_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _fp, _fp, _fp]),

@@ -77,6 +77,12 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+#ifdef TM_TIMELINE
+  __shared__ long long tl[2][12][6];
+#define TL(role, j, e) do { if ((j) < 12) tl[role][j][e] = clock64(); } while (0)
+#else
+#define TL(role, j, e) do { } while (0)
+#endif
 
   if (warp == 0) {
     if (lane == 0) {
@@ -115,6 +121,7 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
         for (int hf = 0; hf < 2; ++hf) {
           mbar_wait(&p_full[hf], j & 1);
           tc_fence_after();
+          if (hf == 0) TL(1, j, 0);
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             const uint64_t dV = umma_desc_mn_sw128(sV + ks * 2048, A3_K_BYTES, 1024);
@@ -127,6 +134,7 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
               tc_fence_after();
             }
             issue_s(j + 1, hf);
+            if (hf == 0) TL(1, j, 1);
           } else {
             umma_commit(&o_full[hf]);
           }
@@ -143,16 +151,23 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
     for (int j = 0; j < ntile; ++j) {
       mbar_wait(&s_full[hf], j & 1);
       tc_fence_after();
-      float tmax = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; c += 2) {
-        uint32_t r0[32], r1[32];
-        tmem_ld_32x32_nowait(tS + c * 32, r0);
-        tmem_ld_32x32_nowait(tS + c * 32 + 32, r1);
-        tmem_ld_wait();
+      if (warp == 2 && lane == 0) TL(0, j, 0);
+      // the 128 scores of this landmark row come to registers in ONE TMEM round trip and are used for both the max and
+      // the exponentials (the TMEM round trip, ~100 cycles per wait, is what the serial chain of a tile is made of)
+      uint32_t r0[32], r1[32], r2[32], r3[32];
+      tmem_ld_32x32_nowait(tS, r0);
+      tmem_ld_32x32_nowait(tS + 32, r1);
+      tmem_ld_32x32_nowait(tS + 64, r2);
+      tmem_ld_32x32_nowait(tS + 96, r3);
+      tmem_ld_wait();
+      if (warp == 2 && lane == 0) TL(0, j, 1);
+      float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int e = 0; e < 32; ++e) tmax = fmaxf(tmax, fmaxf(__uint_as_float(r0[e]), __uint_as_float(r1[e])));
+      for (int e = 0; e < 32; ++e) {
+        m4[0] = fmaxf(m4[0], __uint_as_float(r0[e])); m4[1] = fmaxf(m4[1], __uint_as_float(r1[e]));
+        m4[2] = fmaxf(m4[2], __uint_as_float(r2[e])); m4[3] = fmaxf(m4[3], __uint_as_float(r3[e]));
       }
+      const float tmax = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
       if (j == 0) {
         m_used = tmax;
       } else {
@@ -173,24 +188,28 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
         }
       }
       const float ml = m_used * A3_LOG2E;
-#pragma unroll 1
+      if (warp == 2 && lane == 0) TL(0, j, 2);
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
       for (int c = 0; c < 4; ++c) {
-        uint32_t r[32], pk[16];
-        tmem_ld_32x32_nowait(tS + c * 32, r);
-        tmem_ld_wait();
+        const uint32_t (&r)[32] = c == 0 ? r0 : (c == 1 ? r1 : (c == 2 ? r2 : r3));
+        uint32_t pk[16];
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           const float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * e]), A3_LOG2E, -ml));
           const float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * e + 1]), A3_LOG2E, -ml));
-          sum += p0 + p1;
+          s4[e & 3] += p0 + p1;
           pk[e] = pack_f16x2(p0, p1);
         }
         tmem_st_32x16(tS + c * 16, pk);
       }
+      sum += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+      if (warp == 2 && lane == 0) TL(0, j, 3);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[hf]);
+      if (warp == 2 && lane == 0) TL(0, j, 4);
     }
     if (ntile > 0) {
       mbar_wait(&o_full[hf], 0);
@@ -213,6 +232,14 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
   }
   tc_fence_before();
   __syncthreads();
+#ifdef TM_TIMELINE
+  if (threadIdx.x == 0 && blockIdx.x == 1 && blockIdx.y == 0) {
+    const long long t0 = tl[0][0][0];
+    for (int j = 0; j < 12 && j < ntile; ++j)
+      printf("tile %2d softmax: s_full %6lld ld %6lld max %6lld exp %6lld arrive %6lld | mma: p_full %6lld issued %6lld\n", j,
+             tl[0][j][0] - t0, tl[0][j][1] - t0, tl[0][j][2] - t0, tl[0][j][3] - t0, tl[0][j][4] - t0, tl[1][j][0] - t0, tl[1][j][1] - t0);
+  }
+#endif
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);

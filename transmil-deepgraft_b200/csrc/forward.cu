@@ -5,8 +5,6 @@
 #include "common.cuh"
 
 extern "C" int64_t tm_pinv_scratch_floats(int64_t B);
-extern "C" int tm_qkv16_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
-                            uint32_t flags, void* stream);
 
 namespace tmil {
 
@@ -202,15 +200,16 @@ extern "C" int tm_qkv_fwd(const float* xn, const float* qkv_w, int64_t B, int64_
   return gemm_auto(g, flags, (cudaStream_t)stream);
 }
 
-extern "C" int tm_qkv16_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
+extern "C" int tm_qkv16_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
                             uint32_t flags, void* stream) {
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0 && B * Sp < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_qkv16_fwd: bad shape B=%lld Sp=%lld", (long long)B, (long long)Sp);
   TM_CHECK_ARG(xn && qkv_w && q16 && k16 && v16, TM_ERR_BAD_ARGUMENT, "tm_qkv16_fwd: NULL pointer");
   GemmParams g;
   memset(&g, 0, sizeof(g));
-  g.A = xn; g.Bm = qkv_w; g.C = nullptr;
+  g.A = (const float*)xn; g.Bm = (const float*)qkv_w; g.C = nullptr;
   g.M = (int)(B * Sp); g.N = 3 * TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = 3 * TM_DIM;
   g.batch = 1; g.epi = EPI_QKV16; g.q = (float*)q16; g.k = (float*)k16; g.v = (float*)v16; g.Sp = (int)Sp;
+  g.f16_in = (flags & TM_FLAG_F16_ACT) ? 1 : 0;   // xn and qkv_w are fp16
   return gemm_auto(g, flags, (cudaStream_t)stream);
 }
 
@@ -224,6 +223,7 @@ extern "C" int tm_to_out_residual_fwd(const float* merged, const float* out_w, c
   // all Sp padded rows go through the GEMM (identity A rows, TMA friendly); the epilogue drops the P front-pad rows
   g.M = (int)(B * (S + P)); g.N = TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = TM_DIM;
   g.batch = 1; g.epi = EPI_BIAS_RESID;
+  g.f16_in = (flags & TM_FLAG_F16_ACT) ? 1 : 0;   // merged and out_w are fp16
   g.rows_per_bag = (int)(S + P); g.c_bag_rows = S; g.c_row_off = 0; g.c_skip = (int)P;
   return gemm_auto(g, flags, (cudaStream_t)stream);
 }
@@ -255,7 +255,7 @@ extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, i
   if (use_tc(flags)) {
     // tensor-core engine: every tensor that feeds a tf32 contraction is rounded by its producer; the (static) GEMM
     // weights are rounded here into the workspace.  The user's bag x is read as is (operand truncation by the MMA).
-    flags |= TM_FLAG_TF32_OPERANDS;
+    flags |= TM_FLAG_TF32_OPERANDS | TM_FLAG_F16_ACT;
     const int f0 = fc1_width(w);
     TM_PROPAGATE(tm_round_tf32(w->fc1_w0, ws + L.wr_fc1_0, (int64_t)(f0 ? f0 : TM_DIM) * w->in_features, st));
     wl.fc1_w0 = ws + L.wr_fc1_0;
@@ -263,10 +263,12 @@ extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, i
       TM_PROPAGATE(tm_round_tf32(w->fc1_w1, ws + L.wr_fc1_1, (int64_t)TM_DIM * f0, st));
       wl.fc1_w1 = ws + L.wr_fc1_1;
     }
+    // the layer GEMMs (to_qkv, to_out) run with fp16 operands: xn and merged are produced as fp16 by their kernels, the
+    // weights are converted here
     tm_layer_weights* lws[2] = {&wl.layer1, &wl.layer2};
     for (int l = 0; l < 2; ++l) {
-      TM_PROPAGATE(tm_round_tf32(lws[l]->qkv_w, ws + L.wr_qkv[l], (int64_t)3 * TM_DIM * TM_DIM, st));
-      TM_PROPAGATE(tm_round_tf32(lws[l]->out_w, ws + L.wr_out[l], (int64_t)TM_DIM * TM_DIM, st));
+      TM_PROPAGATE(tm_cvt_f16(lws[l]->qkv_w, ws + L.wr_qkv[l], (int64_t)3 * TM_DIM * TM_DIM, st));
+      TM_PROPAGATE(tm_cvt_f16(lws[l]->out_w, ws + L.wr_out[l], (int64_t)TM_DIM * TM_DIM, st));
       lws[l]->qkv_w = ws + L.wr_qkv[l];
       lws[l]->out_w = ws + L.wr_out[l];
     }
@@ -327,5 +329,6 @@ extern "C" int tm_stage_ptr(const char* name, int64_t B, int64_t n, const tm_wei
 // 1 when the named stage buffer holds fp16 under `flags` on this device (q, k, v of the tensor-core engine).
 extern "C" int tm_stage_is_f16(const char* name, uint32_t flags) {
   if (!name || !use_tc(flags)) return 0;
-  return (strcmp(name, "q") == 0 || strcmp(name, "k") == 0 || strcmp(name, "v") == 0) ? 1 : 0;
+  return (strcmp(name, "q") == 0 || strcmp(name, "k") == 0 || strcmp(name, "v") == 0 || strcmp(name, "xn") == 0 ||
+          strcmp(name, "merged") == 0) ? 1 : 0;
 }

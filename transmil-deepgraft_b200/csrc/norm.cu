@@ -1,13 +1,15 @@
 // Row-wise kernels: LayerNorm (+ front zero pad), in-place LayerNorm for the fc1
 // stems, and the cls-row head (final LayerNorm + _fc).  All HBM-bound: one warp
 // per row, 128-bit loads, row kept in registers between the two passes.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
 namespace tmil {
 
 // One warp normalises one row of width W (multiple of 128, <= 1024).
-template <int W, bool ROUND = false>
+template <int W, int OUT = 0>   // OUT 0: fp32, 1: fp32 rounded to tf32, 2: fp16 (dst then points at __half)
 __device__ __forceinline__ void warp_layernorm_row(const float* src, float* dst,
                                                    const float* __restrict__ gamma, const float* __restrict__ beta, int lane) {
   constexpr int V = W / 128;  // float4 per lane
@@ -36,13 +38,14 @@ __device__ __forceinline__ void warp_layernorm_row(const float* src, float* dst,
     o.y = (x[i].y - mean) * rstd * g.y + b.y;
     o.z = (x[i].z - mean) * rstd * g.z + b.z;
     o.w = (x[i].w - mean) * rstd * g.w + b.w;
-    if (ROUND) { o.x = round_tf32(o.x); o.y = round_tf32(o.y); o.z = round_tf32(o.z); o.w = round_tf32(o.w); }
-    *reinterpret_cast<float4*>(dst + c) = o;
+    if (OUT == 1) { o.x = round_tf32(o.x); o.y = round_tf32(o.y); o.z = round_tf32(o.z); o.w = round_tf32(o.w); }
+    if (OUT == 2) *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(dst) + c) = make_uint2(pack_f16x2(o.x, o.y), pack_f16x2(o.z, o.w));
+    else *reinterpret_cast<float4*>(dst + c) = o;
   }
 }
 
 // xn[b, t] = t < P ? 0 : LN(h[b, t - P])
-template <bool ROUND>
+template <int OUT>
 __global__ void __launch_bounds__(256) ln_pad_kernel(const float* __restrict__ h, const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, long long rows, int S, int Sp, int P,
                                                      float* __restrict__ xn) {
@@ -51,17 +54,22 @@ __global__ void __launch_bounds__(256) ln_pad_kernel(const float* __restrict__ h
   if (row >= rows) return;
   const long long b = row / Sp;
   const int t = (int)(row - b * Sp);
-  float* dst = xn + row * TM_DIM;
+  float* dst = OUT == 2 ? reinterpret_cast<float*>(reinterpret_cast<__half*>(xn) + row * TM_DIM) : xn + row * TM_DIM;
   if (t < P) {
+    if (OUT == 2) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(dst + (i * 32 + lane) * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = 0; i < 2; ++i) *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(dst) + (i * 32 + lane) * 8) = make_uint4(0u, 0u, 0u, 0u);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(dst + (i * 32 + lane) * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     return;
   }
-  warp_layernorm_row<TM_DIM, ROUND>(h + (b * S + (t - P)) * TM_DIM, dst, gamma, beta, lane);
+  warp_layernorm_row<TM_DIM, OUT>(h + (b * S + (t - P)) * TM_DIM, dst, gamma, beta, lane);
 }
 
 // In-place LayerNorm over mapped rows: row r -> (r / rpb) * bag_rows + off + r % rpb.
-template <int W, bool ROUND>
+template <int W, int ROUND>
 __global__ void __launch_bounds__(256) ln_inplace_kernel(float* __restrict__ x, const float* __restrict__ gamma,
                                                          const float* __restrict__ beta, long long rows, int rpb,
                                                          long long bag_rows, int off) {
@@ -82,15 +90,15 @@ int ln_inplace(float* x, const float* gamma, const float* beta, long long rows, 
   if (rows <= 0) return TM_OK;
   unsigned grid = (unsigned)ceil_div(rows, 8);
   if (width == 512 && !round)
-    ln_inplace_kernel<512, false><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+    ln_inplace_kernel<512, 0><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
   else if (width == 768 && !round)
-    ln_inplace_kernel<768, false><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+    ln_inplace_kernel<768, 0><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
   else if (width == 1024 && !round)
-    ln_inplace_kernel<1024, false><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+    ln_inplace_kernel<1024, 0><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
   else if (width == 768 && round)
-    ln_inplace_kernel<768, true><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+    ln_inplace_kernel<768, 1><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
   else if (width == 1024 && round)
-    ln_inplace_kernel<1024, true><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
+    ln_inplace_kernel<1024, 1><<<grid, 256, 0, st>>>(x, gamma, beta, rows, rpb, bag_rows, off);
   else {
     set_error("ln_inplace: unsupported width %d", width);
     return TM_ERR_BAD_SHAPE;
@@ -103,6 +111,13 @@ __global__ void __launch_bounds__(256) round_tf32_kernel(const float* __restrict
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
     float4 v = reinterpret_cast<const float4*>(src)[i];
     reinterpret_cast<float4*>(dst)[i] = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+  }
+}
+
+__global__ void __launch_bounds__(256) cvt_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, long long n4) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    const float4 v = reinterpret_cast<const float4*>(src)[i];
+    reinterpret_cast<uint2*>(dst)[i] = make_uint2(pack_f16x2(v.x, v.y), pack_f16x2(v.z, v.w));
   }
 }
 
@@ -144,6 +159,17 @@ extern "C" int tm_round_tf32(const float* src, float* dst, int64_t n, void* stre
   return TM_OK;
 }
 
+extern "C" int tm_cvt_f16(const float* src, void* dst, int64_t n, void* stream) {
+  TM_CHECK_ARG(src && dst && n >= 0 && n % 4 == 0 && tmil::aligned16(src) && (reinterpret_cast<uintptr_t>(dst) & 7u) == 0, TM_ERR_BAD_ALIGNMENT,
+               "tm_cvt_f16: n must be a multiple of 4, src 16-byte and dst 8-byte aligned");
+  if (n == 0) return TM_OK;
+  long long blocks = tmil::ceil_div(n / 4, 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  tmil::cvt_f16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__half*)dst, n / 4);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
 extern "C" int tm_ln_pad_fwd(const float* h, const float* gamma, const float* beta, int64_t B, int64_t S, int64_t P,
                              float* xn, uint32_t flags, void* stream) {
   TM_CHECK_ARG(B > 0 && S > 0 && P >= 0 && (S + P) % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE,
@@ -151,10 +177,14 @@ extern "C" int tm_ln_pad_fwd(const float* h, const float* gamma, const float* be
   TM_CHECK_ARG(tmil::aligned16(h) && tmil::aligned16(xn) && tmil::aligned16(gamma) && tmil::aligned16(beta), TM_ERR_BAD_ALIGNMENT,
                "tm_ln_pad_fwd: pointers must be 16-byte aligned");
   const long long rows = (long long)B * (S + P);
-  if (flags & TM_FLAG_TF32_OPERANDS)
-    tmil::ln_pad_kernel<true><<<(unsigned)tmil::ceil_div(rows, 8), 256, 0, (cudaStream_t)stream>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+  const unsigned grid = (unsigned)tmil::ceil_div(rows, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (flags & TM_FLAG_F16_ACT)
+    tmil::ln_pad_kernel<2><<<grid, 256, 0, st>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+  else if (flags & TM_FLAG_TF32_OPERANDS)
+    tmil::ln_pad_kernel<1><<<grid, 256, 0, st>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
   else
-    tmil::ln_pad_kernel<false><<<(unsigned)tmil::ceil_div(rows, 8), 256, 0, (cudaStream_t)stream>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+    tmil::ln_pad_kernel<0><<<grid, 256, 0, st>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -27,32 +27,34 @@ constexpr int NT_V_BYTES = NT_HALO_ROWS * 128;
 constexpr int NT_OFF_KLM = 0;
 constexpr int NT_OFF_MT = NT_OFF_KLM + NT_KLM_BYTES;
 constexpr int NT_OFF_T = NT_OFF_MT + NT_MT_BYTES;
-constexpr int NT_OFF_Q = NT_OFF_T + NT_T_BYTES;                 // 2 slots of (Q, Vhalo)
+constexpr int NT_STAGES = 3;                                     // smem stages of (Q, Vhalo): a stage is held for the whole
+                                                                 // chain of its tile, so 3 keep the HBM latency off the chain
+constexpr int NT_OFF_Q = NT_OFF_T + NT_T_BYTES;
 constexpr int NT_SLOT_BYTES = NT_Q_BYTES + NT_V_BYTES;
-constexpr int NT_OFF_BAR = NT_OFF_Q + 2 * NT_SLOT_BYTES;
+constexpr int NT_OFF_BAR = NT_OFF_Q + NT_STAGES * NT_SLOT_BYTES;
 constexpr size_t NT_SMEM = 1024 + NT_OFF_BAR + 256;
 constexpr int NT_THREADS = 320;
 constexpr float NT_LOG2E = 1.4426950408889634f;
 
-template <bool ROUND>
+template <int OUT>   // 0: fp32, 1: fp32 rounded to tf32, 2: fp16 (operand of the fp16 to_out GEMM)
 __global__ void __launch_bounds__(NT_THREADS, 1)
 nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmV,
                       const __grid_constant__ CUtensorMap tmKlm, const __grid_constant__ CUtensorMap tmMT,
-                      const float* __restrict__ conv_w, int Sp, int tiles_per_chunk, int tiles_per_bh, float* __restrict__ merged) {
+                      const float* __restrict__ conv_w, int Sp, int tiles_per_chunk, int tiles_per_bh, void* __restrict__ merged_v) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sKlm = smem + NT_OFF_KLM;
   uint8_t* sMT = smem + NT_OFF_MT;
   uint8_t* sT = smem + NT_OFF_T;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NT_OFF_BAR);
-  uint64_t* q_full = bars;          // [2] TMA -> MMA      (Q tile + V halo landed)
-  uint64_t* q_empty = bars + 2;     // [2] MMA -> TMA      (MMA1 and MMA3 of the tile retired)
-  uint64_t* s_full = bars + 4;      // [2] MMA -> softmax  (S in TMEM)
-  uint64_t* p_full = bars + 6;      // [2] softmax -> MMA  (P in TMEM), 4 arrivals
-  uint64_t* o_full = bars + 8;      // [2] MMA -> epilogue (O and O2 in TMEM)
-  uint64_t* t_empty = bars + 10;    // [2] epilogue -> MMA (TMEM slot drained), 4 arrivals
-  uint64_t* c_full = bars + 12;     // K_lm and M^T landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint64_t* q_full = bars;          // [3] TMA -> MMA      (Q tile + V halo landed)
+  uint64_t* q_empty = bars + 3;     // [3] MMA -> TMA      (MMA1 and MMA3 of the tile retired)
+  uint64_t* s_full = bars + 6;      // [2] MMA -> softmax  (S in TMEM)
+  uint64_t* p_full = bars + 8;      // [2] softmax -> MMA  (P in TMEM), 4 arrivals
+  uint64_t* o_full = bars + 10;     // [2] MMA -> epilogue (O and O2 in TMEM)
+  uint64_t* t_empty = bars + 12;    // [2] epilogue -> MMA (TMEM slot drained), 4 arrivals
+  uint64_t* c_full = bars + 14;     // K_lm and M^T landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bh = blockIdx.y;
@@ -64,9 +66,9 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmKlm); tma_prefetch_desc(&tmMT);
   }
   if (warp == 1 && lane == 0) {
+    for (int i = 0; i < NT_STAGES; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); mbar_init(&s_full[i], 1);
-      mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); mbar_init(&t_empty[i], 4);
+      mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); mbar_init(&t_empty[i], 4);
     }
     mbar_init(c_full, 1);
     fence_barrier_init();
@@ -97,6 +99,12 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+#ifdef TM_TIMELINE
+  __shared__ long long tl[2][12][6];
+#define TL(role, j, e) do { if ((j) < 12) tl[role][j][e] = clock64(); } while (0)
+#else
+#define TL(role, j, e) do { } while (0)
+#endif
 
   if (warp == 0) {
     if (lane == 0) {
@@ -105,13 +113,13 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 #pragma unroll
       for (int kb = 0; kb < 4; ++kb) tma_load_3d(sMT + kb * 8192, &tmMT, c_full, kb * 64, 0, bh);
       for (int i = 0; i < ntile; ++i) {
-        const int s = i & 1;
-        const uint32_t par = (i >> 1) & 1;
-        mbar_wait(&q_empty[s], par ^ 1);
-        uint8_t* sQ = smem + NT_OFF_Q + s * NT_SLOT_BYTES;
-        mbar_arrive_expect_tx(&q_full[s], NT_SLOT_BYTES);
-        tma_load_3d(sQ, &tmQ, &q_full[s], 0, (tile0 + i) * NT_TOK, bh);
-        tma_load_3d(sQ + NT_Q_BYTES, &tmV, &q_full[s], 0, (tile0 + i) * NT_TOK - 16, bh);
+        const int st = i % NT_STAGES;
+        const uint32_t spar = (i / NT_STAGES) & 1;
+        mbar_wait(&q_empty[st], spar ^ 1);
+        uint8_t* sQ = smem + NT_OFF_Q + st * NT_SLOT_BYTES;
+        mbar_arrive_expect_tx(&q_full[st], NT_SLOT_BYTES);
+        tma_load_3d(sQ, &tmQ, &q_full[st], 0, (tile0 + i) * NT_TOK, bh);
+        tma_load_3d(sQ + NT_Q_BYTES, &tmV, &q_full[st], 0, (tile0 + i) * NT_TOK - 16, bh);
       }
     }
   } else if (warp == 1) {
@@ -124,13 +132,16 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       auto front = [&](int i) {
         const int s = i & 1;
         const uint32_t par = (i >> 1) & 1;
-        mbar_wait(&q_full[s], par);
+        const int st = i % NT_STAGES;
+        mbar_wait(&q_full[st], (i / NT_STAGES) & 1);
+        TL(1, i, 0);
         mbar_wait(&t_empty[s], par ^ 1);
         tc_fence_after();
-        const uint64_t dQ = umma_desc_k_sw128(smem_u32(smem + NT_OFF_Q + s * NT_SLOT_BYTES));
+        const uint64_t dQ = umma_desc_k_sw128(smem_u32(smem + NT_OFF_Q + st * NT_SLOT_BYTES));
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_base + s * 256, dQ + 2 * k, dK + 2 * k, idesc_s, k > 0 ? 1u : 0u);
         umma_commit(&s_full[s]);
+        TL(1, i, 1);
       };
       if (ntile > 0) front(0);
       for (int i = 0; i < ntile; ++i) {
@@ -138,6 +149,7 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         const int s = i & 1;
         const uint32_t par = (i >> 1) & 1;
         mbar_wait(&p_full[s], par);
+        TL(1, i, 2);
         tc_fence_after();
         const uint32_t slot = tmem_base + s * 256;
 #pragma unroll
@@ -145,81 +157,120 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           const uint64_t dM = umma_desc_k_sw128(smem_u32(sMT + (ks >> 2) * 8192)) + 2 * (ks & 3);
           umma_f16_ts(slot + 128, slot + 8 * ks, dM, idesc_o, ks > 0 ? 1u : 0u);
         }
-        const uint32_t sV = smem_u32(smem + NT_OFF_Q + s * NT_SLOT_BYTES + NT_Q_BYTES);
+        const uint32_t sV = smem_u32(smem + NT_OFF_Q + (i % NT_STAGES) * NT_SLOT_BYTES + NT_Q_BYTES);
 #pragma unroll
         for (int ks = 0; ks < 10; ++ks) {
           const uint64_t dT = umma_desc_k_sw128(smem_u32(sT + (ks >> 2) * 16384)) + 2 * (ks & 3);
           const uint64_t dV = umma_desc_mn_sw128(sV + ks * 2048, NT_V_BYTES, 1024);
           umma_f16_ss(slot + 192, dT, dV, idesc_c, ks > 0 ? 1u : 0u);
         }
-        umma_commit(&q_empty[s]);
+        umma_commit(&q_empty[i % NT_STAGES]);
         umma_commit(&o_full[s]);
+        TL(1, i, 3);
       }
     }
   } else {
     const int g = (warp - 2) >> 2;      // softmax group = TMEM slot
     const int qd = warp & 3;            // TMEM lane quarter this warp may access
     const uint32_t slot = tmem_base + ((uint32_t)(qd * 32) << 16) + g * 256;
-    float* out_row0 = merged + ((long long)b * Sp + qd * 32 + lane) * TM_DIM + h * TM_DHEAD;
+    const long long out_row0 = ((long long)b * Sp + qd * 32 + lane) * TM_DIM + h * TM_DHEAD;   // element offset into merged
     for (int i = g; i < ntile; i += 2) {
       const uint32_t par = (i >> 1) & 1;
       mbar_wait(&s_full[g], par);
+      if (qd == 2 && lane == 0) TL(0, i, 0);
       tc_fence_after();
-      float mx = -INFINITY;
+      // pass 1: row max over the 256 landmarks.  128 columns per TMEM round trip, four independent max chains.
+      float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
-      for (int c = 0; c < 8; c += 2) {
-        uint32_t r0[32], r1[32];
+      for (int c = 0; c < 8; c += 4) {
+        uint32_t r0[32], r1[32], r2[32], r3[32];
         tmem_ld_32x32_nowait(slot + c * 32, r0);
         tmem_ld_32x32_nowait(slot + c * 32 + 32, r1);
+        tmem_ld_32x32_nowait(slot + c * 32 + 64, r2);
+        tmem_ld_32x32_nowait(slot + c * 32 + 96, r3);
         tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 32; ++e) mx = fmaxf(mx, fmaxf(__uint_as_float(r0[e]), __uint_as_float(r1[e])));
+        for (int e = 0; e < 32; ++e) {
+          m4[0] = fmaxf(m4[0], __uint_as_float(r0[e])); m4[1] = fmaxf(m4[1], __uint_as_float(r1[e]));
+          m4[2] = fmaxf(m4[2], __uint_as_float(r2[e])); m4[3] = fmaxf(m4[3], __uint_as_float(r3[e]));
+        }
       }
+      const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      if (qd == 2 && lane == 0) TL(0, i, 1);
       const float ml = mx * NT_LOG2E;
-      float sum = 0.f;
-#pragma unroll 1
+      // pass 2: P = exp(S - max) as packed fp16, written over the consumed S columns; the next chunk's TMEM load is in
+      // flight while the current one is exponentiated; four independent row-sum chains.
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};
+      uint32_t ra[32], rb[32];
+      tmem_ld_32x32_nowait(slot, ra);
+      tmem_ld_wait();
+#pragma unroll
       for (int c = 0; c < 8; ++c) {
-        uint32_t r[32], pk[16];
-        tmem_ld_32x32_nowait(slot + c * 32, r);
-        tmem_ld_wait();
+        uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+        uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+        if (c + 1 < 8) tmem_ld_32x32_nowait(slot + (c + 1) * 32, nxt);
+        uint32_t pk[16];
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
-          const float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * e]), NT_LOG2E, -ml));
-          const float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * e + 1]), NT_LOG2E, -ml));
-          sum += p0 + p1;
+          const float p0 = ex2_approx(fmaf(__uint_as_float(cur[2 * e]), NT_LOG2E, -ml));
+          const float p1 = ex2_approx(fmaf(__uint_as_float(cur[2 * e + 1]), NT_LOG2E, -ml));
+          s4[e & 3] += p0 + p1;
           pk[e] = pack_f16x2(p0, p1);
         }
-        tmem_st_32x16(slot + c * 16, pk);   // P overwrites S columns that were already consumed
+        if (c + 1 < 8) tmem_ld_wait();      // chunk c+1 is in registers before chunk c's columns... 
+        tmem_st_32x16(slot + c * 16, pk);   // ...P overwrites S columns [16c,16c+16), all read by now (16c+16 <= 32(c+1))
       }
+      const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[g]);
+      if (qd == 2 && lane == 0) TL(0, i, 2);
 
       mbar_wait(&o_full[g], par);
+      if (qd == 2 && lane == 0) TL(0, i, 3);
       tc_fence_after();
       const float inv = 1.0f / sum;
-      float* orow = out_row0 + (long long)(tile0 + i) * NT_TOK * TM_DIM;
-#pragma unroll
-      for (int hf = 0; hf < 2; ++hf) {
-        uint32_t o[32], c2[32];
-        tmem_ld_32x32_nowait(slot + 128 + hf * 32, o);
-        tmem_ld_32x32_nowait(slot + 192 + hf * 32, c2);
+      const long long orow = out_row0 + (long long)(tile0 + i) * NT_TOK * TM_DIM;
+      {
+        uint32_t oa[32], ob[32], ca[32], cb[32];   // O and the conv accumulator, one TMEM round trip
+        tmem_ld_32x32_nowait(slot + 128, oa);
+        tmem_ld_32x32_nowait(slot + 160, ob);
+        tmem_ld_32x32_nowait(slot + 192, ca);
+        tmem_ld_32x32_nowait(slot + 224, cb);
         tmem_ld_wait();
-        if (hf == 1) {   // both halves are in registers: hand the TMEM slot back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&t_empty[g]);
-        }
+        tc_fence_before();   // everything is in registers: hand the TMEM slot back to the MMA warp
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[g]);
+        if (qd == 2 && lane == 0) TL(0, i, 4);
 #pragma unroll
-        for (int e = 0; e < 32; e += 4) {
-          float4 r4;
-          r4.x = fmaf(__uint_as_float(o[e]), inv, __uint_as_float(c2[e]));
-          r4.y = fmaf(__uint_as_float(o[e + 1]), inv, __uint_as_float(c2[e + 1]));
-          r4.z = fmaf(__uint_as_float(o[e + 2]), inv, __uint_as_float(c2[e + 2]));
-          r4.w = fmaf(__uint_as_float(o[e + 3]), inv, __uint_as_float(c2[e + 3]));
-          if (ROUND) { r4.x = round_tf32(r4.x); r4.y = round_tf32(r4.y); r4.z = round_tf32(r4.z); r4.w = round_tf32(r4.w); }
-          *reinterpret_cast<float4*>(orow + hf * 32 + e) = r4;
+        for (int hf = 0; hf < 2; ++hf) {
+          const uint32_t (&o)[32] = hf ? ob : oa;
+          const uint32_t (&c2)[32] = hf ? cb : ca;
+          if (OUT == 2) {
+            __half* op = reinterpret_cast<__half*>(merged_v) + orow + hf * 32;
+#pragma unroll
+            for (int e = 0; e < 32; e += 8) {
+              uint4 u;
+              u.x = pack_f16x2(fmaf(__uint_as_float(o[e]), inv, __uint_as_float(c2[e])), fmaf(__uint_as_float(o[e + 1]), inv, __uint_as_float(c2[e + 1])));
+              u.y = pack_f16x2(fmaf(__uint_as_float(o[e + 2]), inv, __uint_as_float(c2[e + 2])), fmaf(__uint_as_float(o[e + 3]), inv, __uint_as_float(c2[e + 3])));
+              u.z = pack_f16x2(fmaf(__uint_as_float(o[e + 4]), inv, __uint_as_float(c2[e + 4])), fmaf(__uint_as_float(o[e + 5]), inv, __uint_as_float(c2[e + 5])));
+              u.w = pack_f16x2(fmaf(__uint_as_float(o[e + 6]), inv, __uint_as_float(c2[e + 6])), fmaf(__uint_as_float(o[e + 7]), inv, __uint_as_float(c2[e + 7])));
+              *reinterpret_cast<uint4*>(op + e) = u;
+            }
+          } else {
+            float* op = reinterpret_cast<float*>(merged_v) + orow + hf * 32;
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              float4 r4;
+              r4.x = fmaf(__uint_as_float(o[e]), inv, __uint_as_float(c2[e]));
+              r4.y = fmaf(__uint_as_float(o[e + 1]), inv, __uint_as_float(c2[e + 1]));
+              r4.z = fmaf(__uint_as_float(o[e + 2]), inv, __uint_as_float(c2[e + 2]));
+              r4.w = fmaf(__uint_as_float(o[e + 3]), inv, __uint_as_float(c2[e + 3]));
+              if (OUT == 1) { r4.x = round_tf32(r4.x); r4.y = round_tf32(r4.y); r4.z = round_tf32(r4.z); r4.w = round_tf32(r4.w); }
+              *reinterpret_cast<float4*>(op + e) = r4;
+            }
+          }
         }
       }
     }
@@ -227,6 +278,15 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
+#ifdef TM_TIMELINE
+  if (threadIdx.x == 64 && blockIdx.x == 1 && blockIdx.y == 0) {
+    const long long t0 = tl[0][0][0];
+    for (int j = 0; j < 12 && j < ntile; ++j)
+      printf("tile %2d grp%d: s_full %6lld max %6lld p_arrive %6lld o_full %6lld done %6lld | mma: q_full %6lld front %6lld p_full %6lld back %6lld\n", j, j & 1,
+             tl[0][j][0] - t0, tl[0][j][1] - t0, tl[0][j][2] - t0, tl[0][j][3] - t0, tl[0][j][4] - t0, tl[1][j][0] - t0, tl[1][j][1] - t0,
+             tl[1][j][2] - t0, tl[1][j][3] - t0);
+  }
+#endif
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
@@ -277,7 +337,15 @@ __global__ void __launch_bounds__(256) zw16_kernel(const float* __restrict__ Z, 
 }
 
 int attn_chunks(int64_t nbh, int64_t tiles_per_bh) {
-  int64_t c = (148 + nbh / 2) / nbh;   // about one CTA per SM in total
+  // one CTA per SM (512 TMEM columns each): never more CTAs than SMs unless the heads alone exceed them -- 152 CTAs on
+  // 148 SMs is a second wave that doubles the kernel time
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+      sms = 148;
+  }
+  int64_t c = sms / nbh;
   if (c < 1) c = 1;
   if (c > tiles_per_bh) c = tiles_per_bh;
   return (int)c;
@@ -302,7 +370,7 @@ extern "C" int tm_zw16_fwd(const float* Z, const float* W3, int64_t B, float* M,
 }
 
 extern "C" int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const void* mt16, const void* v16, const float* conv_w,
-                                     int64_t B, int64_t Sp, float* merged, uint32_t flags, void* stream) {
+                                     int64_t B, int64_t Sp, void* merged, uint32_t flags, void* stream) {
   using namespace tmil;
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE, "tm_nystrom_out_tc_fwd: Sp must be a multiple of 256 (Sp=%lld)", (long long)Sp);
   TM_CHECK_ARG(q16 && klm16 && mt16 && v16 && conv_w && merged, TM_ERR_BAD_ARGUMENT, "tm_nystrom_out_tc_fwd: NULL pointer");
@@ -315,8 +383,9 @@ extern "C" int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const v
   TM_PROPAGATE(make_tmap_3d_f16(&tmM, mt16, nbh, TM_DHEAD, TM_LANDMARKS, TM_DHEAD * TM_LANDMARKS, TM_LANDMARKS, TM_DHEAD, 64));
   static bool attr_done = false;
   if (!attr_done) {
-    TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
-    TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
+    TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
+    TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
+    TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
     attr_done = true;
   }
   const int tiles_per_bh = (int)(Sp / NT_TOK);
@@ -324,10 +393,12 @@ extern "C" int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const v
   const int tpc = (int)ceil_div(tiles_per_bh, chunks);
   const int used = (int)ceil_div(tiles_per_bh, tpc);
   dim3 grid((unsigned)used, (unsigned)nbh);
-  if (flags & TM_FLAG_TF32_OPERANDS)
-    nystrom_out_tc_kernel<true><<<grid, NT_THREADS, NT_SMEM, (cudaStream_t)stream>>>(tmQ, tmV, tmK, tmM, conv_w, (int)Sp, tpc, tiles_per_bh, merged);
+  if (flags & TM_FLAG_F16_ACT)
+    nystrom_out_tc_kernel<2><<<grid, NT_THREADS, NT_SMEM, (cudaStream_t)stream>>>(tmQ, tmV, tmK, tmM, conv_w, (int)Sp, tpc, tiles_per_bh, merged);
+  else if (flags & TM_FLAG_TF32_OPERANDS)
+    nystrom_out_tc_kernel<1><<<grid, NT_THREADS, NT_SMEM, (cudaStream_t)stream>>>(tmQ, tmV, tmK, tmM, conv_w, (int)Sp, tpc, tiles_per_bh, merged);
   else
-    nystrom_out_tc_kernel<false><<<grid, NT_THREADS, NT_SMEM, (cudaStream_t)stream>>>(tmQ, tmV, tmK, tmM, conv_w, (int)Sp, tpc, tiles_per_bh, merged);
+    nystrom_out_tc_kernel<0><<<grid, NT_THREADS, NT_SMEM, (cudaStream_t)stream>>>(tmQ, tmV, tmK, tmM, conv_w, (int)Sp, tpc, tiles_per_bh, merged);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
