@@ -97,17 +97,144 @@ constexpr int TC_A_BYTES = TC_BM * 128;         // 16 KB per stage
 constexpr int TC_STG_LD = 36;                   // floats per staged row (32 + 4: conflict-free 128-bit access)
 constexpr int TC_STG_BYTES = 32 * TC_STG_LD * 4;
 constexpr int TC_THREADS = 192;
+constexpr int TC_OUT_BYTES = 2 * 16384;         // epilogue staging: two [128 rows][128 bytes] SWIZZLE_128B boxes (TMA store) or the
+                                                // four per-warp transpose tiles of the generic epilogue
+static_assert(4 * TC_STG_BYTES <= TC_OUT_BYTES, "generic staging must fit the output staging region");
+
+// Output tensor maps of the TMA-store epilogues (see epilogue_fast)
+struct TcOutMaps { CUtensorMap m[3]; };
+enum TcFast : int { FAST_NONE = 0, FAST_QKV16 = 1, FAST_BIAS_RESID = 2, FAST_BIAS_GELU = 3 };
 
 template <int BN> struct TcCfg {
   static constexpr int B_BYTES = BN * 128;
   static constexpr int STAGES = BN == 256 ? 4 : 6;
-  static constexpr size_t SMEM = 1024 + STAGES * (TC_A_BYTES + B_BYTES) + 4 * TC_STG_BYTES + 256;
+  static constexpr size_t SMEM = 1024 + STAGES * (TC_A_BYTES + B_BYTES) + TC_OUT_BYTES + 256;
 };
 
-template <int BN, bool F16>
+// ---- TMA-store epilogues ---------------------------------------------------------------------------------------
+// The accumulator layout (thread = output row, 32 consecutive columns per tcgen05.ld) is finished in registers, written to
+// a [128 rows][128 bytes] SWIZZLE_128B box in smem (conflict-free: the 16-byte chunk index is XOR-ed with the row) and
+// stored with ONE cp.async.bulk.tensor per box: full-line writes, no per-element address arithmetic, and the row maps of
+// the path become tensor-map coordinates -- rows with a negative / out-of-extent coordinate are simply not written
+// (front-pad rows of to_out, rows past the bag in fc1).  Two boxes rotate so the store of box k overlaps the math of k+1.
+//   FAST_QKV16       q/k/v head-major fp16 boxes [128 tokens][64 d]         (two 32-column chunks per box)
+//   FAST_BIAS_RESID  h_out = h_in + acc + bias, fp32 boxes [128][32], row coordinate i - P
+//   FAST_BIAS_GELU   C = gelu(acc + bias), fp32 boxes [128][32], plus the duplicate-pad rows as a second store
+template <int BN, int FAST>
+__device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMaps& om, uint32_t tmem_base, uint64_t* tfull,
+                                              uint64_t* tempty, uint8_t* obuf, int n_tiles, int total) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = warp & 3;
+  const int rt = q * 32 + lane;                 // row inside the 128-row tile = TMEM lane
+  const bool leader = threadIdx.x == 64;        // warp 2, lane 0 issues the stores
+  uint32_t unit = 0;                            // boxes written so far (buffer = unit & 1)
+  int it = 0;
+  for (int tile = blockIdx.x; tile < total; tile += gridDim.x, ++it) {
+    const int m_blk = tile / n_tiles, n_blk = tile - m_blk * n_tiles;
+    const int as = it & 1;
+    const uint32_t aphase = (it >> 1) & 1;
+    const int r0 = m_blk * TC_BM;
+    int bag = 0, i0 = r0;
+    if (p.rows_per_bag > 0) { bag = r0 / p.rows_per_bag; i0 = r0 - bag * p.rows_per_bag; }
+    if (FAST == FAST_QKV16) { bag = r0 / p.Sp; i0 = r0 - bag * p.Sp; }
+    // FAST_BIAS_RESID: the first c_skip rows of a bag (front pad) are not stored.  TMA stores take no negative coordinates
+    // here, so a tile of pad rows only is skipped and the tile that straddles the boundary stores a shorter box (map m[1],
+    // 128 - shift rows) whose rows were written `shift` rows higher in smem.
+    const int shift = (FAST == FAST_BIAS_RESID && i0 < p.c_skip) ? p.c_skip - i0 : 0;
+    const float* lrow = nullptr;                // FAST_BIAS_RESID: this thread's residual row (nullptr: not stored)
+    if (FAST == FAST_BIAS_RESID) {
+      const int i = i0 + rt;
+      if (r0 + rt < p.M && i >= p.c_skip) lrow = p.L + ((long long)bag * p.c_bag_rows + p.c_row_off + (i - p.c_skip)) * p.ldl;
+    }
+    mbar_wait(&tfull[as], aphase);
+    tc_fence_after();
+    const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+#pragma unroll 1
+    for (int chunk = 0; chunk < BN / 32; ++chunk) {
+      float v[32];
+      tmem_ld_32x32(t_row + chunk * 32, v);
+      if (chunk == BN / 32 - 1) {   // accumulator fully read: hand the TMEM buffer back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[as]);
+      }
+      const int c0 = n_blk * BN + chunk * 32;
+      if (c0 >= p.N || shift >= TC_BM) continue;      // uniform over the CTA
+      const bool first = FAST == FAST_QKV16 ? (chunk & 1) == 0 : true;
+      const bool last = FAST == FAST_QKV16 ? (chunk & 1) == 1 : true;
+      if (FAST == FAST_BIAS_RESID) {
+        float4 l[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) l[j] = lrow != nullptr ? *reinterpret_cast<const float4*>(lrow + c0 + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
+          v[4 * j] = l[j].x + (v[4 * j] + b.x); v[4 * j + 1] = l[j].y + (v[4 * j + 1] + b.y);
+          v[4 * j + 2] = l[j].z + (v[4 * j + 2] + b.z); v[4 * j + 3] = l[j].w + (v[4 * j + 3] + b.w);
+        }
+      } else if (FAST == FAST_BIAS_GELU) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
+          v[4 * j] = gelu_erf(v[4 * j] + b.x); v[4 * j + 1] = gelu_erf(v[4 * j + 1] + b.y);
+          v[4 * j + 2] = gelu_erf(v[4 * j + 2] + b.z); v[4 * j + 3] = gelu_erf(v[4 * j + 3] + b.w);
+        }
+        if (p.round_out) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] = round_tf32(v[e]);
+        }
+      }
+      if (first) {                   // the box written two units ago must have been read out by its TMA store
+        if (leader) tma_store_wait_read<1>();
+        named_bar_sync(1, 128);
+      }
+      const int srow = rt - shift;   // row of the smem box
+      uint8_t* rowp = obuf + (unit & 1) * 16384 + srow * 128;
+      if (FAST == FAST_QKV16) {
+        const float sc = c0 < TM_DIM ? 0.125f : 1.0f;   // q * dim_head^-0.5 (exact in fp16)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 u;
+          u.x = pack_f16x2(v[8 * j] * sc, v[8 * j + 1] * sc); u.y = pack_f16x2(v[8 * j + 2] * sc, v[8 * j + 3] * sc);
+          u.z = pack_f16x2(v[8 * j + 4] * sc, v[8 * j + 5] * sc); u.w = pack_f16x2(v[8 * j + 6] * sc, v[8 * j + 7] * sc);
+          *reinterpret_cast<uint4*>(rowp + ((((chunk & 1) * 4 + j) ^ (rt & 7)) << 4)) = u;
+        }
+      } else {
+        if (srow >= 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(rowp + ((j ^ (srow & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+      }
+      if (last) {
+        fence_proxy_async();         // generic-proxy smem writes -> visible to the TMA engine
+        named_bar_sync(1, 128);
+        if (leader) {
+          const uint8_t* src = obuf + (unit & 1) * 16384;
+          if (FAST == FAST_QKV16) {
+            const int cb = c0 - 32;  // first column of the 64-wide head slice
+            const int which = cb / TM_DIM, hh = (cb % TM_DIM) / TM_DHEAD;
+            tma_store_3d(&om.m[which], src, 0, i0, bag * TM_HEADS + hh);
+          } else if (FAST == FAST_BIAS_RESID) {
+            if (shift > 0) tma_store_3d(&om.m[1], src, c0, p.c_row_off, bag);
+            else tma_store_3d(&om.m[0], src, c0, p.c_row_off + i0 - p.c_skip, bag);
+          } else {
+            tma_store_3d(&om.m[0], src, c0, p.c_row_off + i0, bag);
+            if (i0 < p.dup) tma_store_3d(&om.m[1], src, c0, p.c_row_off + p.rows_per_bag + i0, bag);   // TransMIL.py:180
+          }
+          tma_store_commit();
+        }
+        ++unit;
+      }
+    }
+  }
+  if (leader) tma_store_wait_all<0>();
+}
+
+template <int BN, bool F16, int FAST>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p, int m_tiles,
-               int n_tiles, int k_blocks, int total) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ TcOutMaps om,
+               const GemmParams p, int m_tiles, int n_tiles, int k_blocks, int total) {
   constexpr int STAGES = TcCfg<BN>::STAGES;
   constexpr int B_BYTES = TcCfg<BN>::B_BYTES;
   constexpr int BK = F16 ? 64 : 32;             // elements per k-block
@@ -116,7 +243,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* sA = smem;
   uint8_t* sB = sA + STAGES * TC_A_BYTES;
   float* stg = reinterpret_cast<float*>(sB + STAGES * B_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stg) + 4 * TC_STG_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stg) + TC_OUT_BYTES);
   uint64_t* full = bars;                 // [STAGES]  TMA -> MMA
   uint64_t* empty = bars + STAGES;       // [STAGES]  MMA -> TMA
   uint64_t* tfull = bars + 2 * STAGES;   // [2]       MMA -> epilogue
@@ -182,6 +309,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         umma_commit(&tfull[as]);
       }
     }
+  } else if (FAST != FAST_NONE) {
+    epilogue_fast<BN, FAST>(p, om, tmem_base, tfull, tempty, reinterpret_cast<uint8_t*>(stg), n_tiles, total);
   } else {
     // ---- epilogue warps: TMEM -> registers -> per-warp smem transpose -> coalesced 128-bit global accesses ----
     const int q = warp & 3;   // TMEM lane quarter this warp may access
@@ -357,15 +486,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
-template <int BN, bool F16>
-static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int batch, cudaStream_t st) {
+template <int BN, bool F16, int FAST>
+static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcOutMaps& om, const GemmParams& p, int batch, cudaStream_t st) {
   static int sms = 0;
   static bool attr_done = false;
   if (!attr_done) {
     int dev = 0;
     TM_CUDA(cudaGetDevice(&dev));
     TM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    TM_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TcCfg<BN>::SMEM));
+    TM_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, F16, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TcCfg<BN>::SMEM));
     attr_done = true;
   }
   const int BK = F16 ? 64 : 32;
@@ -373,9 +502,44 @@ static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmP
   const long long total = (long long)m_tiles * n_tiles * batch;
   TM_CHECK_ARG(total < (1ll << 31), TM_ERR_BAD_SHAPE, "gemm_tc: too many tiles");
   const int grid = total < sms ? (int)total : sms;
-  gemm_tc_kernel<BN, F16><<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(tmA, tmB, p, m_tiles, n_tiles, k_blocks, (int)total);
+  gemm_tc_kernel<BN, F16, FAST><<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(tmA, tmB, om, p, m_tiles, n_tiles, k_blocks, (int)total);
   TM_LAUNCH_CHECK();
   return TM_OK;
+}
+
+// Chooses the TMA-store epilogue when the row map of the call is expressible as tensor-map coordinates.
+static int pick_fast(const GemmParams& p, int batch, TcOutMaps* om) {
+  if (batch != 1 || p.N % 32 != 0 || p.bn128) return FAST_NONE;
+  if (p.epi == EPI_QKV16 && p.Sp % TC_BM == 0 && p.M % p.Sp == 0 && p.N == 3 * TM_DIM) {
+    const uint64_t nb = (uint64_t)(p.M / p.Sp) * TM_HEADS;
+    const void* base[3] = {p.q, p.k, p.v};
+    for (int i = 0; i < 3; ++i)
+      if (make_tmap_3d_f16(&om->m[i], base[i], nb, (uint64_t)p.Sp, TM_DHEAD, (uint64_t)p.Sp * TM_DHEAD, TM_DHEAD, TC_BM, TM_DHEAD) != TM_OK) return FAST_NONE;
+    return FAST_QKV16;
+  }
+  if (p.epi == EPI_BIAS_RESID && p.rows_per_bag > 0 && p.rows_per_bag % TC_BM == 0 && p.M % p.rows_per_bag == 0 && p.ldc % 4 == 0) {
+    const uint64_t nb = (uint64_t)(p.M / p.rows_per_bag);
+    if (make_tmap_3d(&om->m[0], p.C, nb, (uint64_t)p.c_bag_rows, (uint64_t)p.N, (uint64_t)p.c_bag_rows * p.ldc, (uint64_t)p.ldc, TC_BM, 32) != TM_OK)
+      return FAST_NONE;
+    if (p.c_skip % TC_BM != 0 &&
+        make_tmap_3d(&om->m[1], p.C, nb, (uint64_t)p.c_bag_rows, (uint64_t)p.N, (uint64_t)p.c_bag_rows * p.ldc, (uint64_t)p.ldc,
+                     TC_BM - p.c_skip % TC_BM, 32) != TM_OK)
+      return FAST_NONE;
+    return FAST_BIAS_RESID;
+  }
+  if (p.epi == EPI_BIAS_GELU && p.ldc % 4 == 0) {
+    // one bag, or bags whose row count is a multiple of the tile (a tile never straddles two bags)
+    const int rpb = p.rows_per_bag > 0 ? p.rows_per_bag : p.M;
+    if (p.M % rpb != 0 || (p.M != rpb && rpb % TC_BM != 0)) return FAST_NONE;
+    const uint64_t nb = (uint64_t)(p.M / rpb);
+    const uint64_t bag_rows = p.rows_per_bag > 0 ? (uint64_t)p.c_bag_rows : (uint64_t)p.M;
+    if (make_tmap_3d(&om->m[0], p.C, nb, (uint64_t)(p.c_row_off + rpb), (uint64_t)p.N, bag_rows * p.ldc, (uint64_t)p.ldc, TC_BM, 32) != TM_OK)
+      return FAST_NONE;
+    if (p.dup > 0 && make_tmap_3d(&om->m[1], p.C, nb, bag_rows, (uint64_t)p.N, bag_rows * p.ldc, (uint64_t)p.ldc, TC_BM, 32) != TM_OK)
+      return FAST_NONE;
+    return FAST_BIAS_GELU;
+  }
+  return FAST_NONE;
 }
 
 int gemm_tc(const GemmParams& p, cudaStream_t st) {
@@ -386,22 +550,35 @@ int gemm_tc(const GemmParams& p, cudaStream_t st) {
   const uint64_t sA = batch > 1 ? (uint64_t)p.strideA : (uint64_t)p.M * p.lda;
   const uint64_t sB = batch > 1 ? (uint64_t)p.strideB : (uint64_t)p.N * p.ldb;
   CUtensorMap tmA, tmB;
+  TcOutMaps om;
+  memset(&om, 0, sizeof(om));
+  const int fast = pick_fast(p, batch, &om);
   if (p.f16_in) {
     TM_PROPAGATE(make_tmap_3d_f16(&tmA, p.A, batch, (uint64_t)p.M, (uint64_t)p.K, sA, (uint64_t)p.lda, TC_BM, 64));
     if (p.bn128) {
       TM_PROPAGATE(make_tmap_3d_f16(&tmB, p.Bm, batch, (uint64_t)p.N, (uint64_t)p.K, sB, (uint64_t)p.ldb, 128, 64));
-      return launch_tc<128, true>(tmA, tmB, p, batch, st);
+      return launch_tc<128, true, FAST_NONE>(tmA, tmB, om, p, batch, st);
     }
     TM_PROPAGATE(make_tmap_3d_f16(&tmB, p.Bm, batch, (uint64_t)p.N, (uint64_t)p.K, sB, (uint64_t)p.ldb, 256, 64));
-    return launch_tc<256, true>(tmA, tmB, p, batch, st);
+    switch (fast) {
+      case FAST_QKV16: return launch_tc<256, true, FAST_QKV16>(tmA, tmB, om, p, batch, st);
+      case FAST_BIAS_RESID: return launch_tc<256, true, FAST_BIAS_RESID>(tmA, tmB, om, p, batch, st);
+      case FAST_BIAS_GELU: return launch_tc<256, true, FAST_BIAS_GELU>(tmA, tmB, om, p, batch, st);
+      default: return launch_tc<256, true, FAST_NONE>(tmA, tmB, om, p, batch, st);
+    }
   }
   TM_PROPAGATE(make_tmap_3d(&tmA, p.A, batch, (uint64_t)p.M, (uint64_t)p.K, sA, (uint64_t)p.lda, TC_BM, 32));
   if (p.bn128) {
     TM_PROPAGATE(make_tmap_3d(&tmB, p.Bm, batch, (uint64_t)p.N, (uint64_t)p.K, sB, (uint64_t)p.ldb, 128, 32));
-    return launch_tc<128, false>(tmA, tmB, p, batch, st);
+    return launch_tc<128, false, FAST_NONE>(tmA, tmB, om, p, batch, st);
   }
   TM_PROPAGATE(make_tmap_3d(&tmB, p.Bm, batch, (uint64_t)p.N, (uint64_t)p.K, sB, (uint64_t)p.ldb, 256, 32));
-  return launch_tc<256, false>(tmA, tmB, p, batch, st);
+  switch (fast) {
+    case FAST_QKV16: return launch_tc<256, false, FAST_QKV16>(tmA, tmB, om, p, batch, st);
+    case FAST_BIAS_RESID: return launch_tc<256, false, FAST_BIAS_RESID>(tmA, tmB, om, p, batch, st);
+    case FAST_BIAS_GELU: return launch_tc<256, false, FAST_BIAS_GELU>(tmA, tmB, om, p, batch, st);
+    default: return launch_tc<256, false, FAST_NONE>(tmA, tmB, om, p, batch, st);
+  }
 }
 
 }  // namespace tmil
