@@ -102,13 +102,17 @@ constexpr int TC_OUT_BYTES = 2 * 16384;         // epilogue staging: two [128 ro
 static_assert(4 * TC_STG_BYTES <= TC_OUT_BYTES, "generic staging must fit the output staging region");
 
 // Output tensor maps of the TMA-store epilogues (see epilogue_fast)
-struct TcOutMaps { CUtensorMap m[3]; };
+struct TcOutMaps { CUtensorMap m[4]; };
 enum TcFast : int { FAST_NONE = 0, FAST_QKV16 = 1, FAST_BIAS_RESID = 2, FAST_BIAS_GELU = 3 };
 
-template <int BN> struct TcCfg {
+template <int BN, int FAST = 0> struct TcCfg {
   static constexpr int B_BYTES = BN * 128;
-  static constexpr int STAGES = BN == 256 ? 4 : 6;
-  static constexpr size_t SMEM = 1024 + STAGES * (TC_A_BYTES + B_BYTES) + TC_OUT_BYTES + 256;
+  // the bias+residual epilogue streams the residual through four in-place [128][128 B] boxes (TMA load -> add -> TMA store)
+  // and gives up one operand stage for them
+  static constexpr int STAGES = BN == 256 ? (FAST == 2 ? 3 : 4) : 6;
+  static constexpr int OUT_BYTES = FAST == 2 ? 4 * 16384 : TC_OUT_BYTES;
+  static constexpr int THREADS = FAST == 2 ? 224 : TC_THREADS;   // + one warp that loads the residual boxes
+  static constexpr size_t SMEM = 1024 + STAGES * (TC_A_BYTES + B_BYTES) + OUT_BYTES + 256;
 };
 
 // ---- TMA-store epilogues ---------------------------------------------------------------------------------------
@@ -122,12 +126,42 @@ template <int BN> struct TcCfg {
 //   FAST_BIAS_GELU   C = gelu(acc + bias), fp32 boxes [128][32], plus the duplicate-pad rows as a second store
 template <int BN, int FAST>
 __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMaps& om, uint32_t tmem_base, uint64_t* tfull,
-                                              uint64_t* tempty, uint8_t* obuf, int n_tiles, int total) {
+                                              uint64_t* tempty, uint64_t* lfull, uint64_t* lempty, uint8_t* obuf, int n_tiles,
+                                              int total) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int NBUF = FAST == FAST_BIAS_RESID ? 4 : 2;
+
+  if (FAST == FAST_BIAS_RESID && warp == 6) {
+    // ---- residual loader: h_in boxes [128 rows][32 cols] -> smem ring, one per (tile, 32-column chunk), in the order the
+    // epilogue consumes them.  A thread-per-row read of the residual (16 bytes per lane at a 2 KB stride) ran at 1.3 TB/s;
+    // the TMA box is a coalesced full-line read and lands in the layout the TMA store takes back out.
+    if (lane == 0) {
+      uint32_t unit = 0;
+      for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int m_blk = tile / n_tiles, n_blk = tile - m_blk * n_tiles;
+        const int r0 = m_blk * TC_BM;
+        const int bag = r0 / p.rows_per_bag, i0 = r0 - bag * p.rows_per_bag;
+        const int shift = i0 < p.c_skip ? p.c_skip - i0 : 0;
+        if (shift >= TC_BM) continue;
+        for (int chunk = 0; chunk < BN / 32; ++chunk) {
+          const int c0 = n_blk * BN + chunk * 32;
+          if (c0 >= p.N) continue;
+          const int b = unit % NBUF;
+          mbar_wait(&lempty[b], ((unit / NBUF) & 1) ^ 1);
+          mbar_arrive_expect_tx(&lfull[b], (TC_BM - shift) * 128);
+          if (shift > 0) tma_load_3d(obuf + b * 16384, &om.m[3], &lfull[b], c0, p.c_row_off, bag);
+          else tma_load_3d(obuf + b * 16384, &om.m[2], &lfull[b], c0, p.c_row_off + i0 - p.c_skip, bag);
+          ++unit;
+        }
+      }
+    }
+    return;
+  }
+
   const int q = warp & 3;
   const int rt = q * 32 + lane;                 // row inside the 128-row tile = TMEM lane
   const bool leader = threadIdx.x == 64;        // warp 2, lane 0 issues the stores
-  uint32_t unit = 0;                            // boxes written so far (buffer = unit & 1)
+  uint32_t unit = 0;                            // boxes written so far (buffer = unit % NBUF)
   int it = 0;
   for (int tile = blockIdx.x; tile < total; tile += gridDim.x, ++it) {
     const int m_blk = tile / n_tiles, n_blk = tile - m_blk * n_tiles;
@@ -138,14 +172,10 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
     if (p.rows_per_bag > 0) { bag = r0 / p.rows_per_bag; i0 = r0 - bag * p.rows_per_bag; }
     if (FAST == FAST_QKV16) { bag = r0 / p.Sp; i0 = r0 - bag * p.Sp; }
     // FAST_BIAS_RESID: the first c_skip rows of a bag (front pad) are not stored.  TMA stores take no negative coordinates
-    // here, so a tile of pad rows only is skipped and the tile that straddles the boundary stores a shorter box (map m[1],
-    // 128 - shift rows) whose rows were written `shift` rows higher in smem.
+    // here, so a tile of pad rows only is skipped and the tile that straddles the boundary moves a shorter box (maps m[1] /
+    // m[3], 128 - shift rows) whose rows sit `shift` rows higher in smem.
     const int shift = (FAST == FAST_BIAS_RESID && i0 < p.c_skip) ? p.c_skip - i0 : 0;
-    const float* lrow = nullptr;                // FAST_BIAS_RESID: this thread's residual row (nullptr: not stored)
-    if (FAST == FAST_BIAS_RESID) {
-      const int i = i0 + rt;
-      if (r0 + rt < p.M && i >= p.c_skip) lrow = p.L + ((long long)bag * p.c_bag_rows + p.c_row_off + (i - p.c_skip)) * p.ldl;
-    }
+    const int srow = rt - shift;                // row of the smem box
     mbar_wait(&tfull[as], aphase);
     tc_fence_after();
     const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
@@ -162,55 +192,56 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
       if (c0 >= p.N || shift >= TC_BM) continue;      // uniform over the CTA
       const bool first = FAST == FAST_QKV16 ? (chunk & 1) == 0 : true;
       const bool last = FAST == FAST_QKV16 ? (chunk & 1) == 1 : true;
-      if (FAST == FAST_BIAS_RESID) {
-        float4 l[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) l[j] = lrow != nullptr ? *reinterpret_cast<const float4*>(lrow + c0 + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
-          v[4 * j] = l[j].x + (v[4 * j] + b.x); v[4 * j + 1] = l[j].y + (v[4 * j + 1] + b.y);
-          v[4 * j + 2] = l[j].z + (v[4 * j + 2] + b.z); v[4 * j + 3] = l[j].w + (v[4 * j + 3] + b.w);
-        }
-      } else if (FAST == FAST_BIAS_GELU) {
+      const int b = unit % NBUF;
+      uint8_t* rowp = obuf + b * 16384 + srow * 128;
+      if (FAST == FAST_BIAS_GELU) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
-          v[4 * j] = gelu_erf(v[4 * j] + b.x); v[4 * j + 1] = gelu_erf(v[4 * j + 1] + b.y);
-          v[4 * j + 2] = gelu_erf(v[4 * j + 2] + b.z); v[4 * j + 3] = gelu_erf(v[4 * j + 3] + b.w);
+          const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
+          v[4 * j] = gelu_erf(v[4 * j] + bb.x); v[4 * j + 1] = gelu_erf(v[4 * j + 1] + bb.y);
+          v[4 * j + 2] = gelu_erf(v[4 * j + 2] + bb.z); v[4 * j + 3] = gelu_erf(v[4 * j + 3] + bb.w);
         }
         if (p.round_out) {
 #pragma unroll
           for (int e = 0; e < 32; ++e) v[e] = round_tf32(v[e]);
         }
       }
-      if (first) {                   // the box written two units ago must have been read out by its TMA store
-        if (leader) tma_store_wait_read<1>();
-        named_bar_sync(1, 128);
-      }
-      const int srow = rt - shift;   // row of the smem box
-      uint8_t* rowp = obuf + (unit & 1) * 16384 + srow * 128;
-      if (FAST == FAST_QKV16) {
-        const float sc = c0 < TM_DIM ? 0.125f : 1.0f;   // q * dim_head^-0.5 (exact in fp16)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint4 u;
-          u.x = pack_f16x2(v[8 * j] * sc, v[8 * j + 1] * sc); u.y = pack_f16x2(v[8 * j + 2] * sc, v[8 * j + 3] * sc);
-          u.z = pack_f16x2(v[8 * j + 4] * sc, v[8 * j + 5] * sc); u.w = pack_f16x2(v[8 * j + 6] * sc, v[8 * j + 7] * sc);
-          *reinterpret_cast<uint4*>(rowp + ((((chunk & 1) * 4 + j) ^ (rt & 7)) << 4)) = u;
-        }
-      } else {
+      if (FAST == FAST_BIAS_RESID) {
+        mbar_wait(&lfull[b], (unit / NBUF) & 1);   // the residual box of this chunk has landed in the buffer
         if (srow >= 0) {
 #pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4* cell = reinterpret_cast<float4*>(rowp + ((j ^ (srow & 7)) << 4));
+            const float4 l = *cell;
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j);
+            *cell = make_float4(l.x + (v[4 * j] + bb.x), l.y + (v[4 * j + 1] + bb.y), l.z + (v[4 * j + 2] + bb.z), l.w + (v[4 * j + 3] + bb.w));
+          }
+        }
+      } else {
+        if (first) {                 // the box written NBUF units ago must have been read out by its TMA store
+          if (leader) tma_store_wait_read<1>();
+          named_bar_sync(1, 128);
+        }
+        if (FAST == FAST_QKV16) {
+          const float sc = c0 < TM_DIM ? 0.125f : 1.0f;   // q * dim_head^-0.5 (exact in fp16)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 u;
+            u.x = pack_f16x2(v[8 * j] * sc, v[8 * j + 1] * sc); u.y = pack_f16x2(v[8 * j + 2] * sc, v[8 * j + 3] * sc);
+            u.z = pack_f16x2(v[8 * j + 4] * sc, v[8 * j + 5] * sc); u.w = pack_f16x2(v[8 * j + 6] * sc, v[8 * j + 7] * sc);
+            *reinterpret_cast<uint4*>(rowp + ((((chunk & 1) * 4 + j) ^ (rt & 7)) << 4)) = u;
+          }
+        } else {
+#pragma unroll
           for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<float4*>(rowp + ((j ^ (srow & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            *reinterpret_cast<float4*>(rowp + ((j ^ (rt & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         }
       }
       if (last) {
         fence_proxy_async();         // generic-proxy smem writes -> visible to the TMA engine
         named_bar_sync(1, 128);
         if (leader) {
-          const uint8_t* src = obuf + (unit & 1) * 16384;
+          const uint8_t* src = obuf + b * 16384;
           if (FAST == FAST_QKV16) {
             const int cb = c0 - 32;  // first column of the 64-wide head slice
             const int which = cb / TM_DIM, hh = (cb % TM_DIM) / TM_DHEAD;
@@ -223,6 +254,10 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
             if (i0 < p.dup) tma_store_3d(&om.m[1], src, c0, p.c_row_off + p.rows_per_bag + i0, bag);   // TransMIL.py:180
           }
           tma_store_commit();
+          if (FAST == FAST_BIAS_RESID) {   // the store issued two units ago has read its box: give it back to the loader
+            tma_store_wait_read<2>();
+            if (unit >= 2) mbar_arrive(&lempty[(unit - 2) % NBUF]);
+          }
         }
         ++unit;
       }
@@ -232,23 +267,25 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
 }
 
 template <int BN, bool F16, int FAST>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(224, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ TcOutMaps om,
                const GemmParams p, int m_tiles, int n_tiles, int k_blocks, int total) {
-  constexpr int STAGES = TcCfg<BN>::STAGES;
-  constexpr int B_BYTES = TcCfg<BN>::B_BYTES;
+  constexpr int STAGES = TcCfg<BN, FAST>::STAGES;
+  constexpr int B_BYTES = TcCfg<BN, FAST>::B_BYTES;
   constexpr int BK = F16 ? 64 : 32;             // elements per k-block
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
   uint8_t* sB = sA + STAGES * TC_A_BYTES;
   float* stg = reinterpret_cast<float*>(sB + STAGES * B_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stg) + TC_OUT_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stg) + TcCfg<BN, FAST>::OUT_BYTES);
   uint64_t* full = bars;                 // [STAGES]  TMA -> MMA
   uint64_t* empty = bars + STAGES;       // [STAGES]  MMA -> TMA
   uint64_t* tfull = bars + 2 * STAGES;   // [2]       MMA -> epilogue
   uint64_t* tempty = tfull + 2;          // [2]       epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* lfull = tempty + 3;          // [4] residual box landed      (FAST_BIAS_RESID)
+  uint64_t* lempty = lfull + 4;          // [4] residual box stored back (FAST_BIAS_RESID)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
@@ -258,6 +295,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    if (FAST == FAST_BIAS_RESID)
+      for (int i = 0; i < 4; ++i) { mbar_init(&lfull[i], 1); mbar_init(&lempty[i], 1); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, 2 * BN);
@@ -310,7 +349,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (FAST != FAST_NONE) {
-    epilogue_fast<BN, FAST>(p, om, tmem_base, tfull, tempty, reinterpret_cast<uint8_t*>(stg), n_tiles, total);
+    epilogue_fast<BN, FAST>(p, om, tmem_base, tfull, tempty, lfull, lempty, reinterpret_cast<uint8_t*>(stg), n_tiles, total);
   } else {
     // ---- epilogue warps: TMEM -> registers -> per-warp smem transpose -> coalesced 128-bit global accesses ----
     const int q = warp & 3;   // TMEM lane quarter this warp may access
@@ -494,7 +533,7 @@ static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcOut
     int dev = 0;
     TM_CUDA(cudaGetDevice(&dev));
     TM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    TM_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, F16, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TcCfg<BN>::SMEM));
+    TM_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, F16, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TcCfg<BN, FAST>::SMEM));
     attr_done = true;
   }
   const int BK = F16 ? 64 : 32;
@@ -502,7 +541,7 @@ static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcOut
   const long long total = (long long)m_tiles * n_tiles * batch;
   TM_CHECK_ARG(total < (1ll << 31), TM_ERR_BAD_SHAPE, "gemm_tc: too many tiles");
   const int grid = total < sms ? (int)total : sms;
-  gemm_tc_kernel<BN, F16, FAST><<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(tmA, tmB, om, p, m_tiles, n_tiles, k_blocks, (int)total);
+  gemm_tc_kernel<BN, F16, FAST><<<grid, TcCfg<BN, FAST>::THREADS, TcCfg<BN, FAST>::SMEM, st>>>(tmA, tmB, om, p, m_tiles, n_tiles, k_blocks, (int)total);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
@@ -521,10 +560,15 @@ static int pick_fast(const GemmParams& p, int batch, TcOutMaps* om) {
     const uint64_t nb = (uint64_t)(p.M / p.rows_per_bag);
     if (make_tmap_3d(&om->m[0], p.C, nb, (uint64_t)p.c_bag_rows, (uint64_t)p.N, (uint64_t)p.c_bag_rows * p.ldc, (uint64_t)p.ldc, TC_BM, 32) != TM_OK)
       return FAST_NONE;
-    if (p.c_skip % TC_BM != 0 &&
-        make_tmap_3d(&om->m[1], p.C, nb, (uint64_t)p.c_bag_rows, (uint64_t)p.N, (uint64_t)p.c_bag_rows * p.ldc, (uint64_t)p.ldc,
-                     TC_BM - p.c_skip % TC_BM, 32) != TM_OK)
+    if (p.ldl % 4 != 0 ||
+        make_tmap_3d(&om->m[2], p.L, nb, (uint64_t)p.c_bag_rows, (uint64_t)p.N, (uint64_t)p.c_bag_rows * p.ldl, (uint64_t)p.ldl, TC_BM, 32) != TM_OK)
       return FAST_NONE;
+    if (p.c_skip % TC_BM != 0) {
+      const uint32_t rows = TC_BM - p.c_skip % TC_BM;
+      if (make_tmap_3d(&om->m[1], p.C, nb, (uint64_t)p.c_bag_rows, (uint64_t)p.N, (uint64_t)p.c_bag_rows * p.ldc, (uint64_t)p.ldc, rows, 32) != TM_OK ||
+          make_tmap_3d(&om->m[3], p.L, nb, (uint64_t)p.c_bag_rows, (uint64_t)p.N, (uint64_t)p.c_bag_rows * p.ldl, (uint64_t)p.ldl, rows, 32) != TM_OK)
+        return FAST_NONE;
+    }
     return FAST_BIAS_RESID;
   }
   if (p.epi == EPI_BIAS_GELU && p.ldc % 4 == 0) {
