@@ -51,8 +51,12 @@ def parse():
     ap.add_argument("--bags", type=int, default=1, help="bags per step per GPU")
     ap.add_argument("--classes", type=int, default=2)
     ap.add_argument("--simt", action="store_true", help="force the fp32 CUDA-core cross-check engine")
+    ap.add_argument("--shard", default="bags", choices=["bags", "tokens"],
+                    help="bags: whole bags data-parallel across ranks (default, weak scaling); tokens: ONE bag per step, "
+                         "token-sharded across all ranks (BASELINE config 4, strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--clock-hold", type=float, default=1.5, help="seconds of extra identical steps run under the clock sampler")
     return ap.parse_args()
 
 
@@ -112,7 +116,7 @@ class ClockSampler:
     def __init__(self, index):
         self.rows, self.proc = [], None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20", "-i", str(index)],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -194,6 +198,72 @@ def cpu_baseline(a):
                  "sample": f"{reps} pass(es) over the bench bag ({a.bags}x{a.n}x{a.features}) through oracle/transmil_oracle.py after 1 warm-up"}
 
 
+def run_token_sharded(a, rank, local_rank, world, dev, model, barrier):
+    """BASELINE config 4: one bag per step, token-sharded over all ranks (transmil-deepgraft_b200/sharded.py).  Each rank
+    holds only its rows of the bag (device-resident for `value`; pinned host rows copied in for `e2e`)."""
+    import torch.distributed as dist
+    import transmil_b200 as T
+    from transmil_b200.sharded import TokenShardedTransMIL
+    if a.bags != 1:
+        raise SystemExit("--shard tokens runs one bag per step")
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29577")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    L = T.capi.lib()
+    sharded = TokenShardedTransMIL(model)
+    plan = sharded.plan(a.n)
+    x_host = plan.take(make_bag(a, 0), rank).contiguous().pin_memory()     # the same bag on every rank, this rank's rows
+    x_dev = x_host.to(dev)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    for _ in range(max(a.warmup, 3)):
+        logits = sharded(x_dev, n=a.n)
+    barrier()
+    L.tm_reset_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(a.steps):
+        logits = sharded(x_dev, n=a.n)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = int(L.tm_launch_count())
+    for _ in range(2):
+        sharded(x_host, n=a.n).cpu()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        sharded(x_host, n=a.n).cpu()
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    clocks = None
+    if sampler:
+        clocks = sampler.stop()
+    t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+    with torch.no_grad():
+        plain = model(make_bag(a, 0).to(dev)) if rank == 0 else None
+    if rank == 0:
+        value = a.steps / (ms / 1e3)
+        cfg = workload_config(a, world)
+        cfg["workload"] = (f"BASELINE config 4: ONE synthetic bag of {a.n} x {a.features} fp32 patch features per step, token-sharded over "
+                           f"{world} GPU(s) (landmark allreduce + attn3.v allgather/merge + conv and PPEG halos), n_classes={a.classes}, eval forward")
+        cfg["parallelism"] = f"token-shard{world}"
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+                "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32 storage; tf32 (fc1) / fp16 tensor-core contractions with f32 accumulate", "data": "synthetic", "config": cfg,
+                "tokens_per_s": value * a.n, "ms_per_bag": ms / a.steps, "gpu_launches": launches, "clocks": clocks,
+                "e2e": {"value": a.steps / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(x_host.numel() * 4 * world),
+                        "d2h_bytes_per_step": a.classes * 4 * world, "ms_per_step": e2e_ms / a.steps,
+                        "api": "TokenShardedTransMIL(model)(x_rows_pinned_host, n) -> logits.cpu() on every rank"},
+                "parity": {"max_abs_dlogit_vs_unsharded": float((logits - plain).abs().max())}}
+        print(json.dumps(line), flush=True)
+    dist.destroy_process_group()
+
+
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -216,20 +286,26 @@ def main():
     model = T.TransMIL(n_classes=a.classes, in_features=a.features).eval().to(dev)
     if a.simt:
         model.flags = T.capi.TM_FLAG_SIMT_ONLY
-    x_host = make_bag(a, rank).pin_memory()
-    x_dev = x_host.to(dev)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    if a.shard == "tokens":
+        return run_token_sharded(a, rank, local_rank, world, dev, model, barrier)
+    x_host = make_bag(a, rank).pin_memory()
+    x_dev = x_host.to(dev)
+
     with torch.no_grad():
+        # nvidia-smi samples every 20 ms from the warm-up through both timed regions; a K-step region of ~1 ms steps is
+        # shorter than one sample period, so the same step also runs for a further `--clock-hold` seconds (untimed) after
+        # the timed regions with the sampler still attached ("hold_s" in the clocks object).
+        sampler = ClockSampler(local_rank) if rank == 0 else None
         for _ in range(max(a.warmup, 3)):
             logits = model(x_dev)
         barrier()
         # ---- timed region 1: device-resident bag -------------------------------------------
-        sampler = ClockSampler(local_rank) if rank == 0 else None
         L.tm_profile_enable(1)
         T.capi.profile_read()
         L.tm_reset_launch_count()
@@ -241,7 +317,6 @@ def main():
         barrier()
         ms = ev0.elapsed_time(ev1)
         launches = int(L.tm_launch_count())
-        clocks = sampler.stop() if sampler else None
         stages = T.capi.profile_read()
         L.tm_profile_enable(0)
         # ---- timed region 2: end to end from pinned host memory ----------------------------
@@ -257,6 +332,15 @@ def main():
             e1.record()
             barrier()
             e2e_ms = e0.elapsed_time(e1)
+        clocks = None
+        if sampler:
+            t_hold = time.perf_counter()
+            while time.perf_counter() - t_hold < a.clock_hold:
+                for _ in range(20):
+                    model(x_dev)
+                torch.cuda.synchronize(dev)
+            clocks = sampler.stop()
+            clocks["hold_s"] = a.clock_hold
     t = torch.tensor([ms, e2e_ms if e2e_ms is not None else 0.0], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -267,7 +351,7 @@ def main():
         value = total_bags / (ms / 1e3)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
                 "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f32 storage; tf32 tensor-core contractions with f32 accumulate" if not a.simt else "f32",
+                "dtype": "f32 storage; tf32 (fc1) / fp16 tensor-core contractions with f32 accumulate" if not a.simt else "f32",
                 "data": "synthetic", "config": workload_config(a, world),
                 "tokens_per_s": value * a.n, "ms_per_bag": ms / (a.steps * a.bags),
                 "gpu_launches": launches, "clocks": clocks}

@@ -246,6 +246,41 @@ int tm_to_out_residual_fwd(const float* merged, const float* out_w, const float*
 int tm_ppeg_fwd(const tm_weights* w, const float* h_in, int64_t B, int64_t G, float* h_out,
                 float* packed, void* stream);
 
+/* ---- token-sharded single bag (the reference has no counterpart: it runs one bag on one GPU) ----------
+ * Every rank holds a contiguous range [row0, row0+rows) of the PADDED token axis of ONE layer, rows % 256 == 0, and runs
+ * the per-kernel entry points above on it with B = 1, Sp = rows (rank 0 passes P, the others P = 0).  These entry points
+ * produce / consume what crosses rank boundaries; the collectives themselves (NCCL through torch.distributed) are issued
+ * by the host side (transmil-deepgraft_b200/sharded.py). */
+/* K1 without the duplicate pad / cls row: x_rows [rows,D] -> h_rows [rows,512] (TransMIL.py:175 on a run of rows).
+ * scratch: rows*F0 floats for the two-Linear stems. */
+int tm_fc1_rows_fwd(const tm_weights* w, const float* x_rows, int64_t rows, float* h_rows, float* scratch,
+                    uint32_t flags, void* stream);
+/* K5, local half: sums [2][B*8][256][64] fp32 = per landmark group, the sum of this rank's rows of q16 / k16 that fall
+ * into it (group of padded row r = r / l; zeros for groups with no local row).  allreduce(sum) across ranks, then: */
+int tm_landmark_sums16_fwd(const void* q16, const void* k16, int64_t B, int64_t rows, int64_t row0, int64_t l,
+                           float* sums, void* stream);
+/* K5, finish: q_lm, k_lm = sums / l (fp32) and their fp16 copies (same outputs as tm_landmarks16_fwd). */
+int tm_landmark_finish_fwd(const float* sums, int64_t B, int64_t l, float* q_lm, float* k_lm, void* qlm16, void* klm16,
+                           void* stream);
+/* K8, local half: (max [B*8,256], sum [B*8,256], numerator [B*8,256,64]) of softmax_t(q_lm k^T) v over this rank's rows;
+ * partial holds tm_attn3v_partial_floats(B) floats; scratch as tm_attn3v_tc_fwd.  allgather across ranks, then: */
+int64_t tm_attn3v_partial_floats(int64_t B);
+int tm_attn3v_tc_partial_fwd(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t rows,
+                             float* partial, float* scratch, void* stream);
+/* K8, merge: gathered = R partials back to back in rank order -> W3 [B,8,256,64]; fixed visiting order, so every rank
+ * obtains the same bits. */
+int tm_attn3v_merge_fwd(const float* gathered, int64_t R, int64_t B, float* W3, void* stream);
+/* K11 across a shard boundary: adds to the first / last 16 rows of merged16 [B,rows,512] (fp16) the res_conv taps that
+ * read the previous rank's last / next rank's first 16 rows of v (v_prev16, v_next16: [B*8,16,64] fp16, NULL at the ends
+ * of the whole sequence where the conv's zero padding applies). */
+int tm_conv_halo_fix_fwd(const void* v_prev16, const void* v_next16, const float* conv_w, int64_t B, int64_t rows,
+                         void* merged16, void* stream);
+/* K13 on a token range of one bag: out rows = tokens [tok0,tok1); in_rows = whole image rows [y_in0,y_in1) of the GxG token
+ * image (the rank's own rows plus the 3-row halo received from its neighbours; must cover
+ * [max(0, tok0/G - 3), min(G, (tok1-1)/G + 4))).  packed as tm_ppeg_fwd.  The cls row is the caller's to copy. */
+int tm_ppeg_rows_fwd(const tm_weights* w, const float* in_rows, int64_t y_in0, int64_t y_in1, int64_t G, int64_t tok0,
+                     int64_t tok1, float* out, float* packed, void* stream);
+
 /* K14: final LayerNorm on the cls row + _fc (TransMIL.py:202-204).  h [B,S,512] -> logits [B,n_classes]. */
 int tm_head_fwd(const tm_weights* w, const float* h, int64_t B, int64_t S, float* logits,
                 void* stream);

@@ -86,6 +86,14 @@ SIGNATURES = {
     "tm_head_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp]),
     "tm_attn_rows_scratch_floats": (_i64, [_i64, _i64, _i64]),
     "tm_attn_rows_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, C.POINTER(_i64), _i64, _fp, _fp, _fp]),
+    "tm_fc1_rows_fwd": (C.c_int, [_PW, _fp, _i64, _fp, _fp, _u32, _fp]),
+    "tm_landmark_sums16_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _i64, _fp, _fp]),
+    "tm_landmark_finish_fwd": (C.c_int, [_fp, _i64, _i64, _fp, _fp, _fp, _fp, _fp]),
+    "tm_attn3v_partial_floats": (_i64, [_i64]),
+    "tm_attn3v_tc_partial_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _fp]),
+    "tm_attn3v_merge_fwd": (C.c_int, [_fp, _i64, _i64, _fp, _fp]),
+    "tm_conv_halo_fix_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp]),
+    "tm_ppeg_rows_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _i64, _i64, _i64, _fp, _fp, _fp]),
     "tm_gemm_nt": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _u32, _fp]),
 }
 

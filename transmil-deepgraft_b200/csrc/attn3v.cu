@@ -88,25 +88,39 @@ __global__ void __launch_bounds__(256, 1) attn3v_partial_kernel(const float* __r
 }
 
 // W3[bh, j, :] = sum_c e^{m_c - M} O_c / sum_c e^{m_c - M} s_c, chunks visited in index order.
+// Element (bh, c, j) of the max / sum arrays sits at bh*bs_ms + c*cs_ms + j, its numerator row at bh*bs_o + c*cs_o + j*64
+// (floats): the same kernel merges the chunk partials of one launch and the per-rank partials gathered from token-sharded
+// ranks.  With out_m != NULL nothing is normalised: W3 receives the merged numerator and out_m / out_s the merged max / sum
+// (the (max, sum, numerator) triple a rank contributes to the cross-rank merge).
 __global__ void __launch_bounds__(256) attn3v_combine_kernel(const float* __restrict__ pm, const float* __restrict__ ps,
-                                                             const float* __restrict__ pO, int nchunks, float* __restrict__ W3) {
+                                                             const float* __restrict__ pO, int nchunks, long long cs_ms,
+                                                             long long bs_ms, long long cs_o, long long bs_o,
+                                                             float* __restrict__ W3, float* __restrict__ out_m,
+                                                             float* __restrict__ out_s) {
   const int bh = blockIdx.y;
   const int idx = blockIdx.x * 256 + threadIdx.x;  // (j, d4)
   const int j = idx >> 4, d4 = idx & 15;
-  const long long base = (long long)bh * nchunks * TM_LANDMARKS;
+  const long long base = (long long)bh * bs_ms + j, obase = (long long)bh * bs_o + (long long)j * TM_DHEAD;
   float M = -INFINITY;
-  for (int c = 0; c < nchunks; ++c) M = fmaxf(M, pm[base + (long long)c * TM_LANDMARKS + j]);
+  for (int c = 0; c < nchunks; ++c) M = fmaxf(M, pm[base + c * cs_ms]);
   float den = 0.f;
   float4 num = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int c = 0; c < nchunks; ++c) {
-    const long long pi = base + (long long)c * TM_LANDMARKS + j;
-    const float w = expf(pm[pi] - M);
-    den = fmaf(w, ps[pi], den);
-    float4 o = reinterpret_cast<const float4*>(pO + pi * TM_DHEAD)[d4];
+    const float w = expf(pm[base + c * cs_ms] - M);
+    den = fmaf(w, ps[base + c * cs_ms], den);
+    float4 o = reinterpret_cast<const float4*>(pO + obase + c * cs_o)[d4];
     num.x = fmaf(w, o.x, num.x); num.y = fmaf(w, o.y, num.y); num.z = fmaf(w, o.z, num.z); num.w = fmaf(w, o.w, num.w);
   }
-  reinterpret_cast<float4*>(W3 + ((long long)bh * TM_LANDMARKS + j) * TM_DHEAD)[d4] =
-      make_float4(num.x / den, num.y / den, num.z / den, num.w / den);
+  float4* dst = reinterpret_cast<float4*>(W3 + ((long long)bh * TM_LANDMARKS + j) * TM_DHEAD) + d4;
+  if (out_m != nullptr) {
+    *dst = num;
+    if (d4 == 0) {
+      out_m[(long long)bh * TM_LANDMARKS + j] = M;
+      out_s[(long long)bh * TM_LANDMARKS + j] = den;
+    }
+  } else {
+    *dst = make_float4(num.x / den, num.y / den, num.z / den, num.w / den);
+  }
 }
 
 int attn3v_chunks(int64_t B, int64_t Sp) {
@@ -142,7 +156,8 @@ extern "C" int tm_attn3v_fwd(const float* q_lm, const float* k, const float* v, 
   float* pO = ps + (long long)nbh * nchunks * TM_LANDMARKS;
   attn3v_partial_kernel<<<dim3(used, nbh), 256, 0, st>>>(q_lm, k, v, (int)Sp, tpc, used, pm, ps, pO);
   TM_LAUNCH_CHECK();
-  attn3v_combine_kernel<<<dim3(16, nbh), 256, 0, st>>>(pm, ps, pO, used, W3);
+  attn3v_combine_kernel<<<dim3(16, nbh), 256, 0, st>>>(pm, ps, pO, used, TM_LANDMARKS, (long long)used * TM_LANDMARKS, TM_LANDMARKS * TM_DHEAD,
+                                                        (long long)used * TM_LANDMARKS * TM_DHEAD, W3, nullptr, nullptr);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -247,7 +247,8 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
 }
 
 __global__ void attn3v_combine_kernel(const float* __restrict__ pm, const float* __restrict__ ps, const float* __restrict__ pO,
-                                      int nchunks, float* __restrict__ W3);   // attn3v.cu
+                                      int nchunks, long long cs_ms, long long bs_ms, long long cs_o, long long bs_o,
+                                      float* __restrict__ W3, float* __restrict__ out_m, float* __restrict__ out_s);   // attn3v.cu
 
 }  // namespace tmil
 
@@ -256,12 +257,13 @@ extern "C" int64_t tm_attn3v_tc_scratch_floats(int64_t B, int64_t Sp) {
   return nbh * tmil::attn_chunks(nbh, Sp / tmil::A3_TOK) * TM_LANDMARKS * (TM_DHEAD + 2);
 }
 
-extern "C" int tm_attn3v_tc_fwd(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3,
-                                float* scratch, uint32_t flags, void* stream) {
+// partial == NULL: W3 = normalised result.  partial != NULL: the rank-level (max [nbh,256], sum [nbh,256], numerator
+// [nbh,256,64]) triple is written there, unnormalised, and W3 is not touched.
+static int attn3v_tc_run(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3, float* partial,
+                         float* scratch, void* stream) {
   using namespace tmil;
-  (void)flags;
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE, "tm_attn3v_tc_fwd: Sp must be a multiple of 256 (Sp=%lld)", (long long)Sp);
-  TM_CHECK_ARG(qlm16 && k16 && v16 && W3 && scratch, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_fwd: NULL pointer");
+  TM_CHECK_ARG(qlm16 && k16 && v16 && (W3 || partial) && scratch, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_fwd: NULL pointer");
   TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "tm_attn3v_tc_fwd needs an sm_100 device");
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t nbh = B * TM_HEADS;
@@ -283,7 +285,42 @@ extern "C" int tm_attn3v_tc_fwd(const void* qlm16, const void* k16, const void* 
   float* pO = ps + nbh * used * TM_LANDMARKS;
   attn3v_tc_kernel<<<dim3((unsigned)used, (unsigned)nbh), A3_THREADS, A3_SMEM, st>>>(tmQ, tmK, tmV, tpc, tiles_per_bh, used, pm, ps, pO);
   TM_LAUNCH_CHECK();
-  attn3v_combine_kernel<<<dim3(16, (unsigned)nbh), 256, 0, st>>>(pm, ps, pO, used, W3);
+  float* out_m = partial;
+  float* out_s = partial ? partial + nbh * TM_LANDMARKS : nullptr;
+  float* out_n = partial ? partial + 2 * nbh * TM_LANDMARKS : W3;
+  attn3v_combine_kernel<<<dim3(16, (unsigned)nbh), 256, 0, st>>>(pm, ps, pO, used, TM_LANDMARKS, (long long)used * TM_LANDMARKS,
+                                                                  TM_LANDMARKS * TM_DHEAD, (long long)used * TM_LANDMARKS * TM_DHEAD,
+                                                                  out_n, out_m, out_s);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+extern "C" int tm_attn3v_tc_fwd(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3,
+                                float* scratch, uint32_t flags, void* stream) {
+  (void)flags;
+  TM_CHECK_ARG(W3 != nullptr, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_fwd: NULL pointer");
+  return attn3v_tc_run(qlm16, k16, v16, B, Sp, W3, nullptr, scratch, stream);
+}
+
+extern "C" int64_t tm_attn3v_partial_floats(int64_t B) { return B * TM_HEADS * TM_LANDMARKS * (TM_DHEAD + 2); }
+
+// Token-sharded K8, local half: this rank's rows [0, rows) of k16 / v16 (rows % 256 == 0) against the REPLICATED landmark
+// queries -> partial = (max, sum, numerator), tm_attn3v_partial_floats(B) floats.
+extern "C" int tm_attn3v_tc_partial_fwd(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t rows,
+                                        float* partial, float* scratch, void* stream) {
+  TM_CHECK_ARG(partial != nullptr, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_partial_fwd: NULL pointer");
+  return attn3v_tc_run(qlm16, k16, v16, B, rows, nullptr, partial, scratch, stream);
+}
+
+// Token-sharded K8, merge: `gathered` holds the partials of R ranks back to back (rank order); W3 = the softmax-weighted
+// combination, visited in rank order on every rank (bit-identical results on all ranks).
+extern "C" int tm_attn3v_merge_fwd(const float* gathered, int64_t R, int64_t B, float* W3, void* stream) {
+  using namespace tmil;
+  TM_CHECK_ARG(gathered && W3 && R > 0 && B > 0, TM_ERR_BAD_ARGUMENT, "tm_attn3v_merge_fwd: bad arguments");
+  const long long nbh = B * TM_HEADS, per_rank = nbh * TM_LANDMARKS * (TM_DHEAD + 2);
+  attn3v_combine_kernel<<<dim3(16, (unsigned)nbh), 256, 0, (cudaStream_t)stream>>>(
+      gathered, gathered + nbh * TM_LANDMARKS, gathered + 2 * nbh * TM_LANDMARKS, (int)R, per_rank, TM_LANDMARKS, per_rank,
+      TM_LANDMARKS * TM_DHEAD, W3, nullptr, nullptr);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -150,14 +150,15 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
 
 using namespace tmil;
 
-extern "C" int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n, float* h0, float* scratch,
-                          uint32_t flags, void* stream) {
+// pad_cls: write the square duplicate pad and the cls row (whole bags).  Otherwise x is a plain run of `n` rows and h0 the
+// matching run of output rows (token-sharded ranks).
+static int fc1_run(const tm_weights* w, const float* x, int64_t B, int64_t n, float* h0, float* scratch, uint32_t flags,
+                   cudaStream_t st, bool pad_cls) {
   TM_PROPAGATE(check_weights(w));
   tm_plan p;
   TM_PROPAGATE(tm_make_plan(n, &p));
   TM_CHECK_ARG(B > 0 && x && h0, TM_ERR_BAD_ARGUMENT, "tm_fc1_fwd: bad arguments");
   TM_CHECK_ARG(B * n < (1ll << 31) && B * p.Sp < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_fc1_fwd: B*n exceeds 2^31 rows");
-  cudaStream_t st = (cudaStream_t)stream;
   const int D = w->in_features;
   GemmParams g;
   memset(&g, 0, sizeof(g));
@@ -176,15 +177,31 @@ extern "C" int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_
   }
   g.A = a2; g.Bm = w2; g.C = h0; g.bias = b2;
   g.M = (int)(B * n); g.N = TM_DIM; g.K = k2; g.lda = k2; g.ldb = k2; g.ldc = TM_DIM;
-  g.rows_per_bag = (int)n; g.c_bag_rows = p.S; g.c_row_off = 1; g.c_skip = 0; g.dup = (int)p.dup;
+  if (pad_cls) {
+    g.rows_per_bag = (int)n; g.c_bag_rows = p.S; g.c_row_off = 1; g.c_skip = 0; g.dup = (int)p.dup;
+  }
   prof_mark(ST_FC1_GEMM1, st);
   TM_PROPAGATE(gemm_auto(g, flags, st));
   prof_mark(ST_FC1_TAIL, st);
+  if (!pad_cls) {
+    if (w->fc1_kind == TM_FC1_768) TM_PROPAGATE(ln_inplace(h0, w->fc1_ln2_w, w->fc1_ln2_b, B * n, TM_DIM, 0, 0, 0, false, st));
+    return TM_OK;
+  }
   if (w->fc1_kind == TM_FC1_768)  // trailing LayerNorm(512) on every token row (row 0 is the cls token)
     TM_PROPAGATE(ln_inplace(h0, w->fc1_ln2_w, w->fc1_ln2_b, B * p.N, TM_DIM, (int)p.N, p.S, 1, false, st));
   cls_rows_kernel<<<(unsigned)B, TM_DIM / 4, 0, st>>>(w->cls_token, p.S * (long long)TM_DIM, h0);
   TM_LAUNCH_CHECK();
   return TM_OK;
+}
+
+extern "C" int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n, float* h0, float* scratch,
+                          uint32_t flags, void* stream) {
+  return fc1_run(w, x, B, n, h0, scratch, flags, (cudaStream_t)stream, true);
+}
+
+extern "C" int tm_fc1_rows_fwd(const tm_weights* w, const float* x_rows, int64_t rows, float* h_rows, float* scratch,
+                               uint32_t flags, void* stream) {
+  return fc1_run(w, x_rows, 1, rows, h_rows, scratch, flags, (cudaStream_t)stream, false);
 }
 
 extern "C" int tm_qkv_fwd(const float* xn, const float* qkv_w, int64_t B, int64_t Sp, float* q, float* k, float* v,

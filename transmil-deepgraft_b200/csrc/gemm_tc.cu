@@ -88,6 +88,24 @@ int make_tmap_3d_f16(CUtensorMap* out, const void* base, uint64_t batch, uint64_
   return TM_OK;
 }
 
+// fp32 tensor of rank <= 5 with arbitrary (16-byte multiple) byte strides, unswizzled box, zero fill outside the extents.
+int make_tmap_f32_nd(CUtensorMap* out, const float* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                     const uint32_t* box) {
+  TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "TMA tensor maps need an sm_100 device and driver");
+  TM_CHECK_ARG(rank >= 2 && rank <= 5 && aligned16(base), TM_ERR_BAD_ALIGNMENT, "TMA operand must be 16-byte aligned (rank 2..5)");
+  cuuint64_t d[5], s[4];
+  cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) {
+    TM_CHECK_ARG(strides_bytes[i] % 16 == 0, TM_ERR_BAD_ALIGNMENT, "TMA strides must be multiples of 16 bytes");
+    s[i] = strides_bytes[i];
+  }
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, (void*)base, d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TM_CHECK_ARG(r == CUDA_SUCCESS, TM_ERR_CUDA, "cuTensorMapEncodeTiled(nd) failed with %d", (int)r);
+  return TM_OK;
+}
+
 // ---- kernel ------------------------------------------------------------------------------------------------
 // Template parameters: BN = N tile (256: big weight GEMMs, 128: the batched 256^3 products of the pinv chain),
 // F16 = operand type (false: tf32 in fp32 storage, BK = 32; true: fp16, BK = 64).  Either way a k-block row is 128 bytes

@@ -1,0 +1,370 @@
+"""Token-sharded forward of ONE giant bag across the ranks of a process group (BASELINE config 4).
+
+The reference runs a bag on one GPU (code/models/TransMIL.py:167-211); Nystrom attention makes the bag splittable along
+the token axis with a handful of small exchanges per layer, so a 200k-token slide can use 2/4/8 B200s for latency:
+
+  * every rank owns a contiguous range of the PADDED token axis [row0, row1), a multiple of 256 rows, and runs the ordinary
+    per-kernel entry points of libtransmil_b200 on it (B = 1, Sp = rows; rank 0 also owns the P front-pad rows and cls);
+  * landmarks: per-group partial sums -> allreduce(sum) of [2,8,256,64] fp32 (1 MB) -> means (groups may straddle ranks);
+  * sim2 / pseudo-inverse / Z.W3: replicated (identical inputs on every rank -> identical bits, no exchange);
+  * attn3.v: per-rank (max, sum, numerator) partials -> allgather (540 KB per rank) -> log-sum-exp merge in rank order;
+  * res_conv (33 taps): 16-row halo of v to both neighbours (16 KB each way), added by a boundary-fix kernel;
+  * PPEG between the layers: a 3-image-row halo of the layer-1 output to both neighbours (<= 4G rows each way);
+  * fc1 is row-parallel; the duplicate-pad tail (TransMIL.py:177-180) is recomputed from the first `dup` input rows by the
+    rank(s) that own it, so it needs no communication;  * the cls row lives on rank 0: logits there, broadcast at the end.
+
+`ShardPlan` is pure integer arithmetic (testable anywhere).  `sharded_forward` is the host logic: buffers with halo
+room, the collectives (torch.distributed: NCCL over NVLink on the GPUs), and the order of kernel calls.  All arithmetic is
+done by an `ops` object; the product one is `CudaOps` (ctypes -> libtransmil_b200.so, no fallback).  The `ops` seam
+exists so that the world_size-2 gloo test on CPU can drive the very same host logic with a torch restatement that lives
+under tests/ (never imported from here).
+"""
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import capi
+
+LM, HEADS, DHEAD, DIM = 256, 8, 64, 512
+
+
+def bag_plan(n):
+    """Index contract of one bag, same integers as tm_make_plan (TransMIL.py:177-179,184-186; nystrom-attention pad)."""
+    G = int(np.ceil(np.sqrt(n)))
+    N = G * G
+    S = N + 1
+    rem = S % LM
+    P = LM - rem if rem else 0
+    return dict(n=n, G=G, N=N, dup=N - n, S=S, l=math.ceil(S / LM), Sp=S + P, P=P, padding=P)
+
+
+class RankShard:
+    """What one rank owns.  rows: padded rows [row0,row1); seq positions [s0,s1) (0 = cls); tokens [tok0,tok1)."""
+
+    def __init__(self, plan, row0, row1, rank, world):
+        p = plan
+        self.rank, self.world = rank, world
+        self.row0, self.row1, self.rows = row0, row1, row1 - row0
+        self.P_local = p["P"] if rank == 0 else 0
+        self.s0, self.s1 = max(row0 - p["P"], 0), row1 - p["P"]
+        self.S_local = self.s1 - self.s0
+        self.has_cls = rank == 0
+        self.tok0, self.tok1 = max(self.s0 - 1, 0), self.s1 - 1
+        self.ntok = self.tok1 - self.tok0
+        G, n = p["G"], p["n"]
+        # rows of x this rank projects: its tokens t < n are x[t]; tokens t >= n are the duplicate pad x[t - n]
+        self.x_ranges = []
+        if self.tok0 < n:
+            self.x_ranges.append((self.tok0, min(self.tok1, n)))
+        if self.tok1 > n:
+            self.x_ranges.append((max(self.tok0, n) - n, self.tok1 - n))
+        # PPEG: whole image rows [y_in0, y_in1) = own rows + 3-row halo
+        self.y_in0 = max(0, self.tok0 // G - 3)
+        self.y_in1 = min(G, (self.tok1 - 1) // G + 4)
+        self.halo_lo = self.tok0 - self.y_in0 * G        # tokens needed from lower ranks
+        self.halo_hi = self.y_in1 * G - self.tok1        # tokens needed from higher ranks
+
+
+class ShardPlan:
+    def __init__(self, n, world):
+        self.p = p = bag_plan(n)
+        self.world = world
+        l = p["l"]
+        if l < world:
+            raise ValueError(f"a bag of {n} patches has only {l} blocks of 256 padded rows: cannot shard over {world} ranks")
+        cuts = [256 * ((l * r) // world) for r in range(world + 1)]
+        self.shards = [RankShard(p, cuts[r], cuts[r + 1], r, world) for r in range(world)]
+        for r, s in enumerate(self.shards):
+            lo_ok = s.halo_lo == 0 or (r > 0 and s.halo_lo <= self.shards[r - 1].ntok)
+            hi_ok = s.halo_hi == 0 or (r + 1 < world and s.halo_hi <= self.shards[r + 1].ntok)
+            if not (lo_ok and hi_ok and s.rows >= 32):
+                raise ValueError(f"a bag of {n} patches is too small to shard over {world} ranks "
+                                 f"(the PPEG halo of rank {r} would span more than one neighbour)")
+
+    def take(self, x, rank):
+        """The rows of the full bag x [n,D] (or [1,n,D]) that `rank` has to hold: concatenation of its x_ranges."""
+        if x.dim() == 3:
+            x = x[0]
+        return torch.cat([x[a:b] for a, b in self.shards[rank].x_ranges], dim=0)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+class CudaOps:
+    """Arithmetic of the sharded path on the current CUDA device: every method is one (or a few) C-ABI calls."""
+
+    def __init__(self, model):
+        self.m = model
+        self.L = capi.lib()
+        self.dev = model.cls_token.device
+        if self.dev.type != "cuda":
+            raise capi.TransmilError("token-sharded TransMIL needs the model on a CUDA device; there is no CPU path")
+        self.flags = capi.TM_FLAG_TF32_OPERANDS | capi.TM_FLAG_F16_ACT
+        self.w = model._weights()
+        self._st = lambda: torch.cuda.current_stream(self.dev).cuda_stream
+        # operand copies of the GEMM weights (what tm_transmil_fwd derives into its workspace)
+        self._keep = []
+        f = model._fc1
+        self.w.fc1_w0 = self._tf32(f[0].weight)
+        if model._fc1_kind == capi.TM_FC1_2048:
+            self.w.fc1_w1 = self._tf32(f[3].weight)
+        elif model._fc1_kind == capi.TM_FC1_768:
+            self.w.fc1_w1 = self._tf32(f[4].weight)
+        self.layers = {}
+        for name in ("layer1", "layer2"):
+            layer = getattr(model, name)
+            self.layers[name] = dict(
+                norm_w=layer.norm.weight, norm_b=layer.norm.bias, qkv16=self._f16(layer.attn.to_qkv.weight),
+                out16=self._f16(layer.attn.to_out[0].weight), out_b=layer.attn.to_out[0].bias, conv_w=layer.attn.res_conv.weight)
+        self.packed = self.f32(50 * DIM)
+        self.pinv_scratch = self.f32(int(self.L.tm_pinv_scratch_floats(1)))
+
+    # -- small helpers
+    def f32(self, *shape):
+        return torch.empty(*shape, dtype=torch.float32, device=self.dev)
+
+    def f16(self, *shape):
+        return torch.empty(*shape, dtype=torch.float16, device=self.dev)
+
+    def _tf32(self, wt):
+        out = torch.empty_like(wt)
+        capi.check(self.L.tm_round_tf32(wt.data_ptr(), out.data_ptr(), wt.numel(), self._st()))
+        self._keep.append(out)
+        return out.data_ptr()
+
+    def _f16(self, wt):
+        out = torch.empty(wt.shape, dtype=torch.float16, device=self.dev)
+        capi.check(self.L.tm_cvt_f16(wt.data_ptr(), out.data_ptr(), wt.numel(), self._st()))
+        return out
+
+    def to_device(self, x):
+        return x.to(device=self.dev, dtype=torch.float32, non_blocking=True).contiguous()
+
+    def comm_buffer(self, *shape, dtype=torch.float32):
+        return torch.empty(*shape, dtype=dtype, device=self.dev)
+
+    # -- kernels
+    def fc1_rows(self, x_rows, out):
+        rows = x_rows.shape[0]
+        f0 = {capi.TM_FC1_2048: 1024, capi.TM_FC1_768: 768}.get(self.m._fc1_kind, 0)
+        scratch = self.f32(rows * f0) if f0 else None
+        capi.check(self.L.tm_fc1_rows_fwd(C.byref(self.w), x_rows.data_ptr(), rows, out.data_ptr(),
+                                          scratch.data_ptr() if f0 else 0, self.flags, self._st()))
+
+    def cls_row(self, out_row):
+        out_row.copy_(self.m.cls_token.detach().view(DIM))
+
+    def ln_pad(self, h, name, S_local, P_local):
+        lw = self.layers[name]
+        xn = self.f16(S_local + P_local, DIM)
+        capi.check(self.L.tm_ln_pad_fwd(h.data_ptr(), lw["norm_w"].data_ptr(), lw["norm_b"].data_ptr(), 1, S_local, P_local,
+                                        xn.data_ptr(), self.flags, self._st()))
+        return xn
+
+    def qkv(self, xn, name):
+        rows = xn.shape[0]
+        q, k, v = self.f16(HEADS, rows, DHEAD), self.f16(HEADS, rows, DHEAD), self.f16(HEADS, rows, DHEAD)
+        capi.check(self.L.tm_qkv16_fwd(xn.data_ptr(), self.layers[name]["qkv16"].data_ptr(), 1, rows, q.data_ptr(), k.data_ptr(),
+                                       v.data_ptr(), self.flags, self._st()))
+        return q, k, v
+
+    def v_edges(self, v):
+        return v[:, :16].contiguous(), v[:, -16:].contiguous()
+
+    def landmark_sums(self, q, k, row0, l, sums):
+        capi.check(self.L.tm_landmark_sums16_fwd(q.data_ptr(), k.data_ptr(), 1, q.shape[1], row0, l, sums.data_ptr(), self._st()))
+
+    def landmark_finish(self, sums, l):
+        lm = dict(q_lm=self.f32(HEADS, LM, DHEAD), k_lm=self.f32(HEADS, LM, DHEAD), qlm16=self.f16(HEADS, LM, DHEAD),
+                  klm16=self.f16(HEADS, LM, DHEAD))
+        capi.check(self.L.tm_landmark_finish_fwd(sums.data_ptr(), 1, l, lm["q_lm"].data_ptr(), lm["k_lm"].data_ptr(),
+                                                 lm["qlm16"].data_ptr(), lm["klm16"].data_ptr(), self._st()))
+        return lm
+
+    def pinv(self, lm):
+        attn2, Z = self.f32(HEADS, LM, LM), self.f32(HEADS, LM, LM)
+        capi.check(self.L.tm_pinv_fwd(lm["q_lm"].data_ptr(), lm["k_lm"].data_ptr(), 1, attn2.data_ptr(), Z.data_ptr(),
+                                      self.pinv_scratch.data_ptr(), self.flags, self._st()))
+        return Z
+
+    def partial_floats(self):
+        return int(self.L.tm_attn3v_partial_floats(1))
+
+    def attn3v_partial(self, lm, k, v, partial):
+        rows = k.shape[1]
+        scratch = self.f32(int(self.L.tm_attn3v_tc_scratch_floats(1, rows)))
+        capi.check(self.L.tm_attn3v_tc_partial_fwd(lm["qlm16"].data_ptr(), k.data_ptr(), v.data_ptr(), 1, rows, partial.data_ptr(),
+                                                   scratch.data_ptr(), self._st()))
+
+    def attn3v_merge(self, gathered, world):
+        W3 = self.f32(HEADS, LM, DHEAD)
+        capi.check(self.L.tm_attn3v_merge_fwd(gathered.data_ptr(), world, 1, W3.data_ptr(), self._st()))
+        return W3
+
+    def zw(self, Z, W3):
+        M, mt16 = self.f32(HEADS, LM, DHEAD), self.f16(HEADS, DHEAD, LM)
+        capi.check(self.L.tm_zw16_fwd(Z.data_ptr(), W3.data_ptr(), 1, M.data_ptr(), mt16.data_ptr(), self._st()))
+        return mt16
+
+    def nystrom_out(self, q, lm, mt16, v, name):
+        rows = q.shape[1]
+        merged = self.f16(rows, DIM)
+        capi.check(self.L.tm_nystrom_out_tc_fwd(q.data_ptr(), lm["klm16"].data_ptr(), mt16.data_ptr(), v.data_ptr(),
+                                                self.layers[name]["conv_w"].data_ptr(), 1, rows, merged.data_ptr(), self.flags,
+                                                self._st()))
+        return merged
+
+    def conv_halo_fix(self, merged, v_prev, v_next, name):
+        capi.check(self.L.tm_conv_halo_fix_fwd(v_prev.data_ptr() if v_prev is not None else 0,
+                                               v_next.data_ptr() if v_next is not None else 0,
+                                               self.layers[name]["conv_w"].data_ptr(), 1, merged.shape[0], merged.data_ptr(),
+                                               self._st()))
+
+    def to_out(self, merged, name, h_in, S_local, P_local, h_out):
+        lw = self.layers[name]
+        capi.check(self.L.tm_to_out_residual_fwd(merged.data_ptr(), lw["out16"].data_ptr(), lw["out_b"].data_ptr(), h_in.data_ptr(),
+                                                 1, S_local, P_local, h_out.data_ptr(), self.flags, self._st()))
+
+    def ppeg_rows(self, in_rows, y_in0, y_in1, G, tok0, tok1, out):
+        capi.check(self.L.tm_ppeg_rows_fwd(C.byref(self.w), in_rows.data_ptr(), y_in0, y_in1, G, tok0, tok1, out.data_ptr(),
+                                           self.packed.data_ptr(), self._st()))
+
+    def head(self, h, S_local):
+        logits = self.f32(1, self.m.n_classes)
+        capi.check(self.L.tm_head_fwd(C.byref(self.w), h.data_ptr(), 1, S_local, logits.data_ptr(), self._st()))
+        return logits
+
+    def empty_logits(self):
+        return self.f32(1, self.m.n_classes)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def _exchange(rank, world, send_lo=None, send_hi=None, recv_lo=None, recv_hi=None):
+    """Neighbour exchange along the token axis: send_lo -> rank-1, send_hi -> rank+1, recv_lo <- rank-1, recv_hi <- rank+1.
+    Returns the outstanding requests (wait on them before touching the recv buffers)."""
+    p2p = []
+    if rank > 0:
+        if send_lo is not None:
+            p2p.append(dist.P2POp(dist.isend, send_lo, rank - 1))
+        if recv_lo is not None:
+            p2p.append(dist.P2POp(dist.irecv, recv_lo, rank - 1))
+    if rank + 1 < world:
+        if send_hi is not None:
+            p2p.append(dist.P2POp(dist.isend, send_hi, rank + 1))
+        if recv_hi is not None:
+            p2p.append(dist.P2POp(dist.irecv, recv_hi, rank + 1))
+    return dist.batch_isend_irecv(p2p) if p2p else []
+
+
+def _all_gather(gathered, mine):
+    if dist.get_backend() == "nccl":
+        dist.all_gather_into_tensor(gathered, mine)
+    else:
+        dist.all_gather(list(gathered.unbind(0)), mine)
+
+
+def _layer(ops, plan, sh, name, h_in, h_out):
+    """One TransLayer (TransMIL.py:45-57) on this rank's rows; 1 allreduce + 1 allgather + 1 neighbour exchange."""
+    rank, world, l = sh.rank, sh.world, plan.p["l"]
+    xn = ops.ln_pad(h_in, name, sh.S_local, sh.P_local)
+    q, k, v = ops.qkv(xn, name)
+    first, last = ops.v_edges(v)
+    v_prev = ops.comm_buffer(*first.shape, dtype=first.dtype) if rank > 0 else None
+    v_next = ops.comm_buffer(*first.shape, dtype=first.dtype) if rank + 1 < world else None
+    reqs = _exchange(rank, world, send_lo=first, send_hi=last, recv_lo=v_prev, recv_hi=v_next)
+    sums = ops.comm_buffer(2, HEADS, LM, DHEAD)
+    ops.landmark_sums(q, k, sh.row0, l, sums)
+    dist.all_reduce(sums)
+    lm = ops.landmark_finish(sums, l)
+    Z = ops.pinv(lm)                                   # replicated: same inputs, same bits on every rank
+    pf = ops.partial_floats()
+    partial = ops.comm_buffer(pf)
+    ops.attn3v_partial(lm, k, v, partial)
+    gathered = ops.comm_buffer(world, pf)
+    _all_gather(gathered, partial)
+    W3 = ops.attn3v_merge(gathered, world)
+    M = ops.zw(Z, W3)
+    merged = ops.nystrom_out(q, lm, M, v, name)
+    for r in reqs:
+        r.wait()
+    ops.conv_halo_fix(merged, v_prev, v_next, name)
+    ops.to_out(merged, name, h_in, sh.S_local, sh.P_local, h_out)
+
+
+def sharded_forward(ops, plan, x_local):
+    """TransMIL.forward (TransMIL.py:167-211) of ONE bag over the default process group.
+
+    x_local: this rank's rows of the bag, `plan.take(x, rank)` ([ntok, D], host or device).  Returns logits [1, n_classes]
+    on every rank."""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    if world != plan.world:
+        raise ValueError(f"plan was made for {plan.world} ranks, the process group has {world}")
+    sh, p = plan.shards[rank], plan.p
+    off = 1 if sh.has_cls else 0
+    x_local = ops.to_device(x_local)
+    if tuple(x_local.shape[:1]) != (sh.ntok,):
+        raise ValueError(f"rank {rank} expects {sh.ntok} rows of the bag (plan.take), got {tuple(x_local.shape)}")
+    # fc1 + (implicit) duplicate pad + cls  (TransMIL.py:175-186)
+    h0 = ops.f32(sh.S_local, DIM)
+    ops.fc1_rows(x_local, h0[off:])
+    if sh.has_cls:
+        ops.cls_row(h0[0])
+    # layer 1 writes into a buffer with room for the PPEG halos on both sides
+    lo, hi = sh.halo_lo, sh.halo_hi
+    ext = ops.f32(lo + sh.S_local + hi, DIM)
+    h1 = ext[lo:lo + sh.S_local]
+    _layer(ops, plan, sh, "layer1", h0, h1)
+    # PPEG halo: my last tokens go up, my first tokens go down (TransMIL.py:60-75 on the G x G token image)
+    n_up = plan.shards[rank + 1].halo_lo if rank + 1 < world else 0
+    n_dn = plan.shards[rank - 1].halo_hi if rank > 0 else 0
+    toks = h1[off:]
+    reqs = _exchange(rank, world,
+                     send_lo=toks[:n_dn] if n_dn else None, send_hi=toks[sh.ntok - n_up:] if n_up else None,
+                     recv_lo=ext[:lo] if lo else None, recv_hi=ext[lo + sh.S_local:] if hi else None)
+    for r in reqs:
+        r.wait()
+    h2 = ops.f32(sh.S_local, DIM)
+    ops.ppeg_rows(ext[off:], sh.y_in0, sh.y_in1, p["G"], sh.tok0, sh.tok1, h2[off:])
+    if sh.has_cls:
+        h2[0].copy_(h1[0])
+    h3 = ops.f32(sh.S_local, DIM)
+    _layer(ops, plan, sh, "layer2", h2, h3)
+    # final norm + head on the cls row (TransMIL.py:202-204), rank 0; everyone gets the logits
+    logits = ops.head(h3, sh.S_local) if sh.has_cls else ops.empty_logits()
+    dist.broadcast(logits, 0)
+    return logits
+
+
+class TokenShardedTransMIL:
+    """`TokenShardedTransMIL(model)(x)`: the drop-in module's forward for ONE bag, token-sharded over the default process
+    group (one process per GPU).  `x` is the full bag [n,D] / [1,n,D] on every rank (host or device) or, with `n=...`, this
+    rank's rows only (`plan(n).take(x, rank)`) -- the form a sharded loader would hand over."""
+
+    def __init__(self, model):
+        if model.training:
+            raise NotImplementedError("token-sharded path: inference only (model.eval())")
+        self.model = model
+        self.ops = CudaOps(model)
+        self._plans = {}
+
+    def plan(self, n):
+        key = (int(n), dist.get_world_size())
+        if key not in self._plans:
+            self._plans[key] = ShardPlan(*key)
+        return self._plans[key]
+
+    @torch.no_grad()
+    def __call__(self, x, n=None):
+        if n is None:
+            if x.dim() == 3:
+                if x.shape[0] != 1:
+                    raise ValueError("token sharding is for a single bag (B = 1); batch whole bags across ranks instead")
+                x = x[0]
+            plan = self.plan(x.shape[0])
+            x = plan.take(x, dist.get_rank())
+        else:
+            plan = self.plan(n)
+        with torch.cuda.device(self.ops.dev):
+            return sharded_forward(self.ops, plan, x)
