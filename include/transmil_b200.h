@@ -60,6 +60,9 @@ typedef enum tm_fc1_kind {
 #define TM_FLAG_PINV_GEMM_CHAIN 8u /* run the pinv chain as 24 batched tcgen05 GEMM launches (tf32 operands) instead of the
                                     single 4-CTA-cluster kernel (fp16 operands); kept for cross-checking */
 
+#define TM_FLAG_NO_OVERLAP 32u      /* tm_transmil_fwd: keep every stage on the caller's stream (no fork of the pinv chain
+                                    onto the library's side stream while attn3.v runs) */
+
 /* Index contract of one bag (TransMIL.py:177-179,184-186,190-193 and the
  * nystrom-attention 0.0.11 front pad / landmark grouping).  Pure host code. */
 typedef struct tm_plan {

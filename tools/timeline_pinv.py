@@ -1,0 +1,19 @@
+"""Per-step clock64 timeline of pinv_cluster_kernel (build with TM_EXTRA_NVCC_FLAGS=-DTM_PINV_TIMELINE)."""
+import sys, torch
+sys.path.insert(0, '/root/repo')
+import transmil_b200 as T
+L = T.capi.lib()
+g = torch.Generator().manual_seed(0)
+qlm = (torch.randn(1, 8, 256, 64, generator=g) * 0.3).cuda()
+klm = (torch.randn(1, 8, 256, 64, generator=g) * 0.3).cuda()
+attn2 = torch.empty(1, 8, 256, 256, device="cuda"); Z = torch.empty_like(attn2)
+scratch = torch.empty(int(L.tm_pinv_scratch_floats(1)), device="cuda")
+st = torch.cuda.current_stream().cuda_stream
+for i in range(3):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    T.capi.check(L.tm_pinv_fwd(qlm.data_ptr(), klm.data_ptr(), 1, attn2.data_ptr(), Z.data_ptr(), scratch.data_ptr(), 0, st))
+    e1.record(); torch.cuda.synchronize()
+    print("pinv ms", e0.elapsed_time(e1), flush=True)
+A = attn2[0, 0].double(); Zd = Z[0, 0].double()
+print("||AZA-A||/||A||", float((A @ Zd @ A - A).norm() / A.norm()))

@@ -260,7 +260,7 @@ extern "C" int64_t tm_attn3v_tc_scratch_floats(int64_t B, int64_t Sp) {
 // partial == NULL: W3 = normalised result.  partial != NULL: the rank-level (max [nbh,256], sum [nbh,256], numerator
 // [nbh,256,64]) triple is written there, unnormalised, and W3 is not touched.
 static int attn3v_tc_run(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3, float* partial,
-                         float* scratch, void* stream) {
+                         float* scratch, void* stream, int reserved_sms = 0) {
   using namespace tmil;
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE, "tm_attn3v_tc_fwd: Sp must be a multiple of 256 (Sp=%lld)", (long long)Sp);
   TM_CHECK_ARG(qlm16 && k16 && v16 && (W3 || partial) && scratch, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_fwd: NULL pointer");
@@ -277,7 +277,14 @@ static int attn3v_tc_run(const void* qlm16, const void* k16, const void* v16, in
     attr_done = true;
   }
   const int tiles_per_bh = (int)(Sp / A3_TOK);
-  const int chunks = attn_chunks(nbh, tiles_per_bh);
+  int chunks = attn_chunks(nbh, tiles_per_bh);
+  if (reserved_sms > 0) {   // another kernel of the same forward holds `reserved_sms` SMs: stay a single wave on the rest
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int c = (int)((sms - reserved_sms) / nbh);
+    if (c >= 1 && c < chunks) chunks = c;
+  }
   const int tpc = (int)ceil_div(tiles_per_bh, chunks);
   const int used = (int)ceil_div(tiles_per_bh, tpc);
   float* pm = scratch;
@@ -301,6 +308,14 @@ extern "C" int tm_attn3v_tc_fwd(const void* qlm16, const void* k16, const void* 
   TM_CHECK_ARG(W3 != nullptr, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_fwd: NULL pointer");
   return attn3v_tc_run(qlm16, k16, v16, B, Sp, W3, nullptr, scratch, stream);
 }
+
+namespace tmil {
+// tm_attn3v_tc_fwd sized to leave `reserved_sms` SMs to a concurrently running kernel (forward.cu: the pinv cluster kernel).
+int attn3v_tc_fwd_budget(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3, float* scratch,
+                         int reserved_sms, cudaStream_t st) {
+  return attn3v_tc_run(qlm16, k16, v16, B, Sp, W3, nullptr, scratch, st, reserved_sms);
+}
+}  // namespace tmil
 
 extern "C" int64_t tm_attn3v_partial_floats(int64_t B) { return B * TM_HEADS * TM_LANDMARKS * (TM_DHEAD + 2); }
 

@@ -15,6 +15,12 @@ void count_launch(int n = 1);
 enum Stage : int { ST_FC1_GEMM0 = 0, ST_FC1_LN, ST_FC1_GEMM1, ST_FC1_TAIL, ST_LN_PAD, ST_QKV, ST_LANDMARKS, ST_PINV, ST_ATTN3V,
                    ST_ZW, ST_NYSTROM_OUT, ST_TO_OUT, ST_PPEG, ST_HEAD, ST_END, ST_COUNT };
 void prof_mark(int stage, cudaStream_t st);
+bool prof_enabled();
+// Library-owned high-priority side stream of the current device plus a fork/join event pair (created on first use): lets
+// two independent stages of one forward run concurrently on disjoint SMs.  Fork/join through events, so the pattern is also
+// legal inside a stream capture.
+struct SideStream { cudaStream_t stream; cudaEvent_t fork, join; };
+int side_stream(SideStream* out);
 
 #define TM_CHECK_ARG(cond, code, ...)  \
   do {                                 \

@@ -8,6 +8,8 @@ extern "C" int64_t tm_pinv_scratch_floats(int64_t B);
 
 namespace tmil {
 
+int attn3v_tc_fwd_budget(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3, float* scratch,
+                         int reserved_sms, cudaStream_t st);
 int ln_inplace(float* x, const float* gamma, const float* beta, long long rows, int width, int rpb, long long bag_rows,
                int off, bool round, cudaStream_t st);
 
@@ -119,10 +121,27 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
     TM_PROPAGATE(tm_qkv16_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, flags, st));
     prof_mark(ST_LANDMARKS, st);
     TM_PROPAGATE(tm_landmarks16_fwd(q16, k16, B, p.Sp, p.l, q_lm, k_lm, qlm16, klm16, st));
-    prof_mark(ST_PINV, st);
-    TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, st));
-    prof_mark(ST_ATTN3V, st);
-    TM_PROPAGATE(tm_attn3v_tc_fwd(qlm16, k16, v16, B, p.Sp, W3, ws + L.a3_s, flags, st));
+    // sim2 + pinv (32 CTAs per bag, a latency-bound chain of 24 dependent products) and attn3.v (every other SM) are
+    // independent: fork the pinv onto the library's high-priority side stream and join before Z.W3.  Serial when the
+    // stage profiler is on (its events live on `st`), when asked (TM_FLAG_NO_OVERLAP), or when the pinv clusters alone
+    // would take more than a third of the SMs (B > 1).
+    const int pinv_sms = 4 * (int)(B * TM_HEADS);
+    const bool overlap = !(flags & (TM_FLAG_NO_OVERLAP | TM_FLAG_PINV_GEMM_CHAIN)) && !prof_enabled() && pinv_sms * 3 <= 148;
+    if (overlap) {
+      SideStream ss;
+      TM_PROPAGATE(side_stream(&ss));
+      TM_CUDA(cudaEventRecord(ss.fork, st));
+      TM_CUDA(cudaStreamWaitEvent(ss.stream, ss.fork, 0));
+      TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, ss.stream));
+      TM_CUDA(cudaEventRecord(ss.join, ss.stream));
+      TM_PROPAGATE(attn3v_tc_fwd_budget(qlm16, k16, v16, B, p.Sp, W3, ws + L.a3_s, pinv_sms, st));
+      TM_CUDA(cudaStreamWaitEvent(st, ss.join, 0));
+    } else {
+      prof_mark(ST_PINV, st);
+      TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, st));
+      prof_mark(ST_ATTN3V, st);
+      TM_PROPAGATE(tm_attn3v_tc_fwd(qlm16, k16, v16, B, p.Sp, W3, ws + L.a3_s, flags, st));
+    }
     prof_mark(ST_ZW, st);
     TM_PROPAGATE(tm_zw16_fwd(Z, W3, B, M, mt16, st));
     prof_mark(ST_NYSTROM_OUT, st);

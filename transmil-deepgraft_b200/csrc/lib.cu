@@ -2,6 +2,7 @@
 #include <math.h>
 #include <stdarg.h>
 
+#include <mutex>
 #include <utility>
 #include <vector>
 
@@ -31,6 +32,26 @@ void prof_mark(int stage, cudaStream_t st) {
   else if (cudaEventCreate(&ev) != cudaSuccess) return;
   cudaEventRecord(ev, st);
   g_marks.emplace_back(stage, ev);
+}
+bool prof_enabled() { return g_prof_on; }
+
+static std::mutex g_side_mutex;
+static std::vector<std::pair<int, SideStream>> g_side;
+int side_stream(SideStream* out) {
+  int dev = 0;
+  TM_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_side_mutex);
+  for (auto& e : g_side)
+    if (e.first == dev) { *out = e.second; return TM_OK; }
+  SideStream s;
+  int lo = 0, hi = 0;
+  TM_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  TM_CUDA(cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, hi));
+  TM_CUDA(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
+  TM_CUDA(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
+  g_side.emplace_back(dev, s);
+  *out = s;
+  return TM_OK;
 }
 }  // namespace tmil
 

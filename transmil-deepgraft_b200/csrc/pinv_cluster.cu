@@ -47,6 +47,12 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
   uint64_t* mma_done = bars + 8;  // accumulator of the step complete
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
+#ifdef TM_PINV_TIMELINE
+  __shared__ long long tl[PC_STEPS][8];   // per step: producer barrier exit, B issued | mma: barrier exit, B[3] full, issued | epi: barrier exit, mma_done, stores done
+#define TL(s, i) tl[s][i] = clock64()
+#else
+#define TL(s, i)
+#endif
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = blockIdx.x;          // cluster spans gridDim.x = 4
   const int mi = rank >> 1, ni = rank & 1;
@@ -91,11 +97,13 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
     for (int s = 0; s < PC_STEPS; ++s) {
       cluster_sync_all();
       if (lane == 0) {
+        TL(s, 0);
         fence_proxy_async_all();
         const int it = s >> 2, g = s & 3;
         const CUtensorMap* zc = (it & 1) ? &maps.Zb : &maps.Za;
         if (g == 1) loadA(&maps.XZ);
         loadB(g == 0 ? zc : (g == 1 ? &maps.XZ : (g == 2 ? &maps.T1 : &maps.T2)));
+        TL(s, 1);
         if (g == 2) {                       // next A operand = Z rows: independent of the step in flight
           mbar_wait(mma_done, s & 1);
           loadA(zc);
@@ -113,12 +121,15 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
     for (int s = 0; s < PC_STEPS; ++s) {
       cluster_sync_all();
       if (lane == 0) {
+        TL(s, 2);
         tc_fence_after();
         const bool newA = (s & 3) != 2;
 #pragma unroll
         for (int kc = 0; kc < 4; ++kc) {
           if (newA) mbar_wait(&fullA[kc], nA & 1);
           mbar_wait(&fullB[kc], s & 1);
+          if (kc == 0) { TL(s, 6); }
+          if (kc == 3) { TL(s, 3); }
           tc_fence_after();
 #pragma unroll
           for (int k4 = 0; k4 < 4; ++k4) {
@@ -132,6 +143,7 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
           }
         }
         umma_commit(mma_done);
+        TL(s, 4);
         if (newA) ++nA;
       }
       __syncwarp();
@@ -157,6 +169,7 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
       const bool last = s == PC_STEPS - 1;
       __half* dst = g == 0 ? XZ : (g == 1 ? T1 : (g == 2 ? T2 : ((it & 1) ? Za : Zb)));
       mbar_wait(mma_done, s & 1);
+      if (threadIdx.x == 64) { TL(s, 5); }
       tc_fence_after();
 #pragma unroll
       for (int ch = 0; ch < 4; ++ch) {
@@ -195,9 +208,18 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
       }
       tc_fence_before();           // TMEM reads retire before the next step's MMA overwrites the accumulator
       fence_proxy_async_all();     // generic-proxy global stores -> visible to the peers' TMA (async proxy) loads
+      if (threadIdx.x == 64) { TL(s, 7); }
     }
   }
   cluster_sync_all();
+#ifdef TM_PINV_TIMELINE
+  if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
+    const long long t0 = tl[0][0];
+    for (int s = 0; s < 12; ++s)
+      printf("step %2d g%d | tma: bar_exit %6lld issued %6lld | mma: bar_exit %6lld B0_full %6lld B3_full %6lld committed %6lld | epi: mma_done %6lld stored %6lld\n",
+             s, s & 3, tl[s][0] - t0, tl[s][1] - t0, tl[s][2] - t0, tl[s][6] - t0, tl[s][3] - t0, tl[s][4] - t0, tl[s][5] - t0, tl[s][7] - t0);
+  }
+#endif
   tc_fence_after();
   if (warp == 2) tmem_dealloc(tmem_base, 128);
 }
