@@ -20,6 +20,13 @@ class OracleOps:
     def comm_buffer(self, *shape, dtype=torch.float32):
         return torch.zeros(*shape, dtype=dtype)
 
+    def side_stream(self):
+        import contextlib
+        return contextlib.nullcontext()
+
+    def join_side_stream(self):
+        pass
+
     def to_device(self, x):
         return x.float().contiguous()
 

@@ -5,10 +5,12 @@ Layout (only what the path needs):
   capi.py       ctypes binding of include/transmil_b200.h
   transmil.py   host-side mirror of the reference plugin interface (models.TransMIL)
   plugin.py     the reference's "model name -> models/<name>.py class" loader
-  shard.py      bag-data-parallel / token-shard planning over torch.distributed
+  sharded.py    token-sharded forward of one giant bag over torch.distributed (NCCL)
+  ingest.py     slide-at-a-time inference loop with the next bag's H2D copy hidden behind the current forward
   build.py      nvcc build of the shared library
 """
 from . import capi
+from .ingest import StreamedInference
 from .transmil import LazyAttention, NystromAttention, PPEG, TransLayer, TransMIL, y_prob_y_hat
 
-__all__ = ["capi", "TransMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat"]
+__all__ = ["capi", "TransMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]

@@ -106,6 +106,7 @@ class CudaOps:
         self._st = lambda: torch.cuda.current_stream(self.dev).cuda_stream
         # operand copies of the GEMM weights (what tm_transmil_fwd derives into its workspace)
         self._keep = []
+        self._side = None
         f = model._fc1
         self.w.fc1_w0 = self._tf32(f[0].weight)
         if model._fc1_kind == capi.TM_FC1_2048:
@@ -144,6 +145,16 @@ class CudaOps:
 
     def comm_buffer(self, *shape, dtype=torch.float32):
         return torch.empty(*shape, dtype=dtype, device=self.dev)
+
+    def side_stream(self):
+        """Context: kernels launched inside run on a high-priority side stream forked from the current stream."""
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.dev, priority=-1)
+        self._side.wait_stream(torch.cuda.current_stream(self.dev))
+        return torch.cuda.stream(self._side)
+
+    def join_side_stream(self):
+        torch.cuda.current_stream(self.dev).wait_stream(self._side)
 
     # -- kernels
     def fc1_rows(self, x_rows, out):
@@ -278,13 +289,15 @@ def _layer(ops, plan, sh, name, h_in, h_out):
     ops.landmark_sums(q, k, sh.row0, l, sums)
     dist.all_reduce(sums)
     lm = ops.landmark_finish(sums, l)
-    Z = ops.pinv(lm)                                   # replicated: same inputs, same bits on every rank
+    with ops.side_stream():                            # the latency-bound pinv chain runs beside attn3.v (own SMs)
+        Z = ops.pinv(lm)                               # replicated: same inputs, same bits on every rank
     pf = ops.partial_floats()
     partial = ops.comm_buffer(pf)
     ops.attn3v_partial(lm, k, v, partial)
     gathered = ops.comm_buffer(world, pf)
     _all_gather(gathered, partial)
     W3 = ops.attn3v_merge(gathered, world)
+    ops.join_side_stream()
     M = ops.zw(Z, W3)
     merged = ops.nystrom_out(q, lm, M, v, name)
     for r in reqs:
