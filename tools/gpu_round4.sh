@@ -1,0 +1,13 @@
+#!/bin/bash
+set -x
+mkdir -p gpurun_out
+timeout 120 python tools/timeline_pinv.py > gpurun_out/pinv_check.log 2>&1; echo "pinv check exit $?"; cat gpurun_out/pinv_check.log
+grep -q "max|Z" gpurun_out/pinv_check.log || exit 1
+timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
+tail -8 gpurun_out/pytest_gpu.log
+timeout 300 python bench.py --steps 20 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"
+python -c "
+import json; d=json.loads(open('gpurun_out/bench.json').read().strip().splitlines()[-1]); print(d['ms_per_step'], d['stage_pass_ms_per_step'], d['e2e'], d['clocks'], d.get('parity')); print({k:(v['ms_per_launch'],v['frac']) for k,v in d['stages'].items()})"
+timeout 600 python tools/sweep.py > gpurun_out/sweep.jsonl 2> gpurun_out/sweep.err; cat gpurun_out/sweep.jsonl; tail -3 gpurun_out/sweep.err
+TM_EXTRA_NVCC_FLAGS=-DTM_PINV_TIMELINE python transmil-deepgraft_b200/build.py --force > gpurun_out/build_tl.log 2>&1
+timeout 120 python tools/timeline_pinv.py > gpurun_out/timeline_pinv.log 2>&1; head -14 gpurun_out/timeline_pinv.log; tail -4 gpurun_out/timeline_pinv.log

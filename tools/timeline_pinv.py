@@ -17,3 +17,12 @@ for i in range(3):
     print("pinv ms", e0.elapsed_time(e1), flush=True)
 A = attn2[0, 0].double(); Zd = Z[0, 0].double()
 print("||AZA-A||/||A||", float((A @ Zd @ A - A).norm() / A.norm()))
+# reference: the same 6 iterations in fp32 torch on the kernel's own attn2
+A = attn2[0]
+absA = A.abs()
+Zr = A.transpose(-1, -2) / (absA.sum(-1).max() * absA.sum(-2).max())
+I = torch.eye(256, device="cuda")[None]
+for _ in range(6):
+    XZ = A @ Zr
+    Zr = 0.25 * Zr @ (13 * I - XZ @ (15 * I - XZ @ (7 * I - XZ)))
+print("max|Z - Z_ref| / max|Z_ref|", float((Z[0] - Zr).abs().max() / Zr.abs().max()))

@@ -101,15 +101,35 @@ __global__ void __launch_bounds__(256) attn3v_combine_kernel(const float* __rest
   const int idx = blockIdx.x * 256 + threadIdx.x;  // (j, d4)
   const int j = idx >> 4, d4 = idx & 15;
   const long long base = (long long)bh * bs_ms + j, obase = (long long)bh * bs_o + (long long)j * TM_DHEAD;
+  // chunks are visited in index order (fixed summation order), eight at a time so that their loads are all in flight
   float M = -INFINITY;
-  for (int c = 0; c < nchunks; ++c) M = fmaxf(M, pm[base + c * cs_ms]);
+  for (int c0 = 0; c0 < nchunks; c0 += 8) {
+    float m8[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) m8[u] = c0 + u < nchunks ? pm[base + (c0 + u) * cs_ms] : -INFINITY;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) M = fmaxf(M, m8[u]);
+  }
   float den = 0.f;
   float4 num = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int c = 0; c < nchunks; ++c) {
-    const float w = expf(pm[base + c * cs_ms] - M);
-    den = fmaf(w, ps[base + c * cs_ms], den);
-    float4 o = reinterpret_cast<const float4*>(pO + obase + c * cs_o)[d4];
-    num.x = fmaf(w, o.x, num.x); num.y = fmaf(w, o.y, num.y); num.z = fmaf(w, o.z, num.z); num.w = fmaf(w, o.w, num.w);
+  for (int c0 = 0; c0 < nchunks; c0 += 8) {
+    float m8[8], s8[8];
+    float4 o8[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const bool ok = c0 + u < nchunks;
+      m8[u] = ok ? pm[base + (c0 + u) * cs_ms] : -INFINITY;
+      s8[u] = ok ? ps[base + (c0 + u) * cs_ms] : 0.f;
+      o8[u] = ok ? reinterpret_cast<const float4*>(pO + obase + (c0 + u) * cs_o)[d4] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (c0 + u < nchunks) {
+        const float w = expf(m8[u] - M);
+        den = fmaf(w, s8[u], den);
+        num.x = fmaf(w, o8[u].x, num.x); num.y = fmaf(w, o8[u].y, num.y); num.z = fmaf(w, o8[u].z, num.z); num.w = fmaf(w, o8[u].w, num.w);
+      }
+    }
   }
   float4* dst = reinterpret_cast<float4*>(W3 + ((long long)bh * TM_LANDMARKS + j) * TM_DHEAD) + d4;
   if (out_m != nullptr) {

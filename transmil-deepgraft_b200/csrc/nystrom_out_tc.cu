@@ -308,20 +308,28 @@ __global__ void __launch_bounds__(256) mt16_kernel(const float* __restrict__ M, 
 
 // M = Z @ W3 in exact fp32 (256x256 @ 256x64 per head) with both consumers' layouts written at once:
 // M [bh][j][d] fp32 (stage buffer) and mt16 [bh][d][j] fp16 (K-major B operand of attn1 @ M).
-// grid (16, B*8): 16 rows per CTA; thread = (row, 4 columns); Z rows staged in smem, W3 streamed through L1/L2.
+// grid (16, B*8): 16 rows per CTA; thread = (row, 4 columns); the CTA's 16 Z rows and the head's whole W3 (64 KB) are
+// staged in shared memory with every load in flight at once -- the kernel sits on the critical path between the pinv /
+// attn3.v join and nystrom_out, so its latency, not its 67 MFLOP, is what counts.
 __global__ void __launch_bounds__(256) zw16_kernel(const float* __restrict__ Z, const float* __restrict__ W3, float* __restrict__ M,
                                                    __half* __restrict__ mt16) {
-  __shared__ __align__(16) float zs[16][TM_LANDMARKS];
+  extern __shared__ __align__(16) float zw_smem[];
+  float* ws = zw_smem;                                   // [256][64]
+  float (*zs)[TM_LANDMARKS] = reinterpret_cast<float (*)[TM_LANDMARKS]>(zw_smem + TM_LANDMARKS * TM_DHEAD);   // [16][256]
   const int bh = blockIdx.y, r0 = blockIdx.x * 16, tid = threadIdx.x;
   const float4* zg = reinterpret_cast<const float4*>(Z + ((long long)bh * TM_LANDMARKS + r0) * TM_LANDMARKS);
-  for (int i = tid; i < 16 * 64; i += 256) reinterpret_cast<float4*>(&zs[0][0])[i] = __ldg(zg + i);
+  const float4* wg = reinterpret_cast<const float4*>(W3 + (long long)bh * TM_LANDMARKS * TM_DHEAD);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(&zs[0][0])[tid + 256 * i] = __ldg(zg + tid + 256 * i);
+#pragma unroll
+  for (int i = 0; i < 16; ++i) reinterpret_cast<float4*>(ws)[tid + 256 * i] = __ldg(wg + tid + 256 * i);
   __syncthreads();
   const int ry = tid >> 4, cx = tid & 15;
-  const float4* wg = reinterpret_cast<const float4*>(W3 + (long long)bh * TM_LANDMARKS * TM_DHEAD) + cx;
+  const float4* wsv = reinterpret_cast<const float4*>(ws) + cx;
   float4 acc0 = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc0;
-#pragma unroll 4
+#pragma unroll 8
   for (int k = 0; k < TM_LANDMARKS; k += 2) {
-    const float4 w0 = __ldg(wg + (long long)k * 16), w1 = __ldg(wg + (long long)(k + 1) * 16);
+    const float4 w0 = wsv[k * 16], w1 = wsv[(k + 1) * 16];
     const float z0 = zs[ry][k], z1 = zs[ry][k + 1];
     acc0.x = fmaf(z0, w0.x, acc0.x); acc0.y = fmaf(z0, w0.y, acc0.y); acc0.z = fmaf(z0, w0.z, acc0.z); acc0.w = fmaf(z0, w0.w, acc0.w);
     acc1.x = fmaf(z1, w1.x, acc1.x); acc1.y = fmaf(z1, w1.y, acc1.y); acc1.z = fmaf(z1, w1.z, acc1.z); acc1.w = fmaf(z1, w1.w, acc1.w);
@@ -364,7 +372,13 @@ extern "C" int tm_mt16_fwd(const float* M, void* mt16, int64_t B, void* stream) 
 extern "C" int tm_zw16_fwd(const float* Z, const float* W3, int64_t B, float* M, void* mt16, void* stream) {
   using namespace tmil;
   TM_CHECK_ARG(Z && W3 && M && mt16 && B > 0, TM_ERR_BAD_ARGUMENT, "tm_zw16_fwd: bad arguments");
-  zw16_kernel<<<dim3(16, (unsigned)(B * TM_HEADS)), 256, 0, (cudaStream_t)stream>>>(Z, W3, M, (__half*)mt16);
+  const size_t smem = (size_t)(TM_LANDMARKS * TM_DHEAD + 16 * TM_LANDMARKS) * sizeof(float);
+  static bool attr_done = false;
+  if (!attr_done) {
+    TM_CUDA(cudaFuncSetAttribute(zw16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_done = true;
+  }
+  zw16_kernel<<<dim3(16, (unsigned)(B * TM_HEADS)), 256, smem, (cudaStream_t)stream>>>(Z, W3, M, (__half*)mt16);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -13,10 +13,10 @@
 namespace tmil {
 
 constexpr int LM = TM_LANDMARKS;   // 256
-constexpr int ROWS = 32;           // rows of attn2 per CTA
+constexpr int ROWS = 16;           // rows of attn2 per CTA (16 threads per row: 128 CTAs per bag)
 constexpr int KLD = 68;            // padded row stride of k_lm in smem (floats)
 
-// grid (LM/ROWS, B*8).  smem: k_lm [256][68] + q rows [32][68] + P tile [32][257]
+// grid (LM/ROWS, B*8).  smem: k_lm [256][68] + q rows [16][68] + P tile [16][257]
 template <bool ROUND>
 __global__ void __launch_bounds__(256) attn2_kernel(const float* __restrict__ q_lm, const float* __restrict__ k_lm,
                                                     float* __restrict__ attn2, float* __restrict__ rowsum,
@@ -37,38 +37,35 @@ __global__ void __launch_bounds__(256) attn2_kernel(const float* __restrict__ q_
     *reinterpret_cast<float4*>(qs + r * KLD + c) = __ldg(reinterpret_cast<const float4*>(qg + r * TM_DHEAD + c));
   }
   __syncthreads();
-  const int r = tid >> 3, cg = tid & 7;   // 8 threads per row, columns cg, cg+8, ...
-  float s[32];
+  const int r = tid >> 4, cg = tid & 15;   // 16 threads per row, columns cg, cg+16, ...
+  float s[16];
 #pragma unroll
-  for (int jj = 0; jj < 32; ++jj) s[jj] = 0.f;
+  for (int jj = 0; jj < 16; ++jj) s[jj] = 0.f;
 #pragma unroll 4
   for (int d = 0; d < TM_DHEAD; d += 4) {
     float4 qv = *reinterpret_cast<const float4*>(qs + r * KLD + d);
 #pragma unroll
-    for (int jj = 0; jj < 32; ++jj) {
-      float4 kv = *reinterpret_cast<const float4*>(ks + (jj * 8 + cg) * KLD + d);
+    for (int jj = 0; jj < 16; ++jj) {
+      float4 kv = *reinterpret_cast<const float4*>(ks + (jj * 16 + cg) * KLD + d);
       s[jj] = fmaf(qv.x, kv.x, s[jj]); s[jj] = fmaf(qv.y, kv.y, s[jj]);
       s[jj] = fmaf(qv.z, kv.z, s[jj]); s[jj] = fmaf(qv.w, kv.w, s[jj]);
     }
   }
   float mx = s[0];
 #pragma unroll
-  for (int jj = 1; jj < 32; ++jj) mx = fmaxf(mx, s[jj]);
-  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+  for (int jj = 1; jj < 16; ++jj) mx = fmaxf(mx, s[jj]);
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   float sum = 0.f;
 #pragma unroll
-  for (int jj = 0; jj < 32; ++jj) { s[jj] = expf(s[jj] - mx); sum += s[jj]; }
-  sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-  sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-  sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+  for (int jj = 0; jj < 16; ++jj) { s[jj] = expf(s[jj] - mx); sum += s[jj]; }
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
   float rs = 0.f;
 #pragma unroll
-  for (int jj = 0; jj < 32; ++jj) { float p = s[jj] / sum; ps[r * 257 + jj * 8 + cg] = p; rs += p; }
-  rs += __shfl_xor_sync(0xffffffffu, rs, 1);
-  rs += __shfl_xor_sync(0xffffffffu, rs, 2);
-  rs += __shfl_xor_sync(0xffffffffu, rs, 4);
+  for (int jj = 0; jj < 16; ++jj) { float p = s[jj] / sum; ps[r * 257 + jj * 16 + cg] = p; rs += p; }
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) rs += __shfl_xor_sync(0xffffffffu, rs, o);
   if (cg == 0) rowsum[(long long)bh * LM + tile * ROWS + r] = rs;   // |x|.sum(-1) (x >= 0)
   __syncthreads();
   float* ag = attn2 + ((long long)bh * LM + tile * ROWS) * LM;
@@ -137,7 +134,8 @@ static int pinv_gemm(const float* L, const float* R, float* C, float alpha, floa
 // One product of the chain on the tensor cores: every iterate is kept in both orientations, so X @ Y is the NT GEMM
 // X . (Y^T)^T with tf32 operands (all stored iterates are tf32-rounded by their producer) and fp32 accumulation;
 // out = alpha * X@Y + beta * L, with L supplied transposed (LT) and the result written as C and/or C^T.
-int pinv_cluster_run(const float* attn2, const float* scale, int nbh, void* scratch16, float* Z, cudaStream_t st);   // pinv_cluster.cu
+int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpart, int nparts, int nbh, void* scratch16, float* Z,
+                     cudaStream_t st);   // pinv_cluster.cu
 
 static int pinv_gemm_tc(const float* X, const float* YT, float alpha, float beta, const float* LT, float* C, float* CT, bool round,
                         int nbh, cudaStream_t st) {
@@ -155,7 +153,7 @@ static int pinv_gemm_tc(const float* X, const float* YT, float alpha, float beta
 
 extern "C" int64_t tm_pinv_scratch_floats(int64_t B) {
   const int64_t nbh = B * TM_HEADS;
-  return 7 * nbh * 65536 + nbh * 256 * 9 + 64;   // tensor-core chain: XZ, XZ^T, T1^T, T2^T, Z', Z^T, Z'^T
+  return 7 * nbh * 65536 + nbh * 256 * (1 + 256 / 16) + 64;   // + rowsum, column partials (one per 16-row CTA), scale   // tensor-core chain: XZ, XZ^T, T1^T, T2^T, Z', Z^T, Z'^T
 }
 
 extern "C" int tm_pinv_fwd(const float* q_lm, const float* k_lm, int64_t B, float* attn2, float* Z, float* scratch,
@@ -188,10 +186,11 @@ extern "C" int tm_pinv_fwd(const float* q_lm, const float* k_lm, int64_t B, floa
   if (tc && !cluster) attn2_kernel<true><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
   else attn2_kernel<false><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
   TM_LAUNCH_CHECK();
+  if (cluster)   // one 4-CTA-cluster kernel for the whole chain (fp16 operands); attn2 stays exact fp32; the global init
+                 // scalar is reduced inside the operand-preparation kernel
+    return pinv_cluster_run(attn2, rowsum, colpart, LM / ROWS, nbh, XZ, Z, st);
   pinv_scale_kernel<<<1, 1024, 0, st>>>(rowsum, colpart, nbh, scale);
   TM_LAUNCH_CHECK();
-  if (cluster)   // one 4-CTA-cluster kernel for the whole chain (fp16 operands); attn2 stays exact fp32
-    return pinv_cluster_run(attn2, scale, nbh, XZ, Z, st);
   if (tc) {
     pinv_z0_kernel<true><<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, scale, Z, ZTa);
     TM_LAUNCH_CHECK();

@@ -8,11 +8,13 @@
 //   A operand = X[128 mi .. +128, :]   K-major   (4 k-blocks of [128 rows][64 k])
 //   B operand = Y[:, 128 ni .. +128]   MN-major  (2 column groups of [256 k rows][64 n]) -- the row-major iterate serves both
 //   roles, so every iterate is stored once, row-major fp16, in global memory (L2 resident: 128 KB each).
-// A product needs blocks written by the other CTAs of the cluster: one hardware cluster barrier per product orders the
-// global stores of step s before the TMA loads of step s+1 (release/acquire + proxy fence); there is no host round trip and
-// no relaunch.  The second term of each update (XZ, Z) is the CTA's own previous output block: it stays in registers as
+// A product needs blocks written by the other CTAs of the cluster.  The epilogue of a step therefore (1) writes the CTA's own
+// block straight into its shared memory in the operand layouts of the next step (its half of B, and of A when the product
+// is XZ), and (2) publishes the block to the peers with a TMA store from a swizzled staging tile; after ONE hardware
+// cluster barrier per product the peers' TMA loads fetch only the half they do not own (32 KB instead of 64 KB per
+// operand), and the MMA starts on the local half while that load is in flight.  There is no host round trip and no relaunch.  The second term of each update (XZ, Z) is the CTA's own previous output block: it stays in registers as
 // packed fp16.  Operand loads that do not depend on the step in flight (A rows, Z rows) are prefetched behind the barrier.
-// Warp roles: warp 0 TMA, warp 1 MMA issue, warps 2-5 epilogue (one thread per output row).
+// Warp roles: warp 0 TMA, warp 1 MMA issue, warps 2-9 epilogue (one thread per output row and 64-column half).
 #include <cuda_fp16.h>
 
 #include "common.cuh"
@@ -20,9 +22,10 @@
 
 namespace tmil {
 
-constexpr int PC_THREADS = 192;
+constexpr int PC_THREADS = 320;   // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue (two warps per TMEM lane quarter: column halves)
 constexpr int PC_OP_BYTES = 65536;                       // one operand tile: 128 x 256 (A) or 256 x 128 (B) fp16
-constexpr size_t PC_SMEM = 1024 + 2 * PC_OP_BYTES + 256;
+constexpr int PC_STAGE_BYTES = 32768;                    // the CTA's own 128 x 128 output block, K-major, on its way to global
+constexpr size_t PC_SMEM = 1024 + 2 * PC_OP_BYTES + PC_STAGE_BYTES + 256;
 constexpr int PC_STEPS = 4 * TM_PINV_ITERS;
 
 __device__ __forceinline__ void cluster_sync_all() {
@@ -41,14 +44,15 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
   uint8_t* sB = smem + PC_OP_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * PC_OP_BYTES);
+  uint8_t* sStage = smem + 2 * PC_OP_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * PC_OP_BYTES + PC_STAGE_BYTES);
   uint64_t* fullA = bars;         // [4] per k-block of the A operand
   uint64_t* fullB = bars + 4;     // [4] per 64-row k-chunk of the B operand
   uint64_t* mma_done = bars + 8;  // accumulator of the step complete
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
 #ifdef TM_PINV_TIMELINE
-  __shared__ long long tl[PC_STEPS][8];   // per step: producer barrier exit, B issued | mma: barrier exit, B[3] full, issued | epi: barrier exit, mma_done, stores done
+  __shared__ long long tl[PC_STEPS][10];   // per step: producer barrier exit, B issued | mma: barrier exit, B[3] full, issued | epi: barrier exit, mma_done, stores done
 #define TL(s, i) tl[s][i] = clock64()
 #else
 #define TL(s, i)
@@ -76,40 +80,44 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
 
   if (warp == 0) {
     // ---- TMA producer ------------------------------------------------------------------------------------------
-    auto loadA = [&](const CUtensorMap* m) {   // rows 128 mi .. +128 of a row-major iterate, K-major k-blocks
-#pragma unroll
-      for (int kb = 0; kb < 4; ++kb) {
+    // Only the PEER's half of a fresh operand travels through global memory: the CTA's own 128x128 block of the previous
+    // product was written straight into sB (and, for XZ, into sA) by its epilogue.
+    auto loadA = [&](const CUtensorMap* m, int kb0, int kb1) {   // rows 128 mi .. +128 of a row-major iterate, K-major k-blocks
+      for (int kb = kb0; kb < kb1; ++kb) {
         mbar_arrive_expect_tx(&fullA[kb], 16384);
         tma_load_3d(sA + kb * 16384, m, &fullA[kb], kb * 64, 128 * mi, bh);
         tma_load_3d(sA + kb * 16384 + 8192, m, &fullA[kb], kb * 64, 128 * mi + 64, bh);
       }
     };
-    auto loadB = [&](const CUtensorMap* m) {   // columns 128 ni .. +128, MN-major: 2 groups of [256 k rows][64 n]
-#pragma unroll
-      for (int kc = 0; kc < 4; ++kc) {
+    auto loadB = [&](const CUtensorMap* m, int kc0, int kc1) {   // columns 128 ni .. +128, MN-major: 2 groups of [256 k rows][64 n]
+      for (int kc = kc0; kc < kc1; ++kc) {
         mbar_arrive_expect_tx(&fullB[kc], 16384);
         tma_load_3d(sB + kc * 8192, m, &fullB[kc], 128 * ni, kc * 64, bh);
         tma_load_3d(sB + 32768 + kc * 8192, m, &fullB[kc], 128 * ni + 64, kc * 64, bh);
       }
     };
-    if (lane == 0) loadA(&maps.A);
+    const int pB = 2 * (1 - mi), pA = 2 * (1 - ni);   // first k-chunk of the peer's half of B / of A
+    if (lane == 0) loadA(&maps.A, 0, 4);
     __syncwarp();
     for (int s = 0; s < PC_STEPS; ++s) {
       cluster_sync_all();
       if (lane == 0) {
         TL(s, 0);
-        fence_proxy_async_all();
+        // the peers published their blocks with TMA stores (async proxy, completed before they arrived at the barrier) and
+        // this TMA load is async proxy too: no generic <-> async proxy fence is needed on this side
         const int it = s >> 2, g = s & 3;
         const CUtensorMap* zc = (it & 1) ? &maps.Zb : &maps.Za;
-        if (g == 1) loadA(&maps.XZ);
-        loadB(g == 0 ? zc : (g == 1 ? &maps.XZ : (g == 2 ? &maps.T1 : &maps.T2)));
+        const CUtensorMap* mb = g == 0 ? zc : (g == 1 ? &maps.XZ : (g == 2 ? &maps.T1 : &maps.T2));
+        if (s == 0) loadB(mb, 0, 4);        // Z0 comes from the prep kernel: nothing is in shared memory yet
+        else loadB(mb, pB, pB + 2);
+        if (g == 1) loadA(&maps.XZ, pA, pA + 2);
         TL(s, 1);
         if (g == 2) {                       // next A operand = Z rows: independent of the step in flight
           mbar_wait(mma_done, s & 1);
-          loadA(zc);
+          loadA(zc, 0, 4);
         } else if (g == 3 && s + 1 < PC_STEPS) {
           mbar_wait(mma_done, s & 1);
-          loadA(&maps.A);
+          loadA(&maps.A, 0, 4);
         }
       }
       __syncwarp();
@@ -117,19 +125,24 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
   } else if (warp == 1) {
     // ---- MMA issuer --------------------------------------------------------------------------------------------
     constexpr uint32_t idesc = umma_idesc_f16(128, 64, 0, 1);   // A K-major, B MN-major
-    uint32_t nA = 0;
+    uint32_t phA = 0, phB = 0;   // bit kc = parity of the next TMA phase of fullA[kc] / fullB[kc]
+    const int pB = 2 * (1 - mi), pA = 2 * (1 - ni);
     for (int s = 0; s < PC_STEPS; ++s) {
       cluster_sync_all();
       if (lane == 0) {
         TL(s, 2);
         tc_fence_after();
-        const bool newA = (s & 3) != 2;
+        const int g = s & 3;
 #pragma unroll
-        for (int kc = 0; kc < 4; ++kc) {
-          if (newA) mbar_wait(&fullA[kc], nA & 1);
-          mbar_wait(&fullB[kc], s & 1);
-          if (kc == 0) { TL(s, 6); }
-          if (kc == 3) { TL(s, 3); }
+        for (int i = 0; i < 4; ++i) {
+          // the CTA's own half of B (k rows 128 mi ..) is already in shared memory: start there, the peer's half arrives by TMA
+          const int kc = (s == 0) ? i : ((2 * mi + i) & 3);
+          const bool waitA = (g == 0 || g == 3) || (g == 1 && (kc >> 1) == (pA >> 1));
+          const bool waitB = (s == 0) || (kc >> 1) == (pB >> 1);
+          if (waitA) { mbar_wait(&fullA[kc], (phA >> kc) & 1); phA ^= 1u << kc; }
+          if (waitB) { mbar_wait(&fullB[kc], (phB >> kc) & 1); phB ^= 1u << kc; }
+          if (i == 0) { TL(s, 6); }
+          if (i == 3) { TL(s, 3); }
           tc_fence_after();
 #pragma unroll
           for (int k4 = 0; k4 < 4; ++k4) {
@@ -138,13 +151,12 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
 #pragma unroll
             for (int gg = 0; gg < 2; ++gg) {
               const uint64_t dB = umma_desc_mn_sw128(smem_u32(sB + gg * 32768 + ks * 2048), 32768, 1024);
-              umma_f16_ss(tmem_base + gg * 64, dA, dB, idesc, ks > 0 ? 1u : 0u);
+              umma_f16_ss(tmem_base + gg * 64, dA, dB, idesc, (i > 0 || k4 > 0) ? 1u : 0u);
             }
           }
         }
         umma_commit(mma_done);
         TL(s, 4);
-        if (newA) ++nA;
       }
       __syncwarp();
     }
@@ -152,13 +164,14 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
     // ---- epilogue: one thread per row of the 128x128 block ---------------------------------------------------------
     const int qd = warp & 3;
     const int r = qd * 32 + lane;
+    const int ch0 = ((warp - 2) >> 2) * 2;   // this warp's two 32-column chunks of the 128-column block: ch0, ch0 + 1
     const uint32_t t_row = tmem_base + ((uint32_t)(qd * 32) << 16);
     const long long row_off = mat + (long long)(128 * mi + r) * TM_LANDMARKS + 128 * ni;
-    uint32_t xz[64], zs[64];   // own XZ block row / own Z block row, packed fp16 (the second terms of the updates)
+    uint32_t xz[32], zs[32];   // own XZ / own Z half row, packed fp16 (the second terms of the updates)
     {
-      const uint4* z0 = reinterpret_cast<const uint4*>(Za + row_off);
+      const uint4* z0 = reinterpret_cast<const uint4*>(Za + row_off + ch0 * 32);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
+      for (int i = 0; i < 8; ++i) {
         const uint4 u = __ldcg(z0 + i);
         zs[4 * i] = u.x; zs[4 * i + 1] = u.y; zs[4 * i + 2] = u.z; zs[4 * i + 3] = u.w;
       }
@@ -167,32 +180,37 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
       cluster_sync_all();
       const int it = s >> 2, g = s & 3;
       const bool last = s == PC_STEPS - 1;
-      __half* dst = g == 0 ? XZ : (g == 1 ? T1 : (g == 2 ? T2 : ((it & 1) ? Za : Zb)));
       mbar_wait(mma_done, s & 1);
       if (threadIdx.x == 64) { TL(s, 5); }
       tc_fence_after();
+      uint32_t raw[2][32];         // both 32-column chunks in flight before the single wait
+      tmem_ld_32x32_nowait(t_row + ch0 * 32, raw[0]);
+      tmem_ld_32x32_nowait(t_row + ch0 * 32 + 32, raw[1]);
+      tmem_ld_wait();
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {
+      for (int cl = 0; cl < 2; ++cl) {
+        const int ch = ch0 + cl;
         float v[32];
-        tmem_ld_32x32(t_row + ch * 32, v);
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(raw[cl][e]);
         uint32_t pk[16];
         if (g == 0) {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) { pk[e] = pack_f16x2(v[2 * e], v[2 * e + 1]); xz[ch * 16 + e] = pk[e]; }
+          for (int e = 0; e < 16; ++e) { pk[e] = pack_f16x2(v[2 * e], v[2 * e + 1]); xz[cl * 16 + e] = pk[e]; }
         } else if (g == 3) {
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
-            const float2 z = __half22float2(*reinterpret_cast<const __half2*>(&zs[ch * 16 + e]));
+            const float2 z = __half22float2(*reinterpret_cast<const __half2*>(&zs[cl * 16 + e]));
             v[2 * e] = fmaf(3.25f, z.x, -0.25f * v[2 * e]);
             v[2 * e + 1] = fmaf(3.25f, z.y, -0.25f * v[2 * e + 1]);
             pk[e] = pack_f16x2(v[2 * e], v[2 * e + 1]);
-            zs[ch * 16 + e] = pk[e];
+            zs[cl * 16 + e] = pk[e];
           }
         } else {
           const float c = g == 1 ? 7.0f : 15.0f;
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
-            const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&xz[ch * 16 + e]));
+            const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&xz[cl * 16 + e]));
             pk[e] = pack_f16x2(fmaf(c, x.x, -v[2 * e]), fmaf(c, x.y, -v[2 * e + 1]));
           }
         }
@@ -201,13 +219,40 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
 #pragma unroll
           for (int e = 0; e < 8; ++e) zo[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
         } else {
-          uint4* d4 = reinterpret_cast<uint4*>(dst + row_off + ch * 32);
+          // (1) own half of the NEXT step's B operand, MN-major SWIZZLE_128B: k row kk = 128 mi + r, n group = ch / 2
+          // (2) the block in K-major SWIZZLE_128B form [128 rows][64 cols] x 2: source of the TMA store that publishes it
+          //     to the peers; for XZ (g == 0) that form, placed at k-blocks 2 ni, 2 ni + 1 of sA, IS the own half of the
+          //     next step's A operand
+          const int kk = 128 * mi + r;
+          uint8_t* bdst = sB + (ch >> 1) * 32768 + kk * 128;
+          uint8_t* kdst = (g == 0 ? sA + (2 * ni + (ch >> 1)) * 16384 : sStage + (ch >> 1) * 16384) + r * 128;
 #pragma unroll
-          for (int e = 0; e < 4; ++e) d4[e] = make_uint4(pk[4 * e], pk[4 * e + 1], pk[4 * e + 2], pk[4 * e + 3]);
+          for (int e = 0; e < 4; ++e) {
+            const uint4 u = make_uint4(pk[4 * e], pk[4 * e + 1], pk[4 * e + 2], pk[4 * e + 3]);
+            const int c = (ch & 1) * 4 + e;
+            *reinterpret_cast<uint4*>(bdst + ((c ^ (kk & 7)) << 4)) = u;
+            *reinterpret_cast<uint4*>(kdst + ((c ^ (r & 7)) << 4)) = u;
+          }
         }
       }
       tc_fence_before();           // TMEM reads retire before the next step's MMA overwrites the accumulator
-      fence_proxy_async_all();     // generic-proxy global stores -> visible to the peers' TMA (async proxy) loads
+      if (threadIdx.x == 64) { TL(s, 8); }
+      if (!last) {
+        fence_proxy_async();       // generic-proxy smem writes -> visible to the TMA store and to the next step's MMA
+        named_bar_sync(1, 256);
+        if (threadIdx.x == 64) {
+          TL(s, 9);
+          const CUtensorMap* md = g == 0 ? &maps.XZ : (g == 1 ? &maps.T1 : (g == 2 ? &maps.T2 : ((it & 1) ? &maps.Za : &maps.Zb)));
+          const uint8_t* src = g == 0 ? sA + (2 * ni) * 16384 : sStage;
+#pragma unroll
+          for (int bx = 0; bx < 2; ++bx)
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf)
+              tma_store_3d(md, src + bx * 16384 + hf * 8192, 128 * ni + 64 * bx, 128 * mi + 64 * hf, bh);
+          tma_store_commit();
+          tma_store_wait_all<0>();   // the block is in global memory before this thread arrives at the cluster barrier
+        }
+      }
       if (threadIdx.x == 64) { TL(s, 7); }
     }
   }
@@ -216,8 +261,8 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
   if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
     const long long t0 = tl[0][0];
     for (int s = 0; s < 12; ++s)
-      printf("step %2d g%d | tma: bar_exit %6lld issued %6lld | mma: bar_exit %6lld B0_full %6lld B3_full %6lld committed %6lld | epi: mma_done %6lld stored %6lld\n",
-             s, s & 3, tl[s][0] - t0, tl[s][1] - t0, tl[s][2] - t0, tl[s][6] - t0, tl[s][3] - t0, tl[s][4] - t0, tl[s][5] - t0, tl[s][7] - t0);
+      printf("step %2d g%d | tma: bar_exit %6lld issued %6lld | mma: bar_exit %6lld B0_full %6lld B3_full %6lld committed %6lld | epi: mma_done %6lld packed %6lld synced %6lld stored %6lld\n",
+             s, s & 3, tl[s][0] - t0, tl[s][1] - t0, tl[s][2] - t0, tl[s][6] - t0, tl[s][3] - t0, tl[s][4] - t0, tl[s][5] - t0, tl[s][8] - t0, tl[s][9] - t0, tl[s][7] - t0);
   }
 #endif
   tc_fence_after();
@@ -225,9 +270,25 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
 }
 
 // A16 = half(attn2);  Z0 = half(attn2^T / scale)      grid (8, 8, B*8), block (32, 8)
-__global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restrict__ A, const float* __restrict__ scale,
+// scale = max_i rowsum * max_j colsum over ALL bags and heads of the call (moore_penrose_iter_pinv's global scalar): every
+// CTA reduces the 2 x nbh x 256 sums itself (max is order independent, so all CTAs get the same bits) instead of waiting
+// for a one-block kernel in between.
+__global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restrict__ A, const float* __restrict__ rowsum,
+                                                          const float* __restrict__ colpart, int nbh, int nparts,
                                                           __half* __restrict__ A16, __half* __restrict__ Z16) {
   __shared__ float t[32][33];
+  __shared__ float red[2][8];
+  const int tid = threadIdx.y * 32 + threadIdx.x;
+  float mr = 0.f, mc = 0.f;
+  for (int i = tid; i < nbh * TM_LANDMARKS; i += 256) {
+    mr = fmaxf(mr, __ldg(rowsum + i));
+    const int bh = i / TM_LANDMARKS, j = i - bh * TM_LANDMARKS;
+    float c = 0.f;
+    for (int p = 0; p < nparts; ++p) c += __ldg(colpart + ((long long)bh * nparts + p) * TM_LANDMARKS + j);
+    mc = fmaxf(mc, c);
+  }
+  mr = warp_max(mr); mc = warp_max(mc);
+  if (threadIdx.x == 0) { red[0][threadIdx.y] = mr; red[1][threadIdx.y] = mc; }
   const long long base = (long long)blockIdx.z * TM_LANDMARKS * TM_LANDMARKS;
   const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 32;
   for (int i = threadIdx.y; i < 32; i += 8) {
@@ -237,13 +298,17 @@ __global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restric
     A16[o] = __float2half_rn(a);
   }
   __syncthreads();
-  const float sc = scale[0];
+  mr = red[0][0]; mc = red[1][0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) { mr = fmaxf(mr, red[0][w]); mc = fmaxf(mc, red[1][w]); }
+  const float sc = mr * mc;
   for (int i = threadIdx.y; i < 32; i += 8)
     Z16[base + (long long)(x0 + i) * TM_LANDMARKS + y0 + threadIdx.x] = __float2half_rn(t[threadIdx.x][i] / sc);
 }
 
 // scratch16: 6 fp16 matrices per (bag, head): A16, Za, Zb, XZ, T1, T2
-int pinv_cluster_run(const float* attn2, const float* scale, int nbh, void* scratch16, float* Z, cudaStream_t st) {
+int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpart, int nparts, int nbh, void* scratch16, float* Z,
+                     cudaStream_t st) {
   TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "pinv_cluster_run needs an sm_100 device");
   const long long mat = (long long)TM_LANDMARKS * TM_LANDMARKS;
   __half* A16 = (__half*)scratch16;
@@ -252,7 +317,7 @@ int pinv_cluster_run(const float* attn2, const float* scale, int nbh, void* scra
   __half* XZ = Zb + nbh * mat;
   __half* T1 = XZ + nbh * mat;
   __half* T2 = T1 + nbh * mat;
-  pinv_prep16_kernel<<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, scale, A16, Za);
+  pinv_prep16_kernel<<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, rowsum, colpart, nbh, nparts, A16, Za);
   TM_LAUNCH_CHECK();
   PinvMaps maps;
   __half* ptrs[6] = {A16, Za, Zb, XZ, T1, T2};
