@@ -114,6 +114,19 @@ def peaks():
     return {"hbm": 6650.0, "tensor": 1590.0, "src": "fallback (B200_PROFILING.md)"}
 
 
+def ncu_traffic(a, stage):
+    """dram bytes per launch of `stage` from the committed `ncu --set full` capture of this workload (None for other workloads)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as f:
+            t = json.load(f)
+        w = t["workload"]
+        if (w["n"], w["in_features"], w["bags"]) != (a.n, a.features, a.bags):
+            return None
+        return t["stages"][stage]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 class ClockSampler:
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
@@ -401,7 +414,7 @@ def main():
             achieved = alg / dur_s / (1e12 if bound == "tensor" else 1e9)
             line["roofline"] = {"kernel": top, "bound": bound, "achieved": achieved, "peak": pk[bound],
                                 "unit": "TFLOP/s" if bound == "tensor" else "GB/s", "frac": achieved / pk[bound],
-                                "traffic": None, "peak_source": pk["src"], "algorithmic_per_launch": alg,
+                                "traffic": ncu_traffic(a, top), "peak_source": pk["src"], "algorithmic_per_launch": alg,
                                 "ms_per_launch": per_stage[top]["ms_per_launch"],
                                 "timing": "CUDA events on the launch stream at stage boundaries, K steps of the same workload run "
                                           "right after the timed region with the two-stream pinv/attn3v overlap off"}

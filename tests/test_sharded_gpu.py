@@ -168,7 +168,13 @@ def test_sharded_forward_one_rank_matches_unsharded_and_oracle(built_lib, one_ra
     x = make_input("rand", 1, n, D, 11)
     with torch.no_grad():
         plain = m(x.cuda()).cpu()
-    got = TokenShardedTransMIL(m)(x).cpu()
+    sharded = TokenShardedTransMIL(m, cuda_graph=True)
+    got = sharded(x).cpu()                 # first call: eager
+    again = sharded(x).cpu()               # second call: captured into a CUDA graph and replayed
+    third = sharded(x * 1.0).cpu()         # replay with a fresh input tensor
+    assert torch.equal(again, got) and torch.equal(third, got)
+    other = sharded(make_input("rand", 1, n, D, 12)).cpu()
+    assert not torch.equal(other, got)     # the replay really reads its new input
     ref = O.forward({k: v.cpu() for k, v in m.state_dict().items()}, x)
     assert (got - ref).abs().max().item() < LOGIT_TOL
     assert (torch.softmax(got, 1) - torch.softmax(ref, 1)).abs().max().item() < PROB_TOL
@@ -180,6 +186,6 @@ def test_sharded_forward_multi_gpu(built_lib, world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
-                        "--master-port", "29541", os.path.join(ROOT, "tests", "run_sharded_gpu.py")], capture_output=True, text=True, timeout=600)
+                        "--master-port", "29541", os.path.join(ROOT, "tests", "run_sharded_gpu.py")], capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "SHARDED-OK" in r.stdout

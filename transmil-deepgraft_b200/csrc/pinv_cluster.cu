@@ -16,6 +16,7 @@
 // packed fp16.  Operand loads that do not depend on the step in flight (A rows, Z rows) are prefetched behind the barrier.
 // Warp roles: warp 0 TMA, warp 1 MMA issue, warps 2-9 epilogue (one thread per output row and 64-column half).
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -306,6 +307,8 @@ __global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restric
     Z16[base + (long long)(x0 + i) * TM_LANDMARKS + y0 + threadIdx.x] = __float2half_rn(t[threadIdx.x][i] / sc);
 }
 
+int pinv_push_launch(__half* A16, __half* Za, __half* Zb, int nbh, float* Z, cudaStream_t st);   // pinv_push.cu
+
 // scratch16: 6 fp16 matrices per (bag, head): A16, Za, Zb, XZ, T1, T2
 int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpart, int nparts, int nbh, void* scratch16, float* Z,
                      cudaStream_t st) {
@@ -319,6 +322,14 @@ int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpa
   __half* T2 = T1 + nbh * mat;
   pinv_prep16_kernel<<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, rowsum, colpart, nbh, nparts, A16, Za);
   TM_LAUNCH_CHECK();
+  // default: the distributed-shared-memory kernel (pinv_push.cu); TM_PINV_KERNEL=tma selects the first-generation kernel
+  // of this file (peers exchange their blocks through global memory with TMA stores / loads), kept as a cross-check
+  static int use_push = -1;
+  if (use_push < 0) {
+    const char* e = getenv("TM_PINV_KERNEL");
+    use_push = (e != nullptr && strcmp(e, "tma") == 0) ? 0 : 1;
+  }
+  if (use_push) return pinv_push_launch(A16, Za, Zb, nbh, Z, st);
   PinvMaps maps;
   __half* ptrs[6] = {A16, Za, Zb, XZ, T1, T2};
   CUtensorMap* ms[6] = {&maps.A, &maps.Za, &maps.Zb, &maps.XZ, &maps.T1, &maps.T2};

@@ -355,18 +355,49 @@ class TokenShardedTransMIL:
     group (one process per GPU).  `x` is the full bag [n,D] / [1,n,D] on every rank (host or device) or, with `n=...`, this
     rank's rows only (`plan(n).take(x, rank)`) -- the form a sharded loader would hand over."""
 
-    def __init__(self, model):
+    def __init__(self, model, cuda_graph=False):
         if model.training:
             raise NotImplementedError("token-sharded path: inference only (model.eval())")
         self.model = model
         self.ops = CudaOps(model)
         self._plans = {}
+        # cuda_graph=True (single-rank groups only): after an eager first call per bag size the whole schedule -- kernels,
+        # side-stream fork/join -- is captured into a CUDA graph and replayed, one launch per bag.  With more than one rank
+        # the capture would have to include the NCCL point-to-point exchanges; that hung on a 2 x B200 box (r1), so
+        # multi-rank groups always issue the schedule eagerly.
+        self.cuda_graph = bool(cuda_graph) and dist.get_world_size() == 1
+        self._graphs = {}      # n -> dict(graph, x, logits) | "eager" (first call done, capture next) | "failed"
 
     def plan(self, n):
         key = (int(n), dist.get_world_size())
         if key not in self._plans:
             self._plans[key] = ShardPlan(*key)
         return self._plans[key]
+
+    def _run_graph(self, plan, x):
+        n = plan.p["n"]
+        state = self._graphs.get(n)
+        if state is None or state == "failed":
+            if state is None:
+                self._graphs[n] = "eager"
+            return sharded_forward(self.ops, plan, x)
+        if state == "eager":
+            static_x = self.ops.to_device(x).clone()
+            try:
+                torch.cuda.synchronize(self.ops.dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    logits = sharded_forward(self.ops, plan, static_x)
+                state = self._graphs[n] = dict(graph=g, x=static_x, logits=logits)
+            except Exception as e:   # same kernels either way: fall back to issuing them one by one
+                import warnings
+                warnings.warn(f"token-sharded forward: CUDA graph capture failed ({e}); running eagerly")
+                self._graphs[n] = "failed"
+                torch.cuda.synchronize(self.ops.dev)
+                return sharded_forward(self.ops, plan, x)
+        state["x"].copy_(x, non_blocking=True)
+        state["graph"].replay()
+        return state["logits"].clone()
 
     @torch.no_grad()
     def __call__(self, x, n=None):
@@ -380,4 +411,6 @@ class TokenShardedTransMIL:
         else:
             plan = self.plan(n)
         with torch.cuda.device(self.ops.dev):
+            if self.cuda_graph:
+                return self._run_graph(plan, x)
             return sharded_forward(self.ops, plan, x)
