@@ -10,6 +10,9 @@ namespace tmil {
 
 int attn3v_tc_fwd_budget(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3, float* scratch,
                          int reserved_sms, cudaStream_t st);
+int prep_operands(const float* const* srcs, void* const* dsts, const long long* counts, const int* kinds, int njobs,
+                  const tm_weights* w, float* packed, cudaStream_t st);
+int ppeg_fwd_prepacked(const tm_weights* w, const float* h_in, int64_t B, int64_t G, float* h_out, float* packed, cudaStream_t st);
 int ln_inplace(float* x, const float* gamma, const float* beta, long long rows, int width, int rpb, long long bag_rows,
                int off, bool round, cudaStream_t st);
 
@@ -288,31 +291,37 @@ extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, i
   cudaStream_t st = (cudaStream_t)stream;
   float* ws = (float*)workspace;
   tm_weights wl = *w;
+  bool ppeg_packed = false;
   if (use_tc(flags)) {
     // tensor-core engine: every tensor that feeds a tf32 contraction is rounded by its producer; the (static) GEMM
     // weights are rounded here into the workspace.  The user's bag x is read as is (operand truncation by the MMA).
     flags |= TM_FLAG_TF32_OPERANDS | TM_FLAG_F16_ACT;
     const int f0 = fc1_width(w);
-    TM_PROPAGATE(tm_round_tf32(w->fc1_w0, ws + L.wr_fc1_0, (int64_t)(f0 ? f0 : TM_DIM) * w->in_features, st));
+    // every per-forward copy of the parameters in ONE launch: tf32-rounded fc1 weights, fp16 to_qkv / to_out weights (xn and
+    // merged are produced as fp16 by their kernels) and the packed PPEG filter
+    const float* srcs[6]; void* dsts[6]; long long cnt[6]; int kinds[6];
+    int nj = 0;
+    srcs[nj] = w->fc1_w0; dsts[nj] = ws + L.wr_fc1_0; cnt[nj] = (long long)(f0 ? f0 : TM_DIM) * w->in_features; kinds[nj++] = 0;
     wl.fc1_w0 = ws + L.wr_fc1_0;
     if (f0) {
-      TM_PROPAGATE(tm_round_tf32(w->fc1_w1, ws + L.wr_fc1_1, (int64_t)TM_DIM * f0, st));
+      srcs[nj] = w->fc1_w1; dsts[nj] = ws + L.wr_fc1_1; cnt[nj] = (long long)TM_DIM * f0; kinds[nj++] = 0;
       wl.fc1_w1 = ws + L.wr_fc1_1;
     }
-    // the layer GEMMs (to_qkv, to_out) run with fp16 operands: xn and merged are produced as fp16 by their kernels, the
-    // weights are converted here
     tm_layer_weights* lws[2] = {&wl.layer1, &wl.layer2};
     for (int l = 0; l < 2; ++l) {
-      TM_PROPAGATE(tm_cvt_f16(lws[l]->qkv_w, ws + L.wr_qkv[l], (int64_t)3 * TM_DIM * TM_DIM, st));
-      TM_PROPAGATE(tm_cvt_f16(lws[l]->out_w, ws + L.wr_out[l], (int64_t)TM_DIM * TM_DIM, st));
+      srcs[nj] = lws[l]->qkv_w; dsts[nj] = ws + L.wr_qkv[l]; cnt[nj] = (long long)3 * TM_DIM * TM_DIM; kinds[nj++] = 1;
+      srcs[nj] = lws[l]->out_w; dsts[nj] = ws + L.wr_out[l]; cnt[nj] = (long long)TM_DIM * TM_DIM; kinds[nj++] = 1;
       lws[l]->qkv_w = ws + L.wr_qkv[l];
       lws[l]->out_w = ws + L.wr_out[l];
     }
+    TM_PROPAGATE(prep_operands(srcs, dsts, cnt, kinds, nj, w, ws + L.packed, st));
+    ppeg_packed = true;
   }
   TM_PROPAGATE(tm_fc1_fwd(&wl, x, B, n, ws + L.h[0], ws + L.fc1s, flags, st));
   TM_PROPAGATE(layer_fwd(wl.layer1, p, B, ws + L.h[0], ws + L.h[1], ws, L, 0, flags, st));
   prof_mark(ST_PPEG, st);
-  TM_PROPAGATE(tm_ppeg_fwd(&wl, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
+  if (ppeg_packed) TM_PROPAGATE(ppeg_fwd_prepacked(&wl, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
+  else TM_PROPAGATE(tm_ppeg_fwd(&wl, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
   TM_PROPAGATE(layer_fwd(wl.layer2, p, B, ws + L.h[2], ws + L.h[3], ws, L, 1, flags, st));
   prof_mark(ST_HEAD, st);
   TM_PROPAGATE(tm_head_fwd(&wl, ws + L.h[3], B, p.S, logits, st));

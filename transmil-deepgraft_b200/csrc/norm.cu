@@ -121,6 +121,84 @@ __global__ void __launch_bounds__(256) cvt_f16_kernel(const float* __restrict__ 
   }
 }
 
+// One launch for every per-forward operand copy of the parameters: tf32-rounded / fp16 copies of the GEMM weights and the
+// packed PPEG filter (effective 7x7 + bias, see ppeg.cu).  Block b serves job j with first_block[j] <= b < first_block[j+1];
+// the blocks after the last job pack the PPEG filter.
+struct PrepJobs {
+  const float* src[6];
+  void* dst[6];
+  long long n4[6];
+  int kind[6];            // 0: round to tf32 (fp32 out), 1: fp16 out
+  int first_block[7];
+  int njobs;
+  const float *w7, *b7, *w5, *b5, *w3, *b3;
+  float* packed;          // [50][512] or NULL
+};
+
+__global__ void __launch_bounds__(256) prep_operands_kernel(const PrepJobs J) {
+  const int b = blockIdx.x;
+  if (b >= J.first_block[J.njobs]) {
+    if (J.packed == nullptr) return;
+    const int i = (b - J.first_block[J.njobs]) * 256 + threadIdx.x;   // (tap, channel), tap 49 = bias
+    if (i >= 50 * TM_DIM) return;
+    const int t = i / TM_DIM, c = i - t * TM_DIM;
+    float v;
+    if (t == 49) {
+      v = (J.b7[c] + J.b5[c]) + J.b3[c];
+    } else {
+      const int dy = t / 7, dx = t - dy * 7;
+      v = J.w7[c * 49 + t];
+      if (dy >= 1 && dy <= 5 && dx >= 1 && dx <= 5) v += J.w5[c * 25 + (dy - 1) * 5 + (dx - 1)];
+      if (dy >= 2 && dy <= 4 && dx >= 2 && dx <= 4) v += J.w3[c * 9 + (dy - 2) * 3 + (dx - 2)];
+    }
+    J.packed[i] = v;
+    return;
+  }
+  int j = 0;
+#pragma unroll
+  for (int q = 1; q < 6; ++q)
+    if (q < J.njobs && b >= J.first_block[q]) j = q;
+  const long long nb = J.first_block[j + 1] - J.first_block[j];
+  const float4* src = reinterpret_cast<const float4*>(J.src[j]);
+  for (long long i = (long long)(b - J.first_block[j]) * 256 + threadIdx.x; i < J.n4[j]; i += nb * 256) {
+    const float4 v = src[i];
+    if (J.kind[j] == 0)
+      reinterpret_cast<float4*>(J.dst[j])[i] = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+    else
+      reinterpret_cast<uint2*>(J.dst[j])[i] = make_uint2(pack_f16x2(v.x, v.y), pack_f16x2(v.z, v.w));
+  }
+}
+
+// srcs/dsts/counts/kinds: njobs <= 6 conversion jobs (counts in floats, multiples of 4); packed may be NULL
+int prep_operands(const float* const* srcs, void* const* dsts, const long long* counts, const int* kinds, int njobs,
+                  const tm_weights* w, float* packed, cudaStream_t st) {
+  PrepJobs J;
+  memset(&J, 0, sizeof(J));
+  TM_CHECK_ARG(njobs >= 0 && njobs <= 6, TM_ERR_BAD_ARGUMENT, "prep_operands: at most 6 jobs");
+  int blocks = 0;
+  for (int j = 0; j < njobs; ++j) {
+    TM_CHECK_ARG(counts[j] % 4 == 0 && aligned16(srcs[j]) && (reinterpret_cast<uintptr_t>(dsts[j]) & 7u) == 0, TM_ERR_BAD_ALIGNMENT,
+                 "prep_operands: operand %d is not 4-float / 16-byte aligned", j);
+    J.src[j] = srcs[j]; J.dst[j] = dsts[j]; J.n4[j] = counts[j] / 4; J.kind[j] = kinds[j];
+    J.first_block[j] = blocks;
+    long long nb = ceil_div(J.n4[j], 256 * 4);      // 4 float4 per thread
+    if (nb < 1) nb = 1;
+    if (nb > 256) nb = 256;
+    blocks += (int)nb;
+  }
+  J.first_block[njobs] = blocks;
+  J.njobs = njobs;
+  if (packed != nullptr) {
+    J.w7 = w->ppeg_w7; J.b7 = w->ppeg_b7; J.w5 = w->ppeg_w5; J.b5 = w->ppeg_b5; J.w3 = w->ppeg_w3; J.b3 = w->ppeg_b3;
+    J.packed = packed;
+    blocks += (50 * TM_DIM + 255) / 256;
+  }
+  if (blocks == 0) return TM_OK;
+  prep_operands_kernel<<<blocks, 256, 0, st>>>(J);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
 // cls row: logits[b] = _fc(LayerNorm(h[b, 0]))
 __global__ void __launch_bounds__(128) head_kernel(const float* __restrict__ h, long long bag_stride,
                                                    const float* __restrict__ gamma, const float* __restrict__ beta,

@@ -162,10 +162,13 @@ __global__ void __launch_bounds__(256, 1) ppeg_kernel(const __grid_constant__ CU
 
 static int ppeg_launch(const tm_weights* w, const float* in_rows, int64_t y_in0, int64_t y_in1, long long in_bag_stride, int64_t B,
                        int64_t G, int64_t tok0, int64_t tok1, float* out, long long out_bag_stride, const float* cls_in,
-                       long long cls_in_stride, float* cls_out, long long cls_out_stride, float* packed, cudaStream_t st) {
+                       long long cls_in_stride, float* cls_out, long long cls_out_stride, float* packed, cudaStream_t st,
+                       bool packed_ready = false) {
   TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "tm_ppeg_fwd needs an sm_100 device (TMA)");
-  ppeg_pack_kernel<<<2, 256, 0, st>>>(w->ppeg_w7, w->ppeg_b7, w->ppeg_w5, w->ppeg_b5, w->ppeg_w3, w->ppeg_b3, packed);
-  TM_LAUNCH_CHECK();
+  if (!packed_ready) {
+    ppeg_pack_kernel<<<2, 256, 0, st>>>(w->ppeg_w7, w->ppeg_b7, w->ppeg_w5, w->ppeg_b5, w->ppeg_w3, w->ppeg_b3, packed);
+    TM_LAUNCH_CHECK();
+  }
   CUtensorMap tm;
   const uint64_t dims[4] = {(uint64_t)TM_DIM, (uint64_t)G, (uint64_t)(y_in1 - y_in0), (uint64_t)B};
   if (in_bag_stride <= 0) in_bag_stride = (y_in1 - y_in0) * G * (long long)TM_DIM;   // single bag: any valid pitch
@@ -198,6 +201,12 @@ static int ppeg_launch(const tm_weights* w, const float* in_rows, int64_t y_in0,
   ppeg_kernel<<<(unsigned)(16 * workers), 256, PP_SMEM, st>>>(tm, packed, a);
   TM_LAUNCH_CHECK();
   return TM_OK;
+}
+
+// tm_ppeg_fwd with `packed` already filled by prep_operands (tm_transmil_fwd packs every parameter copy in one launch)
+int ppeg_fwd_prepacked(const tm_weights* w, const float* h_in, int64_t B, int64_t G, float* h_out, float* packed, cudaStream_t st) {
+  const long long bag = (G * G + 1) * (long long)TM_DIM;
+  return ppeg_launch(w, h_in + TM_DIM, 0, G, bag, B, G, 0, G * G, h_out + TM_DIM, bag, h_in, bag, h_out, bag, packed, st, true);
 }
 
 }  // namespace tmil
