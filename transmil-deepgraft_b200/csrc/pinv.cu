@@ -134,8 +134,8 @@ static int pinv_gemm(const float* L, const float* R, float* C, float alpha, floa
 // One product of the chain on the tensor cores: every iterate is kept in both orientations, so X @ Y is the NT GEMM
 // X . (Y^T)^T with tf32 operands (all stored iterates are tf32-rounded by their producer) and fp32 accumulation;
 // out = alpha * X@Y + beta * L, with L supplied transposed (LT) and the result written as C and/or C^T.
-int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpart, int nparts, int nbh, void* scratch16, float* Z,
-                     cudaStream_t st);   // pinv_cluster.cu
+int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpart, int nparts, const float* scale, int nbh,
+                     void* scratch16, float* Z, cudaStream_t st);   // pinv_cluster.cu
 
 static int pinv_gemm_tc(const float* X, const float* YT, float alpha, float beta, const float* LT, float* C, float* CT, bool round,
                         int nbh, cudaStream_t st) {
@@ -186,11 +186,13 @@ extern "C" int tm_pinv_fwd(const float* q_lm, const float* k_lm, int64_t B, floa
   if (tc && !cluster) attn2_kernel<true><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
   else attn2_kernel<false><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
   TM_LAUNCH_CHECK();
-  if (cluster)   // one 4-CTA-cluster kernel for the whole chain (fp16 operands); attn2 stays exact fp32; the global init
-                 // scalar is reduced inside the operand-preparation kernel
-    return pinv_cluster_run(attn2, rowsum, colpart, LM / ROWS, nbh, XZ, Z, st);
+  // one 4-CTA-cluster kernel for the whole chain (fp16 operands); attn2 stays exact fp32.  For a few heads the global init
+  // scalar is reduced inside the operand-preparation kernel (one launch less on the latency-critical path); with many
+  // heads that per-CTA reduction would be quadratic, so the one-block kernel computes it once.
+  if (cluster && nbh <= 16) return pinv_cluster_run(attn2, rowsum, colpart, LM / ROWS, nullptr, nbh, XZ, Z, st);
   pinv_scale_kernel<<<1, 1024, 0, st>>>(rowsum, colpart, nbh, scale);
   TM_LAUNCH_CHECK();
+  if (cluster) return pinv_cluster_run(attn2, rowsum, colpart, LM / ROWS, scale, nbh, XZ, Z, st);
   if (tc) {
     pinv_z0_kernel<true><<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, scale, Z, ZTa);
     TM_LAUNCH_CHECK();

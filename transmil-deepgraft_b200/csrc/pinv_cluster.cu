@@ -274,14 +274,17 @@ pinv_cluster_kernel(const __grid_constant__ PinvMaps maps, __half* __restrict__ 
 // scale = max_i rowsum * max_j colsum over ALL bags and heads of the call (moore_penrose_iter_pinv's global scalar): every
 // CTA reduces the 2 x nbh x 256 sums itself (max is order independent, so all CTAs get the same bits) instead of waiting
 // for a one-block kernel in between.
+// With many (bag, head) pairs that per-CTA reduction would be quadratic work: the caller then passes `scale` computed by
+// pinv_scale_kernel (scale != NULL) and the loop below is skipped.
 __global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restrict__ A, const float* __restrict__ rowsum,
                                                           const float* __restrict__ colpart, int nbh, int nparts,
-                                                          __half* __restrict__ A16, __half* __restrict__ Z16) {
+                                                          const float* __restrict__ scale, __half* __restrict__ A16,
+                                                          __half* __restrict__ Z16) {
   __shared__ float t[32][33];
   __shared__ float red[2][8];
   const int tid = threadIdx.y * 32 + threadIdx.x;
   float mr = 0.f, mc = 0.f;
-  for (int i = tid; i < nbh * TM_LANDMARKS; i += 256) {
+  for (int i = tid; scale == nullptr && i < nbh * TM_LANDMARKS; i += 256) {
     mr = fmaxf(mr, __ldg(rowsum + i));
     const int bh = i / TM_LANDMARKS, j = i - bh * TM_LANDMARKS;
     float c = 0.f;
@@ -302,7 +305,7 @@ __global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restric
   mr = red[0][0]; mc = red[1][0];
 #pragma unroll
   for (int w = 1; w < 8; ++w) { mr = fmaxf(mr, red[0][w]); mc = fmaxf(mc, red[1][w]); }
-  const float sc = mr * mc;
+  const float sc = scale != nullptr ? scale[0] : mr * mc;
   for (int i = threadIdx.y; i < 32; i += 8)
     Z16[base + (long long)(x0 + i) * TM_LANDMARKS + y0 + threadIdx.x] = __float2half_rn(t[threadIdx.x][i] / sc);
 }
@@ -310,8 +313,8 @@ __global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restric
 int pinv_push_launch(__half* A16, __half* Za, __half* Zb, int nbh, float* Z, cudaStream_t st);   // pinv_push.cu
 
 // scratch16: 6 fp16 matrices per (bag, head): A16, Za, Zb, XZ, T1, T2
-int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpart, int nparts, int nbh, void* scratch16, float* Z,
-                     cudaStream_t st) {
+int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpart, int nparts, const float* scale, int nbh,
+                     void* scratch16, float* Z, cudaStream_t st) {
   TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "pinv_cluster_run needs an sm_100 device");
   const long long mat = (long long)TM_LANDMARKS * TM_LANDMARKS;
   __half* A16 = (__half*)scratch16;
@@ -320,7 +323,7 @@ int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpa
   __half* XZ = Zb + nbh * mat;
   __half* T1 = XZ + nbh * mat;
   __half* T2 = T1 + nbh * mat;
-  pinv_prep16_kernel<<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, rowsum, colpart, nbh, nparts, A16, Za);
+  pinv_prep16_kernel<<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, rowsum, colpart, nbh, nparts, scale, A16, Za);
   TM_LAUNCH_CHECK();
   // default: the distributed-shared-memory kernel (pinv_push.cu); TM_PINV_KERNEL=tma selects the first-generation kernel
   // of this file (peers exchange their blocks through global memory with TMA stores / loads), kept as a cross-check

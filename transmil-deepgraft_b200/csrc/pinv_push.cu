@@ -20,6 +20,7 @@
 // Only Z (A operand of the last product of an iteration, needed two steps after it is produced) and the constant A go
 // through global memory, by TMA, off the critical path.
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -47,6 +48,24 @@ __device__ __forceinline__ void dsmem_push(uint32_t dst_cluster_addr, uint32_t s
                "r"(src_cta_addr), "r"(bytes), "r"(mbar_cluster_addr)
                : "memory");
 }
+// remote (peer CTA) 16-byte store and remote barrier arrive, for the REMOTE_ST variant
+__device__ __forceinline__ void st_cluster_v4(uint32_t cluster_addr, const uint4& u) {
+  asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(cluster_addr), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t mbar_cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(mbar_cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "W_%=:\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra D_%=;\n\t"
+      "bra W_%=;\n\t"
+      "D_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_full() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void umma_commit_multicast(uint64_t* bar, uint16_t cta_mask) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
                "h"(cta_mask)
@@ -58,6 +77,12 @@ struct PinvPushMaps {
   CUtensorMap A, Za, Zb;   // [nbh][256][256] fp16, box [1][64][64]
 };
 
+// REMOTE_ST = false (default): the own halves are pushed with cp.async.bulk.shared::cluster after the epilogue has packed them.
+// REMOTE_ST = true (TM_PINV_KERNEL=remote): the epilogue threads write the peers' halves themselves with st.shared::cluster
+// while they pack, and one remote barrier arrive per peer replaces the transaction count.  Measured on B200 (r1): the
+// thread-issued remote stores stall the packing loop (3300-6300 cycles per step instead of 1100-1900) and the kernel is
+// 25 % SLOWER than the bulk-copy form (0.142 vs 0.113 ms for the whole pinv); kept as the recorded experiment.
+template <bool REMOTE_ST>
 __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(PP_THREADS, 1)
 pinv_push_kernel(const __grid_constant__ PinvPushMaps maps, const __half* __restrict__ Z0, float* __restrict__ Zout) {
   extern __shared__ uint8_t smem_raw[];
@@ -70,7 +95,9 @@ pinv_push_kernel(const __grid_constant__ PinvPushMaps maps, const __half* __rest
   uint64_t* fullB = bars + 4;      // [4] per 64-row k-chunk of the B operand
   uint64_t* ready = bars + 8;      // 3 arrivals per step: MMA of this CTA, of its B peer and of its A peer complete
   uint64_t* own_ready = bars + 9;  // epilogue -> MMA warp: own halves are in shared memory, TMEM is drained
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* pushB = bars + 10;     // REMOTE_ST: the B peer has written its half of the next B operand into sB
+  uint64_t* pushA = bars + 11;     // REMOTE_ST: the A peer has written its half of XZ into sA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
 
 #ifdef TM_PINV_TIMELINE
   __shared__ long long tl[PP_STEPS][8];   // mma: own_ready seen, operands complete, committed | epi: ready seen, packed, synced, pushed
@@ -93,6 +120,8 @@ pinv_push_kernel(const __grid_constant__ PinvPushMaps maps, const __half* __rest
     for (int i = 0; i < 4; ++i) { mbar_init(&fullA[i], 1); mbar_init(&fullB[i], 1); }
     mbar_init(ready, 3);
     mbar_init(own_ready, 1);
+    mbar_init(pushB, 1);
+    mbar_init(pushA, 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, 128);
@@ -122,12 +151,14 @@ pinv_push_kernel(const __grid_constant__ PinvPushMaps maps, const __half* __rest
         const int it = s >> 2, g = s & 3;
         // the peers push the halves of this step's fresh operands during their epilogue of step s-1, i.e. after `ready`
         // of step s-1; by then this CTA's MMA of step s-1 has consumed the previous phase of every barrier re-armed here
-        mbar_wait(ready, (s - 1) & 1);
-        mbar_arrive_expect_tx(&fullB[pB], 16384);
-        mbar_arrive_expect_tx(&fullB[pB + 1], 16384);
-        if (g == 1) {
-          mbar_arrive_expect_tx(&fullA[pA], 16384);
-          mbar_arrive_expect_tx(&fullA[pA + 1], 16384);
+        mbar_wait(ready, (s - 1) & 1);   // also keeps this loop in lockstep with the phases of `ready` (parity waits must not run ahead)
+        if (!REMOTE_ST) {
+          mbar_arrive_expect_tx(&fullB[pB], 16384);
+          mbar_arrive_expect_tx(&fullB[pB + 1], 16384);
+          if (g == 1) {
+            mbar_arrive_expect_tx(&fullA[pA], 16384);
+            mbar_arrive_expect_tx(&fullA[pA + 1], 16384);
+          }
         }
         if (g == 2) {                        // A operand of step g = 3: the current iterate Z, rows 128 mi (global, L2 resident)
           mbar_wait(ready, s & 1);           // sA (XZ) is free once this step's MMA is done
@@ -154,10 +185,18 @@ pinv_push_kernel(const __grid_constant__ PinvPushMaps maps, const __half* __rest
         for (int i = 0; i < 4; ++i) {
           // own half first (already in shared memory), the peer's half while it is still arriving
           const int kc = (s == 0) ? i : ((2 * mi + i) & 3);
-          const bool waitA = (g == 0 || g == 3) || (g == 1 && (kc >> 1) == (pA >> 1));
-          const bool waitB = (s == 0) || (kc >> 1) == (pB >> 1);
+          const bool peerA = g == 1 && (kc >> 1) == (pA >> 1), peerB = s > 0 && (kc >> 1) == (pB >> 1);
+          const bool waitA = (g == 0 || g == 3) || (peerA && !REMOTE_ST);
+          const bool waitB = (s == 0) || (peerB && !REMOTE_ST);
           if (waitA) { mbar_wait(&fullA[kc], (phA >> kc) & 1); phA ^= 1u << kc; }
           if (waitB) { mbar_wait(&fullB[kc], (phB >> kc) & 1); phB ^= 1u << kc; }
+          if (REMOTE_ST && s > 0) {
+            const bool needB = i == 2;                // i = 2, 3 are the peer's k-chunks of B (own half first)
+            const bool needA = peerA && !(i & 1);     // first of the A peer's two k-blocks of XZ (they are adjacent in this order)
+            if (needB) mbar_wait_cluster(pushB, (s - 1) & 1);
+            if (needA) mbar_wait_cluster(pushA, (s >> 2) & 1);
+            if (needB || needA) fence_proxy_async_full();   // peers' generic-proxy remote stores -> the MMA's async-proxy reads
+          }
           if (i == 3) { TLP(s, 1); }
           tc_fence_after();
 #pragma unroll
@@ -241,12 +280,18 @@ pinv_push_kernel(const __grid_constant__ PinvPushMaps maps, const __half* __rest
           // a K-major staging tile that a TMA store publishes to global memory (A operand of the NEXT iteration's last step)
           uint8_t* bdst = sB + (ch >> 1) * 32768 + kk * 128;
           uint8_t* kdst = g == 0 ? sA + (2 * ni + (ch >> 1)) * 16384 + r * 128 : (g == 3 ? sStage + (ch >> 1) * 16384 + r * 128 : nullptr);
+          const uint32_t rb = REMOTE_ST ? mapa_u32(smem_u32(bdst), rankB) : 0u;
+          const uint32_t ra = (REMOTE_ST && g == 0) ? mapa_u32(smem_u32(kdst), rankA) : 0u;
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const uint4 u = make_uint4(pk[4 * e], pk[4 * e + 1], pk[4 * e + 2], pk[4 * e + 3]);
             const int c = (ch & 1) * 4 + e;
             *reinterpret_cast<uint4*>(bdst + ((c ^ (kk & 7)) << 4)) = u;
             if (kdst != nullptr) *reinterpret_cast<uint4*>(kdst + ((c ^ (r & 7)) << 4)) = u;
+            if (REMOTE_ST) {
+              st_cluster_v4(rb + ((c ^ (kk & 7)) << 4), u);
+              if (g == 0) st_cluster_v4(ra + ((c ^ (r & 7)) << 4), u);
+            }
           }
         }
       }
@@ -258,20 +303,26 @@ pinv_push_kernel(const __grid_constant__ PinvPushMaps maps, const __half* __rest
         if (leader) {
           TLP(s, 5);
           mbar_arrive(own_ready);    // this CTA's MMA warp may start on the own halves
-          // B: k rows 128 mi .. +128 = k-chunks 2 mi, 2 mi + 1, both column groups -> B peer, same offsets
+          if (REMOTE_ST) {
+            // every epilogue thread's remote stores happen-before this point (bar.sync); the release is cumulative
+            mbar_arrive_remote(mapa_u32(smem_u32(pushB), rankB));
+            if (g == 0) mbar_arrive_remote(mapa_u32(smem_u32(pushA), rankA));
+          } else {
+            // B: k rows 128 mi .. +128 = k-chunks 2 mi, 2 mi + 1, both column groups -> B peer, same offsets
 #pragma unroll
-          for (int gg = 0; gg < 2; ++gg)
+            for (int gg = 0; gg < 2; ++gg)
 #pragma unroll
-            for (int q2 = 0; q2 < 2; ++q2) {
-              const int kc = 2 * mi + q2;
-              const uint32_t off = gg * 32768 + kc * 8192;
-              dsmem_push(mapa_u32(sB_u + off, rankB), sB_u + off, 8192, mapa_u32(smem_u32(&fullB[kc]), rankB));
-            }
-          if (g == 0) {              // XZ: own k-blocks 2 ni, 2 ni + 1 -> A peer
+              for (int q2 = 0; q2 < 2; ++q2) {
+                const int kc = 2 * mi + q2;
+                const uint32_t off = gg * 32768 + kc * 8192;
+                dsmem_push(mapa_u32(sB_u + off, rankB), sB_u + off, 8192, mapa_u32(smem_u32(&fullB[kc]), rankB));
+              }
+            if (g == 0) {              // XZ: own k-blocks 2 ni, 2 ni + 1 -> A peer
 #pragma unroll
-            for (int q2 = 0; q2 < 2; ++q2) {
-              const int kb = 2 * ni + q2;
-              dsmem_push(mapa_u32(sA_u + kb * 16384, rankA), sA_u + kb * 16384, 16384, mapa_u32(smem_u32(&fullA[kb]), rankA));
+              for (int q2 = 0; q2 < 2; ++q2) {
+                const int kb = 2 * ni + q2;
+                dsmem_push(mapa_u32(sA_u + kb * 16384, rankA), sA_u + kb * 16384, 16384, mapa_u32(smem_u32(&fullA[kb]), rankA));
+              }
             }
           }
           if (g == 3) {              // Z' -> global (the other buffer of the Za / Zb pair)
@@ -311,12 +362,15 @@ int pinv_push_launch(__half* A16, __half* Za, __half* Zb, int nbh, float* Z, cud
   CUtensorMap* ms[3] = {&maps.A, &maps.Za, &maps.Zb};
   for (int i = 0; i < 3; ++i)
     TM_PROPAGATE(make_tmap_3d_f16(ms[i], ptrs[i], nbh, TM_LANDMARKS, TM_LANDMARKS, mat, TM_LANDMARKS, 64, 64));
-  static bool attr_done = false;
-  if (!attr_done) {
-    TM_CUDA(cudaFuncSetAttribute(pinv_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PP_SMEM_BYTES));
-    attr_done = true;
+  static int remote_st = -1;
+  if (remote_st < 0) {
+    const char* e = getenv("TM_PINV_KERNEL");
+    remote_st = (e != nullptr && strcmp(e, "remote") == 0) ? 1 : 0;   // default: cp.async.bulk pushes; TM_PINV_KERNEL=remote: st.shared::cluster
+    TM_CUDA(cudaFuncSetAttribute(pinv_push_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PP_SMEM_BYTES));
+    TM_CUDA(cudaFuncSetAttribute(pinv_push_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PP_SMEM_BYTES));
   }
-  pinv_push_kernel<<<dim3(4, nbh), PP_THREADS, PP_SMEM_BYTES, st>>>(maps, Za, Z);
+  if (remote_st) pinv_push_kernel<true><<<dim3(4, nbh), PP_THREADS, PP_SMEM_BYTES, st>>>(maps, Za, Z);
+  else pinv_push_kernel<false><<<dim3(4, nbh), PP_THREADS, PP_SMEM_BYTES, st>>>(maps, Za, Z);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
