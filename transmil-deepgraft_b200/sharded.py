@@ -107,6 +107,7 @@ class CudaOps:
         # operand copies of the GEMM weights (what tm_transmil_fwd derives into its workspace)
         self._keep = []
         self._side = None
+        self._arena_key, self._arena, self._arena_pos = None, [], 0
         f = model._fc1
         self.w.fc1_w0 = self._tf32(f[0].weight)
         if model._fc1_kind == capi.TM_FC1_2048:
@@ -123,11 +124,35 @@ class CudaOps:
         self.pinv_scratch = self.f32(int(self.L.tm_pinv_scratch_floats(1)))
 
     # -- small helpers
+    # Buffers: a forward asks for the same sequence of buffers every time it runs the same plan, so they are handed out
+    # from a replayed list (`begin_forward(key)` rewinds it) instead of ~60 allocator calls per bag.  Reuse is safe: every
+    # consumer of a buffer is ordered before its next producer on the same stream (NCCL ops are ordered against it by
+    # torch.distributed).
+    def begin_forward(self, key):
+        if key != self._arena_key:
+            self._arena_key, self._arena = key, []
+        self._arena_pos = 0
+
+    def _buf(self, shape, dtype):
+        shape = tuple(int(v) for v in (shape[0] if len(shape) == 1 and isinstance(shape[0], (tuple, list)) else shape))
+        if self._arena_key is None:
+            return torch.empty(shape, dtype=dtype, device=self.dev)
+        i = self._arena_pos
+        self._arena_pos += 1
+        if i < len(self._arena):
+            t = self._arena[i]
+            if t.shape == shape and t.dtype == dtype:
+                return t
+            del self._arena[i:]
+        t = torch.empty(shape, dtype=dtype, device=self.dev)
+        self._arena.append(t)
+        return t
+
     def f32(self, *shape):
-        return torch.empty(*shape, dtype=torch.float32, device=self.dev)
+        return self._buf(shape, torch.float32)
 
     def f16(self, *shape):
-        return torch.empty(*shape, dtype=torch.float16, device=self.dev)
+        return self._buf(shape, torch.float16)
 
     def _tf32(self, wt):
         out = torch.empty_like(wt)
@@ -144,7 +169,7 @@ class CudaOps:
         return x.to(device=self.dev, dtype=torch.float32, non_blocking=True).contiguous()
 
     def comm_buffer(self, *shape, dtype=torch.float32):
-        return torch.empty(*shape, dtype=dtype, device=self.dev)
+        return self._buf(shape, dtype)
 
     def side_stream(self):
         """Context: kernels launched inside run on a high-priority side stream forked from the current stream."""
@@ -413,4 +438,5 @@ class TokenShardedTransMIL:
         with torch.cuda.device(self.ops.dev):
             if self.cuda_graph:
                 return self._run_graph(plan, x)
-            return sharded_forward(self.ops, plan, x)
+            self.ops.begin_forward(plan.p["n"])
+            return sharded_forward(self.ops, plan, x).clone()      # the buffer list is reused by the next call
