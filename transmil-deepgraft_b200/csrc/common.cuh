@@ -55,6 +55,34 @@ int side_stream(SideStream* out);
     if (_s != TM_OK) return _s; \
   } while (0)
 
+// Programmatic dependent launch.  A kernel launched through launch_pdl() may be scheduled while the previous kernel of the
+// stream is still running: its CTAs take SM slots as the predecessor's CTAs exit, run their prologue (barrier init, TMEM
+// allocation, tensor-map prefetch) and block in pdl_wait() until the predecessor has completed and flushed its memory.
+// Rules kept by every kernel that is launched this way: nothing produced by another kernel is read, and nothing is written
+// to global memory, before pdl_wait(); pdl_trigger() comes after the kernel's own pdl_wait(), so at most one generation of
+// dependents is ever resident early and "my wait returned" implies "every earlier kernel of the stream finished".
+// TM_PDL=0 in the environment launches everything the ordinary way (the device-side calls are then no-ops).
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_trigger(); }
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

@@ -34,6 +34,10 @@ void prof_mark(int stage, cudaStream_t st) {
   g_marks.emplace_back(stage, ev);
 }
 bool prof_enabled() { return g_prof_on; }
+bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("TM_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
 
 static std::mutex g_side_mutex;
 static std::vector<std::pair<int, SideStream>> g_side;
