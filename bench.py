@@ -371,6 +371,36 @@ def main():
             e1.record()
             barrier()
             e2e_ms = e0.elapsed_time(e1)
+            # the same slides as half-precision feature files (fp16 on the host, read as fp16 by fc1)
+            x16_host = x_host.half().pin_memory()
+            x16_dev = x16_host.to(dev)
+            ref32 = model(x16_dev.float())
+            for _ in range(3):
+                got16 = model(x16_dev)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(a.steps):
+                model(x16_dev)
+            e1.record()
+            barrier()
+            f16_dev_ms = e0.elapsed_time(e1)
+            for out_host in loop([x16_host] * 3):
+                pass
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for out_host in loop(x16_host for _ in range(a.steps)):
+                pass
+            e1.record()
+            barrier()
+            f16_e2e_ms = e0.elapsed_time(e1)
+            f16 = {"note": "same bag stored as fp16 feature files (SURVEY 8f/N2): fp16 on the host and in HBM, fc1 contracts fp16 x fp16 -> f32; "
+                           "not the headline (the reference feeds fp32 tensors)",
+                   "device_ms_per_step": f16_dev_ms / a.steps, "e2e_ms_per_step": f16_e2e_ms / a.steps,
+                   "e2e_value": a.steps * a.bags / (f16_e2e_ms / 1e3), "h2d_bytes_per_step": a.bags * a.n * a.features * 2,
+                   "max_abs_dlogit_vs_f32_read_of_the_same_halves": float((got16 - ref32).abs().max())}
+            del x16_dev
         clocks = None
         if sampler:
             t_hold = time.perf_counter()
@@ -401,7 +431,8 @@ def main():
                            "api": "StreamedInference(model)(pinned host bags) -> host logits, one slide at a time: every step copies "
                                   "its 50k x D bag host->device and its logits back; the copy of slide i+1 overlaps the forward of slide i",
                            "serial": {"value": total_bags / (e2e_serial_max / 1e3), "ms_per_step": e2e_serial_max / a.steps,
-                                      "api": "model(x_pinned_host).cpu() per step, copy then compute"}}
+                                      "api": "model(x_pinned_host).cpu() per step, copy then compute"},
+                           "f16_features": f16}
         # roofline of the dominant stage
         cost = stage_cost(a)
         pk = peaks()

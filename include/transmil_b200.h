@@ -62,6 +62,11 @@ typedef enum tm_fc1_kind {
 
 #define TM_FLAG_NO_OVERLAP 32u      /* tm_transmil_fwd: keep every stage on the caller's stream (no fork of the pinv chain
                                     onto the library's side stream while attn3.v runs) */
+#define TM_FLAG_X_F16 64u           /* tm_transmil_fwd / tm_transmil_fwd_host / tm_fc1_fwd: the bag x is fp16 [B,n,D] (feature files
+                                       stored in half precision; the upcast x.float() of TransMIL.py:174 is exact, so is
+                                       reading the halves directly).  The first fc1 contraction then runs fp16 x fp16 -> fp32 with an
+                                       fp16 copy of its weight (same 10-bit mantissa as the tf32 operands of the fp32 path).
+                                       Tensor-core engine only. */
 
 /* Index contract of one bag (TransMIL.py:177-179,184-186,190-193 and the
  * nystrom-attention 0.0.11 front pad / landmark grouping).  Pure host code. */
@@ -173,7 +178,8 @@ int tm_stage_is_f16(const char* name, uint32_t flags);
 /* ---- per-kernel entry points (all device pointers) -------------------- */
 /* K1+K2: _fc1 (TransMIL.py:175) fused with the duplicate pad (:177-180) and the
  * cls token (:184-186).  x [B,n,D] -> h0 [B,S,512].  scratch: B*n*F0 floats
- * (unused for TM_FC1_SINGLE). */
+ * (unused for TM_FC1_SINGLE).  With TM_FLAG_X_F16, x AND w->fc1_w0 point at fp16 data
+ * (tm_transmil_fwd makes the weight copy itself). */
 int tm_fc1_fwd(const tm_weights* w, const float* x, int64_t B, int64_t n, float* h0,
                float* scratch, uint32_t flags, void* stream);
 

@@ -15,6 +15,7 @@ TM_FLAG_TF32_OPERANDS = 4
 TM_FLAG_PINV_GEMM_CHAIN = 8
 TM_FLAG_F16_ACT = 16
 TM_FLAG_NO_OVERLAP = 32
+TM_FLAG_X_F16 = 64
 TM_FC1_SINGLE, TM_FC1_2048, TM_FC1_768 = 0, 1, 2
 
 _fp = C.c_void_p  # device/host float pointers travel as raw addresses

@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(256) attn3v_combine_kernel(const float* __rest
                                                              long long bs_ms, long long cs_o, long long bs_o,
                                                              float* __restrict__ W3, float* __restrict__ out_m,
                                                              float* __restrict__ out_s) {
+  pdl_sync();
   const int bh = blockIdx.y;
   const int idx = blockIdx.x * 256 + threadIdx.x;  // (j, d4)
   const int j = idx >> 4, d4 = idx & 15;

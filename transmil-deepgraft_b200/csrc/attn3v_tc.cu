@@ -76,6 +76,7 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_sync();
   const uint32_t tmem_base = *tmem_slot;
 #ifdef TM_TIMELINE
   __shared__ long long tl[2][12][6];
@@ -290,14 +291,14 @@ static int attn3v_tc_run(const void* qlm16, const void* k16, const void* v16, in
   float* pm = scratch;
   float* ps = pm + nbh * used * TM_LANDMARKS;
   float* pO = ps + nbh * used * TM_LANDMARKS;
-  attn3v_tc_kernel<<<dim3((unsigned)used, (unsigned)nbh), A3_THREADS, A3_SMEM, st>>>(tmQ, tmK, tmV, tpc, tiles_per_bh, used, pm, ps, pO);
+  launch_pdl(attn3v_tc_kernel, dim3((unsigned)used, (unsigned)nbh), dim3(A3_THREADS), A3_SMEM, st, tmQ, tmK, tmV, tpc, (int)tiles_per_bh, used, pm, ps, pO);
   TM_LAUNCH_CHECK();
   float* out_m = partial;
   float* out_s = partial ? partial + nbh * TM_LANDMARKS : nullptr;
   float* out_n = partial ? partial + 2 * nbh * TM_LANDMARKS : W3;
-  attn3v_combine_kernel<<<dim3(16, (unsigned)nbh), 256, 0, st>>>(pm, ps, pO, used, TM_LANDMARKS, (long long)used * TM_LANDMARKS,
-                                                                  TM_LANDMARKS * TM_DHEAD, (long long)used * TM_LANDMARKS * TM_DHEAD,
-                                                                  out_n, out_m, out_s);
+  launch_pdl(attn3v_combine_kernel, dim3(16, (unsigned)nbh), dim3(256), 0, st, (const float*)pm, (const float*)ps, (const float*)pO, (int)used,
+             (long long)TM_LANDMARKS, (long long)used * TM_LANDMARKS, (long long)(TM_LANDMARKS * TM_DHEAD),
+             (long long)used * TM_LANDMARKS * TM_DHEAD, out_n, out_m, out_s);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -63,6 +63,10 @@ int side_stream(SideStream* out);
 // dependents is ever resident early and "my wait returned" implies "every earlier kernel of the stream finished".
 // TM_PDL=0 in the environment launches everything the ordinary way (the device-side calls are then no-ops).
 bool pdl_enabled();
+// The next launch_pdl() of this thread is an ordinary launch (used for the first kernel after a cross-stream event wait).
+void pdl_plain_next();
+void pdl_suspend(bool on);   // every launch_pdl() of this thread is ordinary until switched back
+bool pdl_take_plain();
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -78,7 +82,7 @@ static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 blo
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = (pdl_enabled() && !pdl_take_plain()) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 #endif

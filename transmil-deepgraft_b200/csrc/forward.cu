@@ -23,8 +23,18 @@ static int gemm_auto(const GemmParams& p, uint32_t flags, cudaStream_t st) {
   return gemm_simt(p, st);
 }
 
+// Which launches of a forward stay ordinary launches although their kernels support programmatic dependent launch
+// (TM_PDL_X overrides; measured on B200 at 50k tokens, profiles/r1_pdl_ab.txt): bit 0 attn3.v behind the fork event,
+// 1 the pinv chain on the side stream, 2 attn3.v + its combine, 3 landmarks, 4 nystrom_out, 5 ln_pad, 6 qkv, 7 to_out, 8 ppeg.
+static int pdl_mask() {
+  static const int m = [] { const char* e = getenv("TM_PDL_X"); return e ? atoi(e) : 61; }();
+  return m;
+}
+static void pdl_gate(int bit) { if (pdl_mask() & bit) pdl_plain_next(); }
+
 __global__ void cls_rows_kernel(const float* __restrict__ cls, long long bag_stride, float* __restrict__ h) {
   // h[b, 0, :] = cls_token  (TransMIL.py:184-186)
+  pdl_sync();
   reinterpret_cast<float4*>(h + (long long)blockIdx.x * bag_stride)[threadIdx.x] = __ldg(reinterpret_cast<const float4*>(cls) + threadIdx.x);
 }
 
@@ -115,14 +125,17 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
   float* W3 = ws + L.small[li][SM_W3]; float* M = ws + L.small[li][SM_M];
   float* merged = ws + L.merged;
   prof_mark(ST_LN_PAD, st);
+  pdl_gate(32);
   TM_PROPAGATE(tm_ln_pad_fwd(h_in, lw.norm_w, lw.norm_b, B, p.S, p.P, xn, flags, st));
   if (use_tc(flags)) {
     // tensor-core engine: q, k, v live as fp16 (head-major) in the q/k/v regions; all contractions accumulate in fp32
     void* q16 = q; void* k16 = k; void* v16 = v;
     void* qlm16 = ws + L.qlm16; void* klm16 = ws + L.klm16; void* mt16 = ws + L.mt16;
     prof_mark(ST_QKV, st);
+    pdl_gate(64);
     TM_PROPAGATE(tm_qkv16_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, flags, st));
     prof_mark(ST_LANDMARKS, st);
+    pdl_gate(8);
     TM_PROPAGATE(tm_landmarks16_fwd(q16, k16, B, p.Sp, p.l, q_lm, k_lm, qlm16, klm16, st));
     // sim2 + pinv (32 CTAs per bag, a latency-bound chain of 24 dependent products) and attn3.v (every other SM) are
     // independent: fork the pinv onto the library's high-priority side stream and join before Z.W3.  Serial when the
@@ -135,10 +148,20 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
       TM_PROPAGATE(side_stream(&ss));
       TM_CUDA(cudaEventRecord(ss.fork, st));
       TM_CUDA(cudaStreamWaitEvent(ss.stream, ss.fork, 0));
-      TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, ss.stream));
+      const int pdl_x = pdl_mask();
+      pdl_plain_next();   // first kernel behind a cross-stream wait: ordinary launch
+      if (pdl_x & 2) pdl_suspend(true);
+      const int pinv_rc = tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, ss.stream);
+      pdl_suspend(false);
+      TM_PROPAGATE(pinv_rc);
       TM_CUDA(cudaEventRecord(ss.join, ss.stream));
-      TM_PROPAGATE(attn3v_tc_fwd_budget(qlm16, k16, v16, B, p.Sp, W3, ws + L.a3_s, pinv_sms, st));
+      if (pdl_x & 1) pdl_plain_next();   // an event record sits between landmarks and this launch
+      if (pdl_x & 4) pdl_suspend(true);
+      const int a3_rc = attn3v_tc_fwd_budget(qlm16, k16, v16, B, p.Sp, W3, ws + L.a3_s, pinv_sms, st);
+      pdl_suspend(false);
+      TM_PROPAGATE(a3_rc);
       TM_CUDA(cudaStreamWaitEvent(st, ss.join, 0));
+      pdl_plain_next();
     } else {
       prof_mark(ST_PINV, st);
       TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, B, attn2, Z, ws + L.pinv_s, flags, st));
@@ -148,6 +171,7 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
     prof_mark(ST_ZW, st);
     TM_PROPAGATE(tm_zw16_fwd(Z, W3, B, M, mt16, st));
     prof_mark(ST_NYSTROM_OUT, st);
+    pdl_gate(16);
     TM_PROPAGATE(tm_nystrom_out_tc_fwd(q16, klm16, mt16, v16, lw.conv_w, B, p.Sp, merged, flags, st));
   } else {
   prof_mark(ST_QKV, st);
@@ -164,6 +188,7 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
   TM_PROPAGATE(tm_nystrom_out_fwd(q, k_lm, M, v, lw.conv_w, B, p.Sp, merged, flags, st));
   }
   prof_mark(ST_TO_OUT, st);
+  pdl_gate(128);
   TM_PROPAGATE(tm_to_out_residual_fwd(merged, lw.out_w, lw.out_b, h_in, B, p.S, p.P, h_out, flags, st));
   return TM_OK;
 }
@@ -185,19 +210,24 @@ static int fc1_run(const tm_weights* w, const float* x, int64_t B, int64_t n, fl
   GemmParams g;
   memset(&g, 0, sizeof(g));
   g.batch = 1; g.epi = EPI_BIAS_GELU;
+  const bool x16 = (flags & TM_FLAG_X_F16) != 0;   // x and fc1_w0 are fp16 (the caller passes the fp16 copy of the weight)
+  TM_CHECK_ARG(!x16 || use_tc(flags), TM_ERR_BAD_ARGUMENT, "TM_FLAG_X_F16 needs the tensor-core engine");
   const float* a2 = x; int k2 = D; const float* w2 = w->fc1_w0; const float* b2 = w->fc1_b0;
   if (w->fc1_kind != TM_FC1_SINGLE) {
     const int F0 = fc1_width(w);
     TM_CHECK_ARG(scratch != nullptr, TM_ERR_BAD_ARGUMENT, "tm_fc1_fwd: scratch is required for the two-Linear stems");
     g.A = x; g.Bm = w->fc1_w0; g.C = scratch; g.bias = w->fc1_b0;
     g.M = (int)(B * n); g.N = F0; g.K = D; g.lda = D; g.ldb = D; g.ldc = F0;
+    g.f16_in = x16 ? 1 : 0;
     prof_mark(ST_FC1_GEMM0, st);
     TM_PROPAGATE(gemm_auto(g, flags, st));
+    g.f16_in = 0;
     prof_mark(ST_FC1_LN, st);
     TM_PROPAGATE(ln_inplace(scratch, w->fc1_ln_w, w->fc1_ln_b, B * n, F0, 0, 0, 0, (flags & TM_FLAG_TF32_OPERANDS) != 0, st));
     a2 = scratch; k2 = F0; w2 = w->fc1_w1; b2 = w->fc1_b1;
   }
   g.A = a2; g.Bm = w2; g.C = h0; g.bias = b2;
+  g.f16_in = (x16 && w->fc1_kind == TM_FC1_SINGLE) ? 1 : 0;
   g.M = (int)(B * n); g.N = TM_DIM; g.K = k2; g.lda = k2; g.ldb = k2; g.ldc = TM_DIM;
   if (pad_cls) {
     g.rows_per_bag = (int)n; g.c_bag_rows = p.S; g.c_row_off = 1; g.c_skip = 0; g.dup = (int)p.dup;
@@ -211,7 +241,7 @@ static int fc1_run(const tm_weights* w, const float* x, int64_t B, int64_t n, fl
   }
   if (w->fc1_kind == TM_FC1_768)  // trailing LayerNorm(512) on every token row (row 0 is the cls token)
     TM_PROPAGATE(ln_inplace(h0, w->fc1_ln2_w, w->fc1_ln2_b, B * p.N, TM_DIM, (int)p.N, p.S, 1, false, st));
-  cls_rows_kernel<<<(unsigned)B, TM_DIM / 4, 0, st>>>(w->cls_token, p.S * (long long)TM_DIM, h0);
+  launch_pdl(cls_rows_kernel, dim3((unsigned)B), dim3(TM_DIM / 4), 0, st, (const float*)w->cls_token, p.S * (long long)TM_DIM, h0);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
@@ -301,7 +331,8 @@ extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, i
     // merged are produced as fp16 by their kernels) and the packed PPEG filter
     const float* srcs[6]; void* dsts[6]; long long cnt[6]; int kinds[6];
     int nj = 0;
-    srcs[nj] = w->fc1_w0; dsts[nj] = ws + L.wr_fc1_0; cnt[nj] = (long long)(f0 ? f0 : TM_DIM) * w->in_features; kinds[nj++] = 0;
+    srcs[nj] = w->fc1_w0; dsts[nj] = ws + L.wr_fc1_0; cnt[nj] = (long long)(f0 ? f0 : TM_DIM) * w->in_features;
+    kinds[nj++] = (flags & TM_FLAG_X_F16) ? 1 : 0;   // fp16 copy when the bag itself is fp16
     wl.fc1_w0 = ws + L.wr_fc1_0;
     if (f0) {
       srcs[nj] = w->fc1_w1; dsts[nj] = ws + L.wr_fc1_1; cnt[nj] = (long long)TM_DIM * f0; kinds[nj++] = 0;
@@ -320,6 +351,7 @@ extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, i
   TM_PROPAGATE(tm_fc1_fwd(&wl, x, B, n, ws + L.h[0], ws + L.fc1s, flags, st));
   TM_PROPAGATE(layer_fwd(wl.layer1, p, B, ws + L.h[0], ws + L.h[1], ws, L, 0, flags, st));
   prof_mark(ST_PPEG, st);
+  pdl_gate(256);
   if (ppeg_packed) TM_PROPAGATE(ppeg_fwd_prepacked(&wl, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
   else TM_PROPAGATE(tm_ppeg_fwd(&wl, ws + L.h[1], B, p.G, ws + L.h[2], ws + L.packed, st));
   TM_PROPAGATE(layer_fwd(wl.layer2, p, B, ws + L.h[2], ws + L.h[3], ws, L, 1, flags, st));
@@ -335,7 +367,8 @@ extern "C" int tm_transmil_fwd_host(const tm_weights* w, const float* x_host, in
   TM_PROPAGATE(check_weights(w));
   TM_CHECK_ARG(x_host && logits_host && d_x && d_logits, TM_ERR_BAD_ARGUMENT, "tm_transmil_fwd_host: NULL pointer");
   cudaStream_t st = (cudaStream_t)stream;
-  TM_CUDA(cudaMemcpyAsync(d_x, x_host, (size_t)B * n * w->in_features * sizeof(float), cudaMemcpyHostToDevice, st));
+  const size_t esz = (flags & TM_FLAG_X_F16) ? 2 : sizeof(float);
+  TM_CUDA(cudaMemcpyAsync(d_x, x_host, (size_t)B * n * w->in_features * esz, cudaMemcpyHostToDevice, st));
   TM_PROPAGATE(tm_transmil_fwd(w, d_x, B, n, d_logits, workspace, workspace_bytes, flags, st));
   TM_CUDA(cudaMemcpyAsync(logits_host, d_logits, (size_t)B * w->n_classes * sizeof(float), cudaMemcpyDeviceToHost, st));
   TM_CUDA(cudaStreamSynchronize(st));

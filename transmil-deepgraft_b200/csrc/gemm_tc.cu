@@ -321,6 +321,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_sync();   // barriers, TMEM and descriptors are ready: from here on the predecessor's output is read
   const uint32_t tmem_base = *tmem_slot;
   const int tiles_per_z = m_tiles * n_tiles;
 
@@ -559,7 +560,8 @@ static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcOut
   const long long total = (long long)m_tiles * n_tiles * batch;
   TM_CHECK_ARG(total < (1ll << 31), TM_ERR_BAD_SHAPE, "gemm_tc: too many tiles");
   const int grid = total < sms ? (int)total : sms;
-  gemm_tc_kernel<BN, F16, FAST><<<grid, TcCfg<BN, FAST>::THREADS, TcCfg<BN, FAST>::SMEM, st>>>(tmA, tmB, om, p, m_tiles, n_tiles, k_blocks, (int)total);
+  launch_pdl(gemm_tc_kernel<BN, F16, FAST>, dim3(grid), dim3(TcCfg<BN, FAST>::THREADS), TcCfg<BN, FAST>::SMEM, st, tmA, tmB, om, p, m_tiles,
+             n_tiles, k_blocks, (int)total);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

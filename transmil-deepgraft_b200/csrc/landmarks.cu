@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(256) landmarks16_kernel(const __half* __restri
                                                           long long groups_per_tensor, int l, float* __restrict__ q_lm,
                                                           float* __restrict__ k_lm, __half* __restrict__ qlm16,
                                                           __half* __restrict__ klm16) {
+  pdl_sync();
   const long long gid = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (gid >= 2 * groups_per_tensor) return;
   const int lane = threadIdx.x & 31, lane8 = lane & 7, phase = lane >> 3;
@@ -111,8 +112,8 @@ extern "C" int tm_landmarks16_fwd(const void* q16, const void* k16, int64_t B, i
                    tmil::aligned16(qlm16) && tmil::aligned16(klm16), TM_ERR_BAD_ALIGNMENT,
                "tm_landmarks16_fwd: pointers must be 16-byte aligned");
   const long long groups = (long long)B * TM_HEADS * TM_LANDMARKS;
-  tmil::landmarks16_kernel<<<(unsigned)tmil::ceil_div(2 * groups, 8), 256, 0, (cudaStream_t)stream>>>(
-      (const __half*)q16, (const __half*)k16, groups, (int)l, q_lm, k_lm, (__half*)qlm16, (__half*)klm16);
+  tmil::launch_pdl(tmil::landmarks16_kernel, dim3((unsigned)tmil::ceil_div(2 * groups, 8)), dim3(256), 0, (cudaStream_t)stream,
+                   (const __half*)q16, (const __half*)k16, groups, (int)l, q_lm, k_lm, (__half*)qlm16, (__half*)klm16);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

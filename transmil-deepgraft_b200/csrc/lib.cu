@@ -39,6 +39,12 @@ bool pdl_enabled() {
   return on;
 }
 
+static thread_local bool g_pdl_plain = false;
+static thread_local bool g_pdl_suspended = false;
+void pdl_plain_next() { g_pdl_plain = true; }
+void pdl_suspend(bool on) { g_pdl_suspended = on; }
+bool pdl_take_plain() { const bool v = g_pdl_plain; g_pdl_plain = false; return v || g_pdl_suspended; }
+
 static std::mutex g_side_mutex;
 static std::vector<std::pair<int, SideStream>> g_side;
 int side_stream(SideStream* out) {

@@ -49,6 +49,7 @@ template <int OUT>
 __global__ void __launch_bounds__(256) ln_pad_kernel(const float* __restrict__ h, const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, long long rows, int S, int Sp, int P,
                                                      float* __restrict__ xn) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -136,6 +137,7 @@ struct PrepJobs {
 };
 
 __global__ void __launch_bounds__(256) prep_operands_kernel(const PrepJobs J) {
+  pdl_sync();
   const int b = blockIdx.x;
   if (b >= J.first_block[J.njobs]) {
     if (J.packed == nullptr) return;
@@ -194,7 +196,7 @@ int prep_operands(const float* const* srcs, void* const* dsts, const long long* 
     blocks += (50 * TM_DIM + 255) / 256;
   }
   if (blocks == 0) return TM_OK;
-  prep_operands_kernel<<<blocks, 256, 0, st>>>(J);
+  launch_pdl(prep_operands_kernel, dim3(blocks), dim3(256), 0, st, J);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
@@ -205,6 +207,7 @@ __global__ void __launch_bounds__(128) head_kernel(const float* __restrict__ h, 
                                                    const float* __restrict__ fc_w, const float* __restrict__ fc_b,
                                                    int n_classes, float* __restrict__ logits) {
   __shared__ __align__(16) float hn[TM_DIM];
+  pdl_sync();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.x;
   if (warp == 0) warp_layernorm_row<TM_DIM>(h + (long long)b * bag_stride, hn, gamma, beta, lane);
@@ -258,19 +261,19 @@ extern "C" int tm_ln_pad_fwd(const float* h, const float* gamma, const float* be
   const unsigned grid = (unsigned)tmil::ceil_div(rows, 8);
   cudaStream_t st = (cudaStream_t)stream;
   if (flags & TM_FLAG_F16_ACT)
-    tmil::ln_pad_kernel<2><<<grid, 256, 0, st>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+    tmil::launch_pdl(tmil::ln_pad_kernel<2>, dim3(grid), dim3(256), 0, st, h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
   else if (flags & TM_FLAG_TF32_OPERANDS)
-    tmil::ln_pad_kernel<1><<<grid, 256, 0, st>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+    tmil::launch_pdl(tmil::ln_pad_kernel<1>, dim3(grid), dim3(256), 0, st, h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
   else
-    tmil::ln_pad_kernel<0><<<grid, 256, 0, st>>>(h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
+    tmil::launch_pdl(tmil::ln_pad_kernel<0>, dim3(grid), dim3(256), 0, st, h, gamma, beta, rows, (int)S, (int)(S + P), (int)P, xn);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
 
 extern "C" int tm_head_fwd(const tm_weights* w, const float* h, int64_t B, int64_t S, float* logits, void* stream) {
   TM_CHECK_ARG(w != nullptr && B > 0 && S > 0 && w->n_classes > 0, TM_ERR_BAD_ARGUMENT, "tm_head_fwd: bad arguments");
-  tmil::head_kernel<<<(unsigned)B, 128, 0, (cudaStream_t)stream>>>(h, (long long)S * TM_DIM, w->norm_w, w->norm_b, w->fc_w, w->fc_b,
-                                                                 w->n_classes, logits);
+  tmil::launch_pdl(tmil::head_kernel, dim3((unsigned)B), dim3(128), 0, (cudaStream_t)stream, h, (long long)S * TM_DIM, w->norm_w, w->norm_b,
+                   w->fc_w, w->fc_b, (int)w->n_classes, logits);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -98,6 +98,7 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_sync();   // conv_w above is a module parameter (no kernel of the forward writes it); q, v, k_lm, M are read from here on
   const uint32_t tmem_base = *tmem_slot;
 #ifdef TM_TIMELINE
   __shared__ long long tl[2][12][6];
@@ -314,6 +315,7 @@ __global__ void __launch_bounds__(256) mt16_kernel(const float* __restrict__ M, 
 __global__ void __launch_bounds__(256) zw16_kernel(const float* __restrict__ Z, const float* __restrict__ W3, float* __restrict__ M,
                                                    __half* __restrict__ mt16) {
   extern __shared__ __align__(16) float zw_smem[];
+  pdl_sync();
   float* ws = zw_smem;                                   // [256][64]
   float (*zs)[TM_LANDMARKS] = reinterpret_cast<float (*)[TM_LANDMARKS]>(zw_smem + TM_LANDMARKS * TM_DHEAD);   // [16][256]
   const int bh = blockIdx.y, r0 = blockIdx.x * 16, tid = threadIdx.x;
@@ -378,7 +380,7 @@ extern "C" int tm_zw16_fwd(const float* Z, const float* W3, int64_t B, float* M,
     TM_CUDA(cudaFuncSetAttribute(zw16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done = true;
   }
-  zw16_kernel<<<dim3(16, (unsigned)(B * TM_HEADS)), 256, smem, (cudaStream_t)stream>>>(Z, W3, M, (__half*)mt16);
+  launch_pdl(zw16_kernel, dim3(16, (unsigned)(B * TM_HEADS)), dim3(256), smem, (cudaStream_t)stream, Z, W3, M, (__half*)mt16);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
@@ -408,11 +410,11 @@ extern "C" int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const v
   const int used = (int)ceil_div(tiles_per_bh, tpc);
   dim3 grid((unsigned)used, (unsigned)nbh);
   if (flags & TM_FLAG_F16_ACT)
-    nystrom_out_tc_kernel<2><<<grid, NT_THREADS, NT_SMEM, (cudaStream_t)stream>>>(tmQ, tmV, tmK, tmM, conv_w, (int)Sp, tpc, tiles_per_bh, merged);
+    launch_pdl(nystrom_out_tc_kernel<2>, grid, dim3(NT_THREADS), NT_SMEM, (cudaStream_t)stream, tmQ, tmV, tmK, tmM, conv_w, (int)Sp, (int)tpc, (int)tiles_per_bh, merged);
   else if (flags & TM_FLAG_TF32_OPERANDS)
-    nystrom_out_tc_kernel<1><<<grid, NT_THREADS, NT_SMEM, (cudaStream_t)stream>>>(tmQ, tmV, tmK, tmM, conv_w, (int)Sp, tpc, tiles_per_bh, merged);
+    launch_pdl(nystrom_out_tc_kernel<1>, grid, dim3(NT_THREADS), NT_SMEM, (cudaStream_t)stream, tmQ, tmV, tmK, tmM, conv_w, (int)Sp, (int)tpc, (int)tiles_per_bh, merged);
   else
-    nystrom_out_tc_kernel<0><<<grid, NT_THREADS, NT_SMEM, (cudaStream_t)stream>>>(tmQ, tmV, tmK, tmM, conv_w, (int)Sp, tpc, tiles_per_bh, merged);
+    launch_pdl(nystrom_out_tc_kernel<0>, grid, dim3(NT_THREADS), NT_SMEM, (cudaStream_t)stream, tmQ, tmV, tmK, tmM, conv_w, (int)Sp, (int)tpc, (int)tiles_per_bh, merged);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -22,15 +22,22 @@ __global__ void __launch_bounds__(256) attn2_kernel(const float* __restrict__ q_
                                                     float* __restrict__ attn2, float* __restrict__ rowsum,
                                                     float* __restrict__ colpart) {
   extern __shared__ __align__(16) float sm[];
+  pdl_sync();
   float* ks = sm;                       // 256*68
   float* qs = ks + LM * KLD;            // 32*68
   float* ps = qs + ROWS * KLD;          // 32*257
   const int bh = blockIdx.y, tile = blockIdx.x, tid = threadIdx.x;
   const float* kg = k_lm + (long long)bh * LM * TM_DHEAD;
   const float* qg = q_lm + ((long long)bh * LM + tile * ROWS) * TM_DHEAD;
-  for (int i = tid; i < LM * 16; i += 256) {
-    int r = i >> 4, c = (i & 15) * 4;
-    *reinterpret_cast<float4*>(ks + r * KLD + c) = __ldg(reinterpret_cast<const float4*>(kg + r * TM_DHEAD + c));
+  {
+    float4 kr[16];   // all 16 loads of the 64 KB k_lm tile in flight before the first store (the kernel is on the pinv critical path)
+#pragma unroll
+    for (int u = 0; u < 16; ++u) kr[u] = __ldg(reinterpret_cast<const float4*>(kg) + tid + 256 * u);
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      const int i = tid + 256 * u, r = i >> 4, c = (i & 15) * 4;
+      *reinterpret_cast<float4*>(ks + r * KLD + c) = kr[u];
+    }
   }
   for (int i = tid; i < ROWS * 16; i += 256) {
     int r = i >> 4, c = (i & 15) * 4;
@@ -183,8 +190,8 @@ extern "C" int tm_pinv_fwd(const float* q_lm, const float* k_lm, int64_t B, floa
     attr_done = true;
   }
   const bool cluster = tc && !(flags & TM_FLAG_PINV_GEMM_CHAIN);
-  if (tc && !cluster) attn2_kernel<true><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
-  else attn2_kernel<false><<<dim3(LM / ROWS, nbh), 256, smem, st>>>(q_lm, k_lm, attn2, rowsum, colpart);
+  if (tc && !cluster) launch_pdl(attn2_kernel<true>, dim3(LM / ROWS, nbh), dim3(256), smem, st, q_lm, k_lm, attn2, rowsum, colpart);
+  else launch_pdl(attn2_kernel<false>, dim3(LM / ROWS, nbh), dim3(256), smem, st, q_lm, k_lm, attn2, rowsum, colpart);
   TM_LAUNCH_CHECK();
   // one 4-CTA-cluster kernel for the whole chain (fp16 operands); attn2 stays exact fp32.  For a few heads the global init
   // scalar is reduced inside the operand-preparation kernel (one launch less on the latency-critical path); with many

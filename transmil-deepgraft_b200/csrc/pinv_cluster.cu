@@ -282,6 +282,7 @@ __global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restric
                                                           __half* __restrict__ Z16) {
   __shared__ float t[32][33];
   __shared__ float red[2][8];
+  pdl_sync();
   const int tid = threadIdx.y * 32 + threadIdx.x;
   float mr = 0.f, mc = 0.f;
   for (int i = tid; scale == nullptr && i < nbh * TM_LANDMARKS; i += 256) {
@@ -323,7 +324,7 @@ int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpa
   __half* XZ = Zb + nbh * mat;
   __half* T1 = XZ + nbh * mat;
   __half* T2 = T1 + nbh * mat;
-  pinv_prep16_kernel<<<dim3(8, 8, nbh), dim3(32, 8), 0, st>>>(attn2, rowsum, colpart, nbh, nparts, scale, A16, Za);
+  launch_pdl(pinv_prep16_kernel, dim3(8, 8, nbh), dim3(32, 8), 0, st, attn2, rowsum, colpart, nbh, nparts, scale, A16, Za);
   TM_LAUNCH_CHECK();
   // default: the distributed-shared-memory kernel (pinv_push.cu); TM_PINV_KERNEL=tma selects the first-generation kernel
   // of this file (peers exchange their blocks through global memory with TMA stores / loads), kept as a cross-check

@@ -129,6 +129,7 @@ pinv_push_kernel(const __grid_constant__ PinvPushMaps maps, const __half* __rest
   __syncthreads();
   cluster_sync_all_();             // every CTA's barriers exist before any remote arrive / push can reach them
   tc_fence_after();
+  pdl_sync();                      // A16 / Z0 of the prep kernel are read from here on
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -369,8 +370,8 @@ int pinv_push_launch(__half* A16, __half* Za, __half* Zb, int nbh, float* Z, cud
     TM_CUDA(cudaFuncSetAttribute(pinv_push_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PP_SMEM_BYTES));
     TM_CUDA(cudaFuncSetAttribute(pinv_push_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PP_SMEM_BYTES));
   }
-  if (remote_st) pinv_push_kernel<true><<<dim3(4, nbh), PP_THREADS, PP_SMEM_BYTES, st>>>(maps, Za, Z);
-  else pinv_push_kernel<false><<<dim3(4, nbh), PP_THREADS, PP_SMEM_BYTES, st>>>(maps, Za, Z);
+  if (remote_st) launch_pdl(pinv_push_kernel<true>, dim3(4, nbh), dim3(PP_THREADS), PP_SMEM_BYTES, st, maps, (const __half*)Za, Z);
+  else launch_pdl(pinv_push_kernel<false>, dim3(4, nbh), dim3(PP_THREADS), PP_SMEM_BYTES, st, maps, (const __half*)Za, Z);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

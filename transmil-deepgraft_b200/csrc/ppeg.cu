@@ -79,9 +79,6 @@ __global__ void __launch_bounds__(256, 1) ppeg_kernel(const __grid_constant__ CU
   const int cp = lane & 15, xg = lane >> 4;
   const int per_bag = a.tiles_x * a.tiles_y, ntiles = per_bag * a.B;
 
-  if (a.cls_in != nullptr && worker == 0 && tid < PP_C)  // cls token passes through (TransMIL.py:67,74)
-    for (int b = 0; b < a.B; ++b) a.cls_out[b * a.cls_out_stride + c0 + tid] = a.cls_in[b * a.cls_in_stride + c0 + tid];
-
   if (tid == 0) {
     tma_prefetch_desc(&tm_in);
     mbar_init(&full[0], 1);
@@ -89,6 +86,9 @@ __global__ void __launch_bounds__(256, 1) ppeg_kernel(const __grid_constant__ CU
     fence_barrier_init();
   }
   __syncthreads();
+  pdl_sync();
+  if (a.cls_in != nullptr && worker == 0 && tid < PP_C)  // cls token passes through (TransMIL.py:67,74)
+    for (int b = 0; b < a.B; ++b) a.cls_out[b * a.cls_out_stride + c0 + tid] = a.cls_in[b * a.cls_in_stride + c0 + tid];
   auto issue = [&](int tile, int s) {
     const int b = tile / per_bag, r = tile % per_bag;
     const int y0 = a.ty0 + (r / a.tiles_x) * PP_T, x0 = (r % a.tiles_x) * PP_T;
@@ -198,7 +198,7 @@ static int ppeg_launch(const tm_weights* w, const float* in_rows, int64_t y_in0,
   long long workers = sms / 16;                  // 9 on a 148-SM B200: 144 CTAs, each with a fixed channel slice
   if (workers < 1) workers = 1;
   if (workers > ntiles) workers = ntiles;
-  ppeg_kernel<<<(unsigned)(16 * workers), 256, PP_SMEM, st>>>(tm, packed, a);
+  launch_pdl(ppeg_kernel, dim3((unsigned)(16 * workers)), dim3(256), PP_SMEM, st, tm, (const float*)packed, a);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

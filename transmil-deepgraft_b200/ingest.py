@@ -29,13 +29,14 @@ class StreamedInference:
         if x.dim() == 2:
             x = x.unsqueeze(0)
         slot = self._slots[i]
-        if slot is None or slot["buf"].numel() < x.numel():
-            slot = self._slots[i] = dict(buf=torch.empty(x.numel(), dtype=torch.float32, device=self.device),
+        nbytes = x.numel() * x.element_size()              # slots are raw bytes: fp32 and fp16 feature bags share them
+        if slot is None or slot["buf"].numel() < nbytes:
+            slot = self._slots[i] = dict(buf=torch.empty(nbytes, dtype=torch.uint8, device=self.device),
                                          ready=torch.cuda.Event(), free=torch.cuda.Event())
             slot["buf"].record_stream(self.copy_stream)
             slot["free"].record(torch.cuda.current_stream(self.device))
         self.copy_stream.wait_event(slot["free"])          # the forward that last read this slot is done
-        dst = slot["buf"][:x.numel()].view(x.shape)
+        dst = slot["buf"][:nbytes].view(x.dtype).view(x.shape)
         with torch.cuda.stream(self.copy_stream):
             dst.copy_(x, non_blocking=True)
             slot["ready"].record(self.copy_stream)
@@ -43,7 +44,8 @@ class StreamedInference:
 
     @torch.no_grad()
     def __call__(self, bags):
-        """bags: iterable of host tensors [n_i, D] / [1, n_i, D] (fp32; pinned memory makes the copy asynchronous).
+        """bags: iterable of host tensors [n_i, D] / [1, n_i, D] (fp32, or fp16 feature files as stored -- the model reads halves
+        directly; pinned memory makes the copy asynchronous).
         Yields the logits of each bag as a host tensor [1, n_classes], in order."""
         main = torch.cuda.current_stream(self.device)
         it = iter(bags)

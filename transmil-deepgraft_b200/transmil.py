@@ -185,6 +185,11 @@ class TransMIL(nn.Module):
         L = capi.lib()
         B, n, D = (int(s) for s in x.shape)
         flags = int(self.flags) | (capi.TM_FLAG_KEEP_STAGES if return_attn else 0)
+        # fp16 feature bags (half-precision feature files) are consumed as they are: x.float() of
+        # TransMIL.py:174 is an exact upcast, so fc1 reads the halves directly (half the H2D and HBM bytes)
+        half_in = x.dtype == torch.float16 and not (flags & capi.TM_FLAG_SIMT_ONLY)
+        if half_in:
+            flags |= capi.TM_FLAG_X_F16
         with torch.cuda.device(device):
             w = self._weights()
             nbytes = C.c_size_t()
@@ -193,9 +198,10 @@ class TransMIL(nn.Module):
             logits = torch.empty((B, self.n_classes), dtype=torch.float32, device=device)
             stream = torch.cuda.current_stream(device).cuda_stream
             xd = x.detach()
-            if xd.dtype != torch.float32 or not xd.is_contiguous() or not xd.is_cuda:
+            want = torch.float16 if half_in else torch.float32
+            if xd.dtype != want or not xd.is_contiguous() or not xd.is_cuda:
                 # x.float() (TransMIL.py:174); host bags are copied on the current stream
-                xd = xd.to(device=device, dtype=torch.float32, non_blocking=True).contiguous()
+                xd = xd.to(device=device, dtype=want, non_blocking=True).contiguous()
             capi.check(L.tm_transmil_fwd(C.byref(w), xd.data_ptr(), B, n, logits.data_ptr(), ws.data_ptr(),
                                          ws.numel(), flags, stream))
             self._stage_key = (B, n, flags)
