@@ -226,6 +226,11 @@ int tm_nystrom_out_fwd(const float* q, const float* k_lm, const float* M, const 
  * xn and qkv_w are fp32 (tf32 contraction) or, with TM_FLAG_F16_ACT, fp16 (fp16 contraction, fp32 accumulate). */
 int tm_qkv16_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16,
                  void* v16, uint32_t flags, void* stream);
+/* The same projection restricted to columns [col0, col0+ncols) of to_qkv (whole q / k / v blocks: multiples of 512).
+ * tm_transmil_fwd projects q and k first, forks the pinv chain, and projects v beside it on max_ctas SMs (0 = all).
+ * qkv_w is the FULL weight; only the outputs the slice covers are written. */
+int tm_qkv16_cols_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16,
+                      void* v16, int64_t col0, int64_t ncols, int64_t max_ctas, uint32_t flags, void* stream);
 /* K5 on fp16 q/k: fp32 landmark means (fp32 accumulation) plus their fp16 copies. */
 int tm_landmarks16_fwd(const void* q16, const void* k16, int64_t B, int64_t Sp, int64_t l, float* q_lm,
                        float* k_lm, void* qlm16, void* klm16, void* stream);

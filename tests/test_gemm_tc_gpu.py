@@ -46,3 +46,29 @@ def test_gemm_tc_truncates_unrounded_operands(built_lib):
     ref = A.double() @ W.double().T
     rel = (C.double() - ref).abs().max().item() / ref.abs().max().item()
     assert rel < 5e-3
+
+
+@pytest.mark.parametrize("B,Sp", [(1, 3072), (2, 1280), (1, 50432)])
+def test_qkv_column_slices_equal_the_full_projection(built_lib, B, Sp):
+    """tm_transmil_fwd projects q,k first and v later beside the pinv chain (tm_qkv16_cols_fwd, capped grid): the slices
+    must write exactly the bits of the one-launch projection, and nothing outside their own outputs."""
+    import transmil_b200 as T
+    L = T.capi.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    g = torch.Generator().manual_seed(5)
+    xn = torch.randn(B, Sp, 512, generator=g).half().cuda()
+    w = (torch.randn(1536, 512, generator=g) * 0.04).half().cuda()
+    shape = (B, 8, Sp, 64)
+    full = [torch.empty(shape, dtype=torch.float16, device="cuda") for _ in range(3)]
+    T.capi.check(L.tm_qkv16_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *[t.data_ptr() for t in full], T.capi.TM_FLAG_F16_ACT, st))
+    ref = (xn.float() @ w.float().T).view(B, Sp, 3, 8, 64).permute(2, 0, 3, 1, 4)
+    assert (full[0].float() - ref[0] * 0.125).abs().max().item() < 2e-2 and (full[2].float() - ref[2]).abs().max().item() < 5e-2
+    part = [torch.full(shape, 7.0, dtype=torch.float16, device="cuda") for _ in range(3)]
+    ptrs = [t.data_ptr() for t in part]
+    T.capi.check(L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 0, 1024, 0, T.capi.TM_FLAG_F16_ACT, st))
+    assert torch.equal(part[0], full[0]) and torch.equal(part[1], full[1])
+    assert bool((part[2] == 7.0).all())                       # v untouched by the q,k slice
+    T.capi.check(L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 1024, 512, 100, T.capi.TM_FLAG_F16_ACT, st))
+    assert torch.equal(part[2], full[2]) and torch.equal(part[0], full[0])
+    rc = L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 256, 512, 0, T.capi.TM_FLAG_F16_ACT, st)
+    assert rc != 0

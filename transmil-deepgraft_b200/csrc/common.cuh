@@ -139,6 +139,8 @@ struct GemmParams {
   int bn128;                   // tensor-core engine: use the 128-wide N tile (small batched problems)
   // EPI_QKV
   float* q; float* k; float* v; int Sp;
+  int col_off;                 // EPI_QKV16: logical column of C column 0 (a GEMM over a column slice of to_qkv: Bm points at row col_off)
+  int max_ctas;                // tensor-core engine: cap on the persistent grid (0 = one CTA per SM); leaves SMs to a concurrent stream
 };
 int gemm_simt(const GemmParams& p, cudaStream_t st);
 

@@ -131,18 +131,22 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
     // tensor-core engine: q, k, v live as fp16 (head-major) in the q/k/v regions; all contractions accumulate in fp32
     void* q16 = q; void* k16 = k; void* v16 = v;
     void* qlm16 = ws + L.qlm16; void* klm16 = ws + L.klm16; void* mt16 = ws + L.mt16;
-    prof_mark(ST_QKV, st);
-    pdl_gate(64);
-    TM_PROPAGATE(tm_qkv16_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, flags, st));
-    prof_mark(ST_LANDMARKS, st);
-    pdl_gate(8);
-    TM_PROPAGATE(tm_landmarks16_fwd(q16, k16, B, p.Sp, p.l, q_lm, k_lm, qlm16, klm16, st));
     // sim2 + pinv (32 CTAs per bag, a latency-bound chain of 24 dependent products) and attn3.v (every other SM) are
     // independent: fork the pinv onto the library's high-priority side stream and join before Z.W3.  Serial when the
     // stage profiler is on (its events live on `st`), when asked (TM_FLAG_NO_OVERLAP), or when the pinv clusters alone
     // would take more than a third of the SMs (B > 1).
     const int pinv_sms = 4 * (int)(B * TM_HEADS);
     const bool overlap = !(flags & (TM_FLAG_NO_OVERLAP | TM_FLAG_PINV_GEMM_CHAIN)) && !prof_enabled() && pinv_sms * 3 <= 148;
+    // With the fork, only q and k are projected before the landmarks; the v third of to_qkv runs after the fork, beside the
+    // pinv chain, on the SMs attn3.v will use (the pinv chain is the longer branch, so v comes for free).
+    static const bool split_v = [] { const char* e = getenv("TM_SPLIT_V"); return !(e && e[0] == '0'); }();
+    const bool v_late = overlap && split_v;
+    prof_mark(ST_QKV, st);
+    pdl_gate(64);
+    TM_PROPAGATE(tm_qkv16_cols_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, 0, v_late ? 2 * TM_DIM : 3 * TM_DIM, 0, flags, st));
+    prof_mark(ST_LANDMARKS, st);
+    pdl_gate(8);
+    TM_PROPAGATE(tm_landmarks16_fwd(q16, k16, B, p.Sp, p.l, q_lm, k_lm, qlm16, klm16, st));
     if (overlap) {
       SideStream ss;
       TM_PROPAGATE(side_stream(&ss));
@@ -155,6 +159,13 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
       pdl_suspend(false);
       TM_PROPAGATE(pinv_rc);
       TM_CUDA(cudaEventRecord(ss.join, ss.stream));
+      if (v_late) {
+        int sms = 148, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        pdl_plain_next();   // an event record sits between landmarks and this launch
+        TM_PROPAGATE(tm_qkv16_cols_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, 2 * TM_DIM, TM_DIM, sms - pinv_sms, flags, st));
+      }
       if (pdl_x & 1) pdl_plain_next();   // an event record sits between landmarks and this launch
       if (pdl_x & 4) pdl_suspend(true);
       const int a3_rc = attn3v_tc_fwd_budget(qlm16, k16, v16, B, p.Sp, W3, ws + L.a3_s, pinv_sms, st);
@@ -269,17 +280,28 @@ extern "C" int tm_qkv_fwd(const float* xn, const float* qkv_w, int64_t B, int64_
   return gemm_auto(g, flags, (cudaStream_t)stream);
 }
 
-extern "C" int tm_qkv16_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
-                            uint32_t flags, void* stream) {
+extern "C" int tm_qkv16_cols_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
+                                 int64_t col0, int64_t ncols, int64_t max_ctas, uint32_t flags, void* stream) {
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0 && B * Sp < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_qkv16_fwd: bad shape B=%lld Sp=%lld", (long long)B, (long long)Sp);
   TM_CHECK_ARG(xn && qkv_w && q16 && k16 && v16, TM_ERR_BAD_ARGUMENT, "tm_qkv16_fwd: NULL pointer");
+  TM_CHECK_ARG(col0 >= 0 && ncols > 0 && col0 % TM_DIM == 0 && ncols % TM_DIM == 0 && col0 + ncols <= 3 * TM_DIM, TM_ERR_BAD_SHAPE,
+               "tm_qkv16_cols_fwd: the column slice must be whole q / k / v blocks (col0=%lld ncols=%lld)", (long long)col0, (long long)ncols);
+  const bool f16 = (flags & TM_FLAG_F16_ACT) != 0;   // xn and qkv_w are fp16
   GemmParams g;
   memset(&g, 0, sizeof(g));
-  g.A = (const float*)xn; g.Bm = (const float*)qkv_w; g.C = nullptr;
-  g.M = (int)(B * Sp); g.N = 3 * TM_DIM; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = 3 * TM_DIM;
+  g.A = (const float*)xn;
+  g.Bm = (const float*)((const char*)qkv_w + (size_t)col0 * TM_DIM * (f16 ? 2 : 4));
+  g.C = nullptr;
+  g.M = (int)(B * Sp); g.N = (int)ncols; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = 3 * TM_DIM;
   g.batch = 1; g.epi = EPI_QKV16; g.q = (float*)q16; g.k = (float*)k16; g.v = (float*)v16; g.Sp = (int)Sp;
-  g.f16_in = (flags & TM_FLAG_F16_ACT) ? 1 : 0;   // xn and qkv_w are fp16
+  g.col_off = (int)col0; g.max_ctas = (int)max_ctas;
+  g.f16_in = f16 ? 1 : 0;
   return gemm_auto(g, flags, (cudaStream_t)stream);
+}
+
+extern "C" int tm_qkv16_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
+                            uint32_t flags, void* stream) {
+  return tm_qkv16_cols_fwd(xn, qkv_w, B, Sp, q16, k16, v16, 0, 3 * TM_DIM, 0, flags, stream);
 }
 
 extern "C" int tm_to_out_residual_fwd(const float* merged, const float* out_w, const float* out_b, const float* h_in,

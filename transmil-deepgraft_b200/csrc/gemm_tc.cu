@@ -241,7 +241,7 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
           named_bar_sync(1, 128);
         }
         if (FAST == FAST_QKV16) {
-          const float sc = c0 < TM_DIM ? 0.125f : 1.0f;   // q * dim_head^-0.5 (exact in fp16)
+          const float sc = c0 + p.col_off < TM_DIM ? 0.125f : 1.0f;   // q * dim_head^-0.5 (exact in fp16)
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 u;
@@ -261,7 +261,7 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
         if (leader) {
           const uint8_t* src = obuf + b * 16384;
           if (FAST == FAST_QKV16) {
-            const int cb = c0 - 32;  // first column of the 64-wide head slice
+            const int cb = c0 + p.col_off - 32;  // first column of the 64-wide head slice
             const int which = cb / TM_DIM, hh = (cb % TM_DIM) / TM_DHEAD;
             tma_store_3d(&om.m[which], src, 0, i0, bag * TM_HEADS + hh);
           } else if (FAST == FAST_BIAS_RESID) {
@@ -493,8 +493,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             case EPI_QKV:
             case EPI_QKV16: {
-              const int which = c / TM_DIM;               // uniform over the 32-column chunk
-              const int cc = c - which * TM_DIM;
+              const int cl = c + p.col_off;               // column of the full [q | k | v] projection
+              const int which = cl / TM_DIM;              // uniform over the 32-column chunk
+              const int cc = cl - which * TM_DIM;
               const int hh = cc / TM_DHEAD, d = cc % TM_DHEAD;
               const float s = which == 0 ? 0.125f : 1.0f;  // q * dim_head^-0.5
               float* base = which == 0 ? p.q : (which == 1 ? p.k : p.v);
@@ -559,7 +560,8 @@ static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcOut
   const int m_tiles = (int)ceil_div(p.M, TC_BM), n_tiles = (int)ceil_div(p.N, BN), k_blocks = (int)ceil_div(p.K, BK);
   const long long total = (long long)m_tiles * n_tiles * batch;
   TM_CHECK_ARG(total < (1ll << 31), TM_ERR_BAD_SHAPE, "gemm_tc: too many tiles");
-  const int grid = total < sms ? (int)total : sms;
+  int grid = total < sms ? (int)total : sms;
+  if (p.max_ctas > 0 && grid > p.max_ctas) grid = p.max_ctas;
   launch_pdl(gemm_tc_kernel<BN, F16, FAST>, dim3(grid), dim3(TcCfg<BN, FAST>::THREADS), TcCfg<BN, FAST>::SMEM, st, tmA, tmB, om, p, m_tiles,
              n_tiles, k_blocks, (int)total);
   TM_LAUNCH_CHECK();
@@ -569,7 +571,8 @@ static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcOut
 // Chooses the TMA-store epilogue when the row map of the call is expressible as tensor-map coordinates.
 static int pick_fast(const GemmParams& p, int batch, TcOutMaps* om) {
   if (batch != 1 || p.N % 32 != 0 || p.bn128) return FAST_NONE;
-  if (p.epi == EPI_QKV16 && p.Sp % TC_BM == 0 && p.M % p.Sp == 0 && p.N == 3 * TM_DIM) {
+  if (p.epi == EPI_QKV16 && p.Sp % TC_BM == 0 && p.M % p.Sp == 0 && p.N + p.col_off <= 3 * TM_DIM && p.N % TM_DIM == 0 &&
+      p.col_off % TM_DIM == 0) {
     const uint64_t nb = (uint64_t)(p.M / p.Sp) * TM_HEADS;
     const void* base[3] = {p.q, p.k, p.v};
     for (int i = 0; i < 3; ++i)
