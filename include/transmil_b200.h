@@ -228,9 +228,16 @@ int tm_qkv16_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void*
                  void* v16, uint32_t flags, void* stream);
 /* The same projection restricted to columns [col0, col0+ncols) of to_qkv (whole q / k / v blocks: multiples of 512).
  * tm_transmil_fwd projects q and k first, forks the pinv chain, and projects v beside it on max_ctas SMs (0 = all).
- * qkv_w is the FULL weight; only the outputs the slice covers are written. */
+ * qkv_w is the FULL weight; only the outputs the slice covers are written.
+ * lm_part (may be NULL; needs col0 == 0, fp16 operands and l = Sp/256 >= 128): B*(Sp/128)*8*1024 floats that receive the
+ * column sums of every stored 128-row q / k box, split at the landmark-group boundary inside the box and by row quarter
+ * (layout in csrc/common.cuh GemmParams::lm_part); tm_landmarks_parts_fwd turns them into the landmark means, so q and k
+ * are not read a second time ('... (n l) d -> ... n d' sum / l of nystrom-attention). */
 int tm_qkv16_cols_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16,
-                      void* v16, int64_t col0, int64_t ncols, int64_t max_ctas, uint32_t flags, void* stream);
+                      void* v16, int64_t col0, int64_t ncols, int64_t max_ctas, float* lm_part, uint32_t flags,
+                      void* stream);
+int tm_landmarks_parts_fwd(const float* lm_part, int64_t B, int64_t Sp, int64_t l, float* q_lm, float* k_lm,
+                           void* qlm16, void* klm16, void* stream);
 /* K5 on fp16 q/k: fp32 landmark means (fp32 accumulation) plus their fp16 copies. */
 int tm_landmarks16_fwd(const void* q16, const void* k16, int64_t B, int64_t Sp, int64_t l, float* q_lm,
                        float* k_lm, void* qlm16, void* klm16, void* stream);

@@ -65,10 +65,49 @@ def test_qkv_column_slices_equal_the_full_projection(built_lib, B, Sp):
     assert (full[0].float() - ref[0] * 0.125).abs().max().item() < 2e-2 and (full[2].float() - ref[2]).abs().max().item() < 5e-2
     part = [torch.full(shape, 7.0, dtype=torch.float16, device="cuda") for _ in range(3)]
     ptrs = [t.data_ptr() for t in part]
-    T.capi.check(L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 0, 1024, 0, T.capi.TM_FLAG_F16_ACT, st))
+    T.capi.check(L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 0, 1024, 0, None, T.capi.TM_FLAG_F16_ACT, st))
     assert torch.equal(part[0], full[0]) and torch.equal(part[1], full[1])
     assert bool((part[2] == 7.0).all())                       # v untouched by the q,k slice
-    T.capi.check(L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 1024, 512, 100, T.capi.TM_FLAG_F16_ACT, st))
+    T.capi.check(L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 1024, 512, 100, None, T.capi.TM_FLAG_F16_ACT, st))
     assert torch.equal(part[2], full[2]) and torch.equal(part[0], full[0])
-    rc = L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 256, 512, 0, T.capi.TM_FLAG_F16_ACT, st)
+    rc = L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, *ptrs, 256, 512, 0, None, T.capi.TM_FLAG_F16_ACT, st)
+    assert rc != 0
+
+
+@pytest.mark.parametrize("B,Sp", [(1, 50432), (2, 32768), (1, 33280), (1, 200704)])
+def test_landmarks_from_the_projection_epilogue(built_lib, B, Sp):
+    """l >= 128: the q,k projection leaves per-tile column sums and tm_landmarks_parts_fwd finishes the landmark means;
+    they must agree with the separate pass over the stored fp16 q / k (same values, different fp32 summation order) and
+    with a float64 mean of those values."""
+    import transmil_b200 as T
+    L = T.capi.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    l = Sp // 256
+    g = torch.Generator().manual_seed(9)
+    xn = torch.randn(B, Sp, 512, generator=g).half().cuda()
+    xn[:, :37] = 0                                              # front pad rows
+    w = (torch.randn(1536, 512, generator=g) * 0.04).half().cuda()
+    shape = (B, 8, Sp, 64)
+    q, k, v = (torch.empty(shape, dtype=torch.float16, device="cuda") for _ in range(3))
+    part = torch.full((B * (Sp // 128) * 8 * 1024,), float("nan"), device="cuda")
+    T.capi.check(L.tm_qkv16_cols_fwd(xn.data_ptr(), w.data_ptr(), B, Sp, q.data_ptr(), k.data_ptr(), v.data_ptr(), 0, 1024, 0,
+                                     part.data_ptr(), T.capi.TM_FLAG_F16_ACT, st))
+    assert not bool(torch.isnan(part).any())
+    lm = [torch.empty(B, 8, 256, 64, device="cuda") for _ in range(4)]
+    lm16 = [torch.empty(B, 8, 256, 64, dtype=torch.float16, device="cuda") for _ in range(4)]
+    T.capi.check(L.tm_landmarks_parts_fwd(part.data_ptr(), B, Sp, l, lm[0].data_ptr(), lm[1].data_ptr(), lm16[0].data_ptr(),
+                                          lm16[1].data_ptr(), st))
+    T.capi.check(L.tm_landmarks16_fwd(q.data_ptr(), k.data_ptr(), B, Sp, l, lm[2].data_ptr(), lm[3].data_ptr(), lm16[2].data_ptr(),
+                                      lm16[3].data_ptr(), st))
+    for t, src in ((lm[0], q), (lm[1], k)):
+        ref = src.double().view(B, 8, 256, l, 64).sum(3) / l
+        assert (t.double() - ref).abs().max().item() < 2e-6
+    assert (lm[0] - lm[2]).abs().max().item() < 2e-6 and (lm[1] - lm[3]).abs().max().item() < 2e-6
+    assert (lm16[0].float() - lm16[2].float()).abs().max().item() < 2e-3
+    # the same call twice gives the same bits (fixed summation order)
+    lm2 = [torch.empty(B, 8, 256, 64, device="cuda") for _ in range(2)]
+    T.capi.check(L.tm_landmarks_parts_fwd(part.data_ptr(), B, Sp, l, lm2[0].data_ptr(), lm2[1].data_ptr(), lm16[2].data_ptr(),
+                                          lm16[3].data_ptr(), st))
+    assert torch.equal(lm2[0], lm[0]) and torch.equal(lm2[1], lm[1])
+    rc = L.tm_landmarks_parts_fwd(part.data_ptr(), 1, 2560, 10, lm[0].data_ptr(), lm[1].data_ptr(), lm16[0].data_ptr(), lm16[1].data_ptr(), st)
     assert rc != 0

@@ -76,7 +76,8 @@ SIGNATURES = {
     "tm_zw_fwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp]),
     "tm_nystrom_out_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
     "tm_qkv16_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _u32, _fp]),
-    "tm_qkv16_cols_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _i64, _i64, _i64, _u32, _fp]),
+    "tm_qkv16_cols_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _i64, _i64, _i64, _fp, _u32, _fp]),
+    "tm_landmarks_parts_fwd": (C.c_int, [_fp, _i64, _i64, _i64, _fp, _fp, _fp, _fp, _fp]),
     "tm_landmarks16_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _fp, _fp, _fp, _fp, _fp]),
     "tm_stage_is_f16": (C.c_int, [C.c_char_p, _u32]),
     "tm_zw16_fwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp, _fp]),

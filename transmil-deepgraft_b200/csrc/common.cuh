@@ -141,6 +141,10 @@ struct GemmParams {
   float* q; float* k; float* v; int Sp;
   int col_off;                 // EPI_QKV16: logical column of C column 0 (a GEMM over a column slice of to_qkv: Bm points at row col_off)
   int max_ctas;                // tensor-core engine: cap on the persistent grid (0 = one CTA per SM); leaves SMs to a concurrent stream
+  // EPI_QKV16, TMA-store epilogue only: per-tile column sums of the stored fp16 q / k boxes, split at the landmark-group
+  // boundary inside the tile (needs lm_l >= 128 so that a 128-row tile meets at most two groups):
+  // lm_part[((bag * Sp/128 + tile) * 4 + row quarter) * 2 + (0: first group of the tile, 1: next group)][1024 q|k columns]
+  float* lm_part; int lm_l;
 };
 int gemm_simt(const GemmParams& p, cudaStream_t st);
 

@@ -16,6 +16,10 @@ int ppeg_fwd_prepacked(const tm_weights* w, const float* h_in, int64_t B, int64_
 int ln_inplace(float* x, const float* gamma, const float* beta, long long rows, int width, int rpb, long long bag_rows,
                int off, bool round, cudaStream_t st);
 
+static bool fused_lm_enabled() {
+  static const bool on = [] { const char* e = getenv("TM_FUSED_LM"); return e && e[0] == '1'; }();
+  return on;
+}
 static bool use_tc(uint32_t flags) { return !(flags & TM_FLAG_SIMT_ONLY) && tc_available(); }
 
 static int gemm_auto(const GemmParams& p, uint32_t flags, cudaStream_t st) {
@@ -52,6 +56,7 @@ struct Layout {
   size_t h[4], fc1s, xn, merged, q, k, v, small[2][6], pinv_s, a3_s, packed;
   size_t wr_fc1_0, wr_fc1_1, wr_qkv[2], wr_out[2];   // tf32-rounded copies of the GEMM weights
   size_t qlm16, klm16, mt16;                         // fp16 operands of the tensor-core attention kernels
+  size_t lm_part;                                    // per-tile landmark partial sums of the q,k projection (l >= 128 only)
 };
 enum { SM_QLM = 0, SM_KLM, SM_ATTN2, SM_Z, SM_W3, SM_M };
 
@@ -95,6 +100,7 @@ static int make_layout(int64_t B, const tm_plan& p, const tm_weights* w, uint32_
   L->klm16 = bump(cur, lm / 2);
   L->mt16 = bump(cur, lm / 2);
   L->packed = bump(cur, 50 * TM_DIM);
+  L->lm_part = bump(cur, (fused_lm_enabled() && p.l >= 128) ? (size_t)B * (p.Sp / 128) * 8 * (2 * TM_DIM) : 0);
   L->wr_fc1_0 = bump(cur, (size_t)(f0 ? f0 : TM_DIM) * w->in_features);
   L->wr_fc1_1 = bump(cur, (size_t)TM_DIM * f0);
   for (int l = 0; l < 2; ++l) {
@@ -141,12 +147,19 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
     // pinv chain, on the SMs attn3.v will use (the pinv chain is the longer branch, so v comes for free).
     static const bool split_v = [] { const char* e = getenv("TM_SPLIT_V"); return !(e && e[0] == '0'); }();
     const bool v_late = overlap && split_v;
+    // Opt-in (TM_FUSED_LM=1), bags of >= 32 768 padded tokens (l >= 128): the projection's epilogue leaves per-tile column
+    // sums of the q / k boxes it stores and the landmark means come from those 13 MB instead of a second pass over q and k
+    // (103 MB at 50 k).  Measured on B200 at 50 k: landmarks 24.7 -> 10.2 us but qkv 69 -> 87 us (the epilogue is what
+    // bounds that GEMM), 0.895 -> 0.908 ms per bag -- so the separate landmarks16 pass stays the default.
+    const bool fused_lm = fused_lm_enabled() && p.l >= 128 && (flags & TM_FLAG_F16_ACT);
+    float* lm_part = fused_lm ? ws + L.lm_part : nullptr;
     prof_mark(ST_QKV, st);
     pdl_gate(64);
-    TM_PROPAGATE(tm_qkv16_cols_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, 0, v_late ? 2 * TM_DIM : 3 * TM_DIM, 0, flags, st));
+    TM_PROPAGATE(tm_qkv16_cols_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, 0, v_late ? 2 * TM_DIM : 3 * TM_DIM, 0, lm_part, flags, st));
     prof_mark(ST_LANDMARKS, st);
     pdl_gate(8);
-    TM_PROPAGATE(tm_landmarks16_fwd(q16, k16, B, p.Sp, p.l, q_lm, k_lm, qlm16, klm16, st));
+    if (fused_lm) TM_PROPAGATE(tm_landmarks_parts_fwd(lm_part, B, p.Sp, p.l, q_lm, k_lm, qlm16, klm16, st));
+    else TM_PROPAGATE(tm_landmarks16_fwd(q16, k16, B, p.Sp, p.l, q_lm, k_lm, qlm16, klm16, st));
     if (overlap) {
       SideStream ss;
       TM_PROPAGATE(side_stream(&ss));
@@ -164,7 +177,7 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         pdl_plain_next();   // an event record sits between landmarks and this launch
-        TM_PROPAGATE(tm_qkv16_cols_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, 2 * TM_DIM, TM_DIM, sms - pinv_sms, flags, st));
+        TM_PROPAGATE(tm_qkv16_cols_fwd(xn, lw.qkv_w, B, p.Sp, q16, k16, v16, 2 * TM_DIM, TM_DIM, sms - pinv_sms, nullptr, flags, st));
       }
       if (pdl_x & 1) pdl_plain_next();   // an event record sits between landmarks and this launch
       if (pdl_x & 4) pdl_suspend(true);
@@ -281,7 +294,7 @@ extern "C" int tm_qkv_fwd(const float* xn, const float* qkv_w, int64_t B, int64_
 }
 
 extern "C" int tm_qkv16_cols_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
-                                 int64_t col0, int64_t ncols, int64_t max_ctas, uint32_t flags, void* stream) {
+                                 int64_t col0, int64_t ncols, int64_t max_ctas, float* lm_part, uint32_t flags, void* stream) {
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0 && B * Sp < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_qkv16_fwd: bad shape B=%lld Sp=%lld", (long long)B, (long long)Sp);
   TM_CHECK_ARG(xn && qkv_w && q16 && k16 && v16, TM_ERR_BAD_ARGUMENT, "tm_qkv16_fwd: NULL pointer");
   TM_CHECK_ARG(col0 >= 0 && ncols > 0 && col0 % TM_DIM == 0 && ncols % TM_DIM == 0 && col0 + ncols <= 3 * TM_DIM, TM_ERR_BAD_SHAPE,
@@ -295,13 +308,15 @@ extern "C" int tm_qkv16_cols_fwd(const void* xn, const void* qkv_w, int64_t B, i
   g.M = (int)(B * Sp); g.N = (int)ncols; g.K = TM_DIM; g.lda = TM_DIM; g.ldb = TM_DIM; g.ldc = 3 * TM_DIM;
   g.batch = 1; g.epi = EPI_QKV16; g.q = (float*)q16; g.k = (float*)k16; g.v = (float*)v16; g.Sp = (int)Sp;
   g.col_off = (int)col0; g.max_ctas = (int)max_ctas;
+  g.lm_part = lm_part; g.lm_l = (int)(Sp / TM_LANDMARKS);
+  TM_CHECK_ARG(lm_part == nullptr || col0 == 0, TM_ERR_BAD_ARGUMENT, "tm_qkv16_cols_fwd: landmark partial sums need the slice to start at q");
   g.f16_in = f16 ? 1 : 0;
   return gemm_auto(g, flags, (cudaStream_t)stream);
 }
 
 extern "C" int tm_qkv16_fwd(const void* xn, const void* qkv_w, int64_t B, int64_t Sp, void* q16, void* k16, void* v16,
                             uint32_t flags, void* stream) {
-  return tm_qkv16_cols_fwd(xn, qkv_w, B, Sp, q16, k16, v16, 0, 3 * TM_DIM, 0, flags, stream);
+  return tm_qkv16_cols_fwd(xn, qkv_w, B, Sp, q16, k16, v16, 0, 3 * TM_DIM, 0, nullptr, flags, stream);
 }
 
 extern "C" int tm_to_out_residual_fwd(const float* merged, const float* out_w, const float* out_b, const float* h_in,

@@ -258,6 +258,34 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
       if (last) {
         fence_proxy_async();         // generic-proxy smem writes -> visible to the TMA engine
         named_bar_sync(1, 128);
+        if (FAST == FAST_QKV16 && p.lm_part != nullptr && c0 + p.col_off - 32 < 2 * TM_DIM) {
+          // landmark partial sums of this box (q or k head slice), read back from the fp16 values the box holds: lane =
+          // column pair, warp = row quarter; rows before `rb` belong to the tile's first landmark group, the rest to the next
+          const uint8_t* box = obuf + b * 16384;
+          const int g0 = i0 / p.lm_l;
+          const int rb = (g0 + 1) * p.lm_l - i0;                    // first row of the next group (may lie beyond the tile)
+          const int split = min(32, max(0, rb - q * 32));           // rows of this quarter that fall before the boundary
+          const uint32_t coff = (uint32_t)(lane & 3) * 4;
+          const int c16 = lane >> 2;
+          float ax = 0.f, ay = 0.f, bx = 0.f, by = 0.f;
+          int rr = 0;
+          for (; rr < split; ++rr) {
+            const int r = q * 32 + rr;
+            const uint32_t u = *reinterpret_cast<const uint32_t*>(box + r * 128 + ((c16 ^ (r & 7)) << 4) + coff);
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u));
+            ax += f.x; ay += f.y;
+          }
+          for (; rr < 32; ++rr) {
+            const int r = q * 32 + rr;
+            const uint32_t u = *reinterpret_cast<const uint32_t*>(box + r * 128 + ((c16 ^ (r & 7)) << 4) + coff);
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u));
+            bx += f.x; by += f.y;
+          }
+          const long long trow = ((long long)bag * (p.Sp / TC_BM) + i0 / TC_BM) * 4 + q;
+          float* dst = p.lm_part + (trow * 2) * (2 * TM_DIM) + (c0 + p.col_off - 32) + 2 * lane;
+          *reinterpret_cast<float2*>(dst) = make_float2(ax, ay);
+          *reinterpret_cast<float2*>(dst + 2 * TM_DIM) = make_float2(bx, by);
+        }
         if (leader) {
           const uint8_t* src = obuf + b * 16384;
           if (FAST == FAST_QKV16) {
@@ -620,6 +648,8 @@ int gemm_tc(const GemmParams& p, cudaStream_t st) {
   TcOutMaps om;
   memset(&om, 0, sizeof(om));
   const int fast = pick_fast(p, batch, &om);
+  TM_CHECK_ARG(p.lm_part == nullptr || (fast == FAST_QKV16 && p.f16_in && !p.bn128 && p.lm_l >= TC_BM && p.lm_l * TM_LANDMARKS == p.Sp),
+               TM_ERR_BAD_SHAPE, "gemm_tc: landmark partial sums need the fp16 TMA-store qkv epilogue and l >= 128");
   if (p.f16_in) {
     TM_PROPAGATE(make_tmap_3d_f16(&tmA, p.A, batch, (uint64_t)p.M, (uint64_t)p.K, sA, (uint64_t)p.lda, TC_BM, 64));
     if (p.bn128) {

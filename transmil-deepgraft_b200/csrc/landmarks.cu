@@ -90,7 +90,54 @@ __global__ void __launch_bounds__(256) landmarks16_kernel(const __half* __restri
   reinterpret_cast<uint4*>((is_k ? klm16 : qlm16) + g * TM_DHEAD)[lane8] = o;
 }
 
+// Landmark means from the per-tile partial column sums the q,k projection left behind (GemmParams::lm_part): group j of
+// l >= 128 rows meets the tiles floor(j l / 128) .. floor(((j+1) l - 1) / 128); of each tile it takes the "first group" or
+// the "next group" half, four row quarters each, always in ascending row order (deterministic).
+__global__ void __launch_bounds__(256) landmarks_from_parts_kernel(const float* __restrict__ part, int tiles_per_bag, int l,
+                                                                   long long total, float* __restrict__ q_lm, float* __restrict__ k_lm,
+                                                                   __half* __restrict__ qlm16, __half* __restrict__ klm16) {
+  pdl_sync();
+  const long long i = ((long long)blockIdx.x * 256 + threadIdx.x) * 2;   // (b, which, h, j, d pair)
+  if (i >= total) return;
+  const int d = (int)(i % TM_DHEAD);
+  long long r = i / TM_DHEAD;
+  const int j = (int)(r % TM_LANDMARKS); r /= TM_LANDMARKS;
+  const int h = (int)(r % TM_HEADS); r /= TM_HEADS;
+  const int which = (int)(r % 2);
+  const long long b = r / 2;
+  const int col = which * TM_DIM + h * TM_DHEAD + d;
+  const int t0 = (int)(((long long)j * l) / 128), t1 = (int)((((long long)j + 1) * l - 1) / 128);
+  float sx = 0.f, sy = 0.f;
+  for (int t = t0; t <= t1; ++t) {
+    const int g0 = (t * 128) / l;
+    const int ab = j == g0 ? 0 : 1;
+    const float* p = part + (((b * tiles_per_bag + t) * 4) * 2 + ab) * (long long)(2 * TM_DIM) + col;
+#pragma unroll
+    for (int rq = 0; rq < 4; ++rq) {
+      const float2 v = __ldg(reinterpret_cast<const float2*>(p + (long long)rq * 2 * (2 * TM_DIM)));
+      sx += v.x; sy += v.y;
+    }
+  }
+  const float fl = (float)l;
+  sx /= fl; sy /= fl;
+  const long long o = ((b * TM_HEADS + h) * TM_LANDMARKS + j) * TM_DHEAD + d;
+  *reinterpret_cast<float2*>((which ? k_lm : q_lm) + o) = make_float2(sx, sy);
+  *reinterpret_cast<uint32_t*>((which ? klm16 : qlm16) + o) = pack_f16x2(sx, sy);
+}
+
 }  // namespace tmil
+
+extern "C" int tm_landmarks_parts_fwd(const float* lm_part, int64_t B, int64_t Sp, int64_t l, float* q_lm, float* k_lm,
+                                      void* qlm16, void* klm16, void* stream) {
+  TM_CHECK_ARG(B > 0 && l >= 128 && Sp == l * TM_LANDMARKS, TM_ERR_BAD_SHAPE,
+               "tm_landmarks_parts_fwd: needs Sp = 256*l with l >= 128 (Sp=%lld l=%lld)", (long long)Sp, (long long)l);
+  TM_CHECK_ARG(lm_part && q_lm && k_lm && qlm16 && klm16, TM_ERR_BAD_ARGUMENT, "tm_landmarks_parts_fwd: NULL pointer");
+  const long long total = (long long)B * 2 * TM_HEADS * TM_LANDMARKS * TM_DHEAD;
+  tmil::launch_pdl(tmil::landmarks_from_parts_kernel, dim3((unsigned)tmil::ceil_div(total / 2, 256)), dim3(256), 0, (cudaStream_t)stream,
+                   lm_part, (int)(Sp / 128), (int)l, total, q_lm, k_lm, (__half*)qlm16, (__half*)klm16);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
 
 extern "C" int tm_landmarks_fwd(const float* q, const float* k, int64_t B, int64_t Sp, int64_t l, float* q_lm,
                                 float* k_lm, void* stream) {
