@@ -127,6 +127,8 @@ template <int BN, int FAST = 0> struct TcCfg {
   static constexpr int B_BYTES = BN * 128;
   // the bias+residual epilogue streams the residual through four in-place [128][128 B] boxes (TMA load -> add -> TMA store)
   // and gives up one operand stage for them
+  // (four boxes + three stages for the other TMA-store epilogues too was measured slower: fc1 99 -> 109 us, qkv 74 -> 77 us,
+  // profiles/r1_gemm_epilogue_study.txt -- the operand pipeline needs its fourth stage more than the stores need boxes)
   static constexpr int STAGES = BN == 256 ? (FAST == 2 ? 3 : 4) : 6;
   static constexpr int OUT_BYTES = FAST == 2 ? 4 * 16384 : TC_OUT_BYTES;
   static constexpr int THREADS = FAST == 2 ? 224 : TC_THREADS;   // + one warp that loads the residual boxes
@@ -196,11 +198,29 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
     const int srow = rt - shift;                // row of the smem box
     mbar_wait(&tfull[as], aphase);
     tc_fence_after();
+    if (p.dbg == 1) {   // measurement: release the accumulator, do nothing else
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+      continue;
+    }
     const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
 #pragma unroll 1
     for (int chunk = 0; chunk < BN / 32; ++chunk) {
       float v[32];
       tmem_ld_32x32(t_row + chunk * 32, v);
+      if (p.dbg == 2) {   // measurement: TMEM loads and a stand-in for the math, nothing stored
+        float acc = 0.f;
+#pragma unroll
+        for (int e = 0; e < 32; ++e) acc += v[e] * 0.125f;
+        if (acc == 12345.678f) obuf[0] = 1;
+        if (chunk == BN / 32 - 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[as]);
+        }
+        continue;
+      }
       if (chunk == BN / 32 - 1) {   // accumulator fully read: hand the TMEM buffer back to the MMA warp
         tc_fence_before();
         __syncwarp();
@@ -208,7 +228,6 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
       }
       const int c0 = n_blk * BN + chunk * 32;
       if (c0 >= p.N || shift >= TC_BM) continue;      // uniform over the CTA
-      const bool first = FAST == FAST_QKV16 ? (chunk & 1) == 0 : true;
       const bool last = FAST == FAST_QKV16 ? (chunk & 1) == 1 : true;
       const int b = unit % NBUF;
       uint8_t* rowp = obuf + b * 16384 + srow * 128;
@@ -236,10 +255,7 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
           }
         }
       } else {
-        if (first) {                 // the box written NBUF units ago must have been read out by its TMA store
-          if (leader) tma_store_wait_read<1>();
-          named_bar_sync(1, 128);
-        }
+        // (no barrier here: the buffer of this unit was freed before the previous unit's barrier, see below)
         if (FAST == FAST_QKV16) {
           const float sc = c0 + p.col_off < TM_DIM ? 0.125f : 1.0f;   // q * dim_head^-0.5 (exact in fp16)
 #pragma unroll
@@ -256,8 +272,13 @@ __device__ __forceinline__ void epilogue_fast(const GemmParams& p, const TcOutMa
         }
       }
       if (last) {
+        if (p.dbg == 3) { ++unit; continue; }   // measurement: smem writes only
         fence_proxy_async();         // generic-proxy smem writes -> visible to the TMA engine
+        // ONE barrier per box.  Two boxes rotate: before arriving, the leader waits until the store of the PREVIOUS box
+        // (issued a whole unit ago) has drained its buffer -- that is the buffer the next unit writes after this barrier.
+        if (FAST != FAST_BIAS_RESID && leader) tma_store_wait_read<0>();
         named_bar_sync(1, 128);
+        if (p.dbg == 4) { ++unit; continue; }   // measurement: everything but the TMA store
         if (FAST == FAST_QKV16 && p.lm_part != nullptr && c0 + p.col_off - 32 < 2 * TM_DIM) {
           // landmark partial sums of this box (q or k head slice), read back from the fp16 values the box holds: lane =
           // column pair, warp = row quarter; rows before `rb` belong to the tile's first landmark group, the rest to the next
@@ -590,7 +611,10 @@ static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcOut
   TM_CHECK_ARG(total < (1ll << 31), TM_ERR_BAD_SHAPE, "gemm_tc: too many tiles");
   int grid = total < sms ? (int)total : sms;
   if (p.max_ctas > 0 && grid > p.max_ctas) grid = p.max_ctas;
-  launch_pdl(gemm_tc_kernel<BN, F16, FAST>, dim3(grid), dim3(TcCfg<BN, FAST>::THREADS), TcCfg<BN, FAST>::SMEM, st, tmA, tmB, om, p, m_tiles,
+  static const int dbg = [] { const char* e = getenv("TM_GEMM_DBG"); return e ? atoi(e) : 0; }();
+  GemmParams pd = p;
+  pd.dbg = FAST == FAST_BIAS_RESID ? 0 : dbg;   // the residual ring has its own loader handshake: never switched off
+  launch_pdl(gemm_tc_kernel<BN, F16, FAST>, dim3(grid), dim3(TcCfg<BN, FAST>::THREADS), TcCfg<BN, FAST>::SMEM, st, tmA, tmB, om, pd, m_tiles,
              n_tiles, k_blocks, (int)total);
   TM_LAUNCH_CHECK();
   return TM_OK;

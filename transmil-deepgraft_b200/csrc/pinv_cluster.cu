@@ -29,9 +29,6 @@ constexpr int PC_STAGE_BYTES = 32768;                    // the CTA's own 128 x 
 constexpr size_t PC_SMEM = 1024 + 2 * PC_OP_BYTES + PC_STAGE_BYTES + 256;
 constexpr int PC_STEPS = 4 * TM_PINV_ITERS;
 
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
 struct PinvMaps {
