@@ -272,10 +272,9 @@ static int attn3v_tc_run(const void* qlm16, const void* k16, const void* v16, in
   TM_PROPAGATE(make_tmap_3d_f16(&tmQ, qlm16, nbh, TM_LANDMARKS, TM_DHEAD, TM_LANDMARKS * TM_DHEAD, TM_DHEAD, TM_LANDMARKS, TM_DHEAD));
   TM_PROPAGATE(make_tmap_3d_f16(&tmK, k16, nbh, Sp, TM_DHEAD, Sp * TM_DHEAD, TM_DHEAD, A3_TOK, TM_DHEAD));
   TM_PROPAGATE(make_tmap_3d_f16(&tmV, v16, nbh, Sp, TM_DHEAD, Sp * TM_DHEAD, TM_DHEAD, A3_TOK, TM_DHEAD));
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_device(&attr_done)) {
     TM_CUDA(cudaFuncSetAttribute(attn3v_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A3_SMEM));
-    attr_done = true;
   }
   const int tiles_per_bh = (int)(Sp / A3_TOK);
   int chunks = attn_chunks(nbh, tiles_per_bh);

@@ -103,6 +103,17 @@ static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 blo
 }
 #endif
 
+// cudaFuncSetAttribute applies to the current device only: `done` is a per-call-site bit mask of the devices that already
+// have the attribute (one process per GPU is the normal deployment, but a process may also drive several devices).
+static inline bool first_use_on_device(unsigned long long* done) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (*done & bit) return false;
+  *done |= bit;
+  return true;
+}
+
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

@@ -597,13 +597,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 template <int BN, bool F16, int FAST>
 static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcOutMaps& om, const GemmParams& p, int batch, cudaStream_t st) {
   static int sms = 0;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_device(&attr_done)) {
     int dev = 0;
     TM_CUDA(cudaGetDevice(&dev));
     TM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     TM_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, F16, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TcCfg<BN, FAST>::SMEM));
-    attr_done = true;
   }
   const int BK = F16 ? 64 : 32;
   const int m_tiles = (int)ceil_div(p.M, TC_BM), n_tiles = (int)ceil_div(p.N, BN), k_blocks = (int)ceil_div(p.K, BK);

@@ -123,11 +123,10 @@ extern "C" int tm_nystrom_out_fwd(const float* q, const float* k_lm, const float
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE, "tm_nystrom_out_fwd: Sp must be a multiple of 256 (Sp=%lld)", (long long)Sp);
   TM_CHECK_ARG(q && k_lm && M && v && conv_w && merged, TM_ERR_BAD_ARGUMENT, "tm_nystrom_out_fwd: NULL pointer");
   const size_t smem = (size_t)(2 * TM_LANDMARKS * TM_DHEAD + (NO_TOK + 2 * NO_HALO) * TM_DHEAD) * sizeof(float);
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_device(&attr_done)) {
     TM_CUDA(cudaFuncSetAttribute(nystrom_out_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     TM_CUDA(cudaFuncSetAttribute(nystrom_out_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done = true;
   }
   dim3 grid((unsigned)(Sp / NO_TOK), (unsigned)(B * TM_HEADS));
   if (flags & TM_FLAG_TF32_OPERANDS)

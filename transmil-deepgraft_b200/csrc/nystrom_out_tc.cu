@@ -375,10 +375,9 @@ extern "C" int tm_zw16_fwd(const float* Z, const float* W3, int64_t B, float* M,
   using namespace tmil;
   TM_CHECK_ARG(Z && W3 && M && mt16 && B > 0, TM_ERR_BAD_ARGUMENT, "tm_zw16_fwd: bad arguments");
   const size_t smem = (size_t)(TM_LANDMARKS * TM_DHEAD + 16 * TM_LANDMARKS) * sizeof(float);
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_device(&attr_done)) {
     TM_CUDA(cudaFuncSetAttribute(zw16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done = true;
   }
   launch_pdl(zw16_kernel, dim3(16, (unsigned)(B * TM_HEADS)), dim3(256), smem, (cudaStream_t)stream, Z, W3, M, (__half*)mt16);
   TM_LAUNCH_CHECK();
@@ -397,12 +396,11 @@ extern "C" int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const v
   TM_PROPAGATE(make_tmap_3d_f16(&tmV, v16, nbh, Sp, TM_DHEAD, Sp * TM_DHEAD, TM_DHEAD, NT_HALO_ROWS, TM_DHEAD));
   TM_PROPAGATE(make_tmap_3d_f16(&tmK, klm16, nbh, TM_LANDMARKS, TM_DHEAD, TM_LANDMARKS * TM_DHEAD, TM_DHEAD, TM_LANDMARKS, TM_DHEAD));
   TM_PROPAGATE(make_tmap_3d_f16(&tmM, mt16, nbh, TM_DHEAD, TM_LANDMARKS, TM_DHEAD * TM_LANDMARKS, TM_LANDMARKS, TM_DHEAD, 64));
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_device(&attr_done)) {
     TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
     TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
     TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
-    attr_done = true;
   }
   const int tiles_per_bh = (int)(Sp / NT_TOK);
   const int chunks = attn_chunks(nbh, tiles_per_bh);

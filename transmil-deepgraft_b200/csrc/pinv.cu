@@ -182,12 +182,11 @@ extern "C" int tm_pinv_fwd(const float* q_lm, const float* k_lm, int64_t B, floa
   float* colpart = rowsum + (long long)nbh * LM;
   float* scale = colpart + (long long)nbh * LM * (LM / ROWS);
 
-  static bool attr_done = false;
+  static unsigned long long attr_done = 0;
   const size_t smem = (size_t)(LM * KLD + ROWS * KLD + ROWS * 257) * sizeof(float);
-  if (!attr_done) {
+  if (first_use_on_device(&attr_done)) {
     TM_CUDA(cudaFuncSetAttribute(attn2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     TM_CUDA(cudaFuncSetAttribute(attn2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done = true;
   }
   const bool cluster = tc && !(flags & TM_FLAG_PINV_GEMM_CHAIN);
   if (tc && !cluster) launch_pdl(attn2_kernel<true>, dim3(LM / ROWS, nbh), dim3(256), smem, st, q_lm, k_lm, attn2, rowsum, colpart);

@@ -336,10 +336,9 @@ int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpa
   CUtensorMap* ms[6] = {&maps.A, &maps.Za, &maps.Zb, &maps.XZ, &maps.T1, &maps.T2};
   for (int i = 0; i < 6; ++i)
     TM_PROPAGATE(make_tmap_3d_f16(ms[i], ptrs[i], nbh, TM_LANDMARKS, TM_LANDMARKS, mat, TM_LANDMARKS, 64, 64));
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_device(&attr_done)) {
     TM_CUDA(cudaFuncSetAttribute(pinv_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PC_SMEM));
-    attr_done = true;
   }
   pinv_cluster_kernel<<<dim3(4, nbh), PC_THREADS, PC_SMEM, st>>>(maps, Za, Zb, XZ, T1, T2, Z);
   TM_LAUNCH_CHECK();

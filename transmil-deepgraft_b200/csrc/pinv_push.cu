@@ -363,10 +363,10 @@ int pinv_push_launch(__half* A16, __half* Za, __half* Zb, int nbh, float* Z, cud
   CUtensorMap* ms[3] = {&maps.A, &maps.Za, &maps.Zb};
   for (int i = 0; i < 3; ++i)
     TM_PROPAGATE(make_tmap_3d_f16(ms[i], ptrs[i], nbh, TM_LANDMARKS, TM_LANDMARKS, mat, TM_LANDMARKS, 64, 64));
-  static int remote_st = -1;
-  if (remote_st < 0) {
-    const char* e = getenv("TM_PINV_KERNEL");
-    remote_st = (e != nullptr && strcmp(e, "remote") == 0) ? 1 : 0;   // default: cp.async.bulk pushes; TM_PINV_KERNEL=remote: st.shared::cluster
+  // default: cp.async.bulk pushes; TM_PINV_KERNEL=remote: st.shared::cluster
+  static const int remote_st = [] { const char* e = getenv("TM_PINV_KERNEL"); return (e != nullptr && strcmp(e, "remote") == 0) ? 1 : 0; }();
+  static unsigned long long attr_done = 0;
+  if (first_use_on_device(&attr_done)) {
     TM_CUDA(cudaFuncSetAttribute(pinv_push_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PP_SMEM_BYTES));
     TM_CUDA(cudaFuncSetAttribute(pinv_push_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PP_SMEM_BYTES));
   }

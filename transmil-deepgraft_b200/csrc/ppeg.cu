@@ -175,10 +175,9 @@ static int ppeg_launch(const tm_weights* w, const float* in_rows, int64_t y_in0,
   const uint64_t strides[3] = {TM_DIM * sizeof(float), (uint64_t)G * TM_DIM * sizeof(float), (uint64_t)in_bag_stride * sizeof(float)};
   const uint32_t box[4] = {PP_C, PP_H, PP_H, 1};
   TM_PROPAGATE(make_tmap_f32_nd(&tm, in_rows, 4, dims, strides, box));
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_device(&attr_done)) {
     TM_CUDA(cudaFuncSetAttribute(ppeg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PP_SMEM));
-    attr_done = true;
   }
   PpegArgs a;
   a.G = (int)G; a.y_in0 = (int)y_in0;
