@@ -82,3 +82,27 @@ def test_load_reference_checkpoint_keys_roundtrip():
     missing, unexpected = dst.load_state_dict(stripped, strict=True)
     assert not missing and not unexpected
     assert all(torch.equal(a, b) for a, b in zip(src.state_dict().values(), dst.state_dict().values()))
+
+
+def test_reference_checkpoint_loads_with_the_model_prefix(tmp_path):
+    """visualize_mil.py:165-172: Lightning checkpoints hold the TransMIL parameters under `model.`; keys are renamed and
+    loaded strictly, foreign keys only pass with strict=False."""
+    import torch
+    from common import build_model
+    from transmil_b200 import plugin
+    src = build_model(3, 1024, seed=7)
+    ckpt = {"state_dict": {"model." + k: v.clone() for k, v in src.state_dict().items()}, "epoch": 3}
+    dst = build_model(3, 1024, seed=8)
+    assert not torch.equal(dst.state_dict()["_fc.weight"], src.state_dict()["_fc.weight"])
+    plugin.load_reference_checkpoint(dst, ckpt)
+    for k, v in src.state_dict().items():
+        assert torch.equal(dst.state_dict()[k], v), k
+    path = tmp_path / "epoch3.ckpt"
+    torch.save(ckpt, path)
+    dst2 = build_model(3, 1024, seed=9)
+    plugin.load_reference_checkpoint(dst2, str(path))
+    assert torch.equal(dst2.state_dict()["layer1.attn.to_qkv.weight"], src.state_dict()["layer1.attn.to_qkv.weight"])
+    ckpt["state_dict"]["loss.weight"] = torch.ones(3)
+    with pytest.raises(RuntimeError):
+        plugin.load_reference_checkpoint(build_model(3, 1024, seed=1), ckpt)
+    plugin.load_reference_checkpoint(build_model(3, 1024, seed=1), ckpt, strict=False)

@@ -48,3 +48,24 @@ def model_cfg_from_yaml(cfg):
     if fe in FEATURE_DIMS:
         model["in_features"] = FEATURE_DIMS[fe]
     return model
+
+
+def load_reference_checkpoint(model, checkpoint, strict=True, map_location="cpu"):
+    """Loads a checkpoint written by the reference's Lightning run into `model` (a TransMIL of this package).
+
+    The reference saves `ModelInterface.state_dict()`, whose TransMIL parameters carry the attribute prefix `model.`, and
+    restores them by replacing that prefix in every key (code/visualize_mil.py:165-172).  Same here; `checkpoint` is the
+    dict `torch.load` returns (or a path to it), with or without the outer `state_dict` entry.  Keys that do not belong
+    to the model (e.g. loss buffers of the LightningModule) are dropped when `strict` is False and raise, as the
+    reference's strict load does, when it is True."""
+    import torch
+    if isinstance(checkpoint, (str, os.PathLike)):
+        checkpoint = torch.load(checkpoint, map_location=map_location)
+    weights = checkpoint.get("state_dict", checkpoint)
+    renamed = {}
+    for key, value in weights.items():
+        renamed[key.replace("model.", "")] = value
+    if not strict:
+        own = set(model.state_dict().keys())
+        renamed = {k: v for k, v in renamed.items() if k in own}
+    return model.load_state_dict(renamed, strict=strict)
