@@ -324,6 +324,67 @@ int tm_round_tf32(const float* src, float* dst, int64_t n, void* stream);
 int tm_gemm_nt(const float* A, const float* W, float* C, int64_t M, int64_t N, int64_t K,
                uint32_t flags, void* stream);
 
+/* ---- backward (csrc/backward.cu) ------------------------------------------------------------------
+ * The reference has no backward code of its own: `training_step` (code/models/model_interface.py:333-383) differentiates
+ * TransMIL.forward (code/models/TransMIL.py:167-211) and nystrom-attention 0.0.11 with torch.autograd.  These entry points
+ * are the contractions of that backward, in the order oracle/transmil_backward.py writes them out; the host side
+ * (transmil-deepgraft_b200/training.py, a torch.autograd.Function) strings them together.  First correct build: fp32
+ * CUDA-core kernels, deterministic two-stage reductions, no atomics.  All pointers are device pointers, fp32. */
+
+/* Strided batched GEMM: C[z][m,n] = alpha * sum_k A[z][m*sam + k*sak] * B[z][k*sbk + n*sbn] + beta * L[z][m*ldl + n],
+ * z < batch (pointer + z*stride).  Element strides make every transposition a view; L may be NULL, may alias C, and
+ * ldl = 0 broadcasts a bias row.  Every dX = dY W, dW = dY^T X and attention contraction of the backward is one call. */
+int tm_bgemm(const float* A, const float* B, float* C, const float* L, int64_t M, int64_t N, int64_t K, int64_t sam, int64_t sak,
+             int64_t sbk, int64_t sbn, int64_t ldc, int64_t ldl, int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC,
+             int64_t strideL, float alpha, float beta, void* stream);
+/* In-place row softmax (attn1 / attn3 are recomputed by the backward, not kept by the forward). */
+int tm_softmax_rows(float* X, int64_t rows, int64_t len, void* stream);
+/* dP <- P * (dP - sum(dP * P, -1)): backward of P = softmax(S, -1), in place on dP. */
+int tm_softmax_rows_bwd(const float* P, float* dP, int64_t rows, int64_t len, void* stream);
+/* LayerNorm(C) over rows (eps 1e-5, affine): the 2048-d stem's LN is recomputed by the backward. */
+int tm_ln_rows_fwd(const float* x, const float* gamma, const float* beta, int64_t rows, int64_t C, float* y, void* stream);
+/* LayerNorm backward.  x [rows,C]; the dy row of x row r is (r / rows_per_bag) * dy_bag_rows + dy_row_off + r % rows_per_bag
+ * (TransLayer.norm: x is [B,S,512] while the gradient arrives on the front-padded axis [B,Sp,512], off = P).
+ * dx = (add ? add : 0) + dLN (add = the residual branch's gradient, TransMIL.py:53); g_gamma, g_beta [C]. */
+int64_t tm_ln_bwd_scratch_floats(int64_t rows, int64_t C);
+int tm_ln_rows_bwd(const float* x, const float* gamma, const float* dy, int64_t rows, int64_t C, int64_t rows_per_bag,
+                   int64_t dy_bag_rows, int64_t dy_row_off, const float* add, float* dx, float* g_gamma, float* g_beta,
+                   float* scratch, void* stream);
+/* out[c] = sum_r X[r*ld + c] (bias and cls_token gradients).  scratch: tm_colsum_scratch_floats(rows, cols). */
+int64_t tm_colsum_scratch_floats(int64_t rows, int64_t cols);
+int tm_colsum(const float* X, int64_t rows, int64_t cols, int64_t ld, float* out, float* scratch, void* stream);
+/* nn.GELU() (erf form) and its derivative; dz may alias z or dy. */
+int tm_gelu_fwd(const float* z, float* a, int64_t n, void* stream);
+int tm_gelu_bwd(const float* z, const float* dy, float* dz, int64_t n, void* stream);
+/* Training-mode Dropout(p) of to_out (nystrom-attention: to_out = Sequential(Linear, Dropout(dropout)); TransMIL.py:33 passes
+ * 0.7), applied in place after tm_to_out_residual_fwd: y = h_in + to_out  ->  h_in + mask * to_out / (1-p).  The keep mask is
+ * a counter-based function of (seed, element index), regenerated by tm_pad_front_bwd. */
+int tm_dropout_resid_fwd(float* y, const float* h_in, int64_t n, uint64_t seed, float p, void* stream);
+/* dy [B,S,C] -> out [B,S+P,C]: P zero rows in front (backward of the `[:, -S:]` slice), times the dropout mask when p > 0. */
+int tm_pad_front_bwd(const float* dy, int64_t B, int64_t S, int64_t P, int64_t C, uint64_t seed, float p, float* out, void* stream);
+/* 'b n (h d) -> b h n d' on a [B,Sp,512] gradient. */
+int tm_split_heads(const float* merged, int64_t B, int64_t Sp, float* out, void* stream);
+/* dqkv [B,Sp,1536] = [ (dq + dq_lm[group]/l) * 64^-0.5 | dk + dk_lm[group]/l | dv ]: backward of the landmark means
+ * ('... (n l) d -> ... n d' sum / l), of q *= 64^-0.5 and of the head split, in one pass. */
+int tm_qkv_grad_merge(const float* dq, const float* dk, const float* dv, const float* dq_lm, const float* dk_lm, int64_t B, int64_t Sp,
+                      int64_t l, float* dqkv, void* stream);
+/* res_conv backward: dO, v [B,8,Sp,64] -> dv [B,8,Sp,64], g_w [8,1,33,1]. */
+int tm_conv33_bwd(const float* dO, const float* v, const float* conv_w, int64_t B, int64_t Sp, float* dv, float* g_w, void* stream);
+/* moore_penrose_iter_pinv backward (6 iterations, init scalar = global max row sum x max column sum over every bag and
+ * head): A = attn2 [nb,256,256] with nb = B*8, dZ = gradient of Z (clobbered) -> dA.  The iterates are recomputed. */
+int64_t tm_pinv_bwd_scratch_floats(int64_t nb);
+int tm_pinv_bwd(const float* A, float* dZ, int64_t nb, float* dA, float* scratch, void* stream);
+/* PPEG backward (TransMIL.py:60-75): h_in, dy -> dh [B,S,512] and the six parameter gradients. */
+int64_t tm_ppeg_bwd_scratch_floats(int64_t B, int64_t G);
+int tm_ppeg_bwd(const tm_weights* w, const float* h_in, const float* dy, int64_t B, int64_t G, float* dh, float* g_w7, float* g_b7,
+                float* g_w5, float* g_b5, float* g_w3, float* g_b3, float* scratch, void* stream);
+/* Head backward (TransMIL.py:202-204): h3 [B,S,512], dlogits [B,n_classes] -> dcls [B,512] (gradient of h3[:,0]; the other
+ * rows of dh3 are zero), g_norm_w, g_norm_b [512], g_fc_w [n_classes,512], g_fc_b [n_classes]. */
+int tm_head_bwd(const tm_weights* w, const float* h3, const float* dlogits, int64_t B, int64_t S, float* dcls, float* g_norm_w,
+                float* g_norm_b, float* g_fc_w, float* g_fc_b, void* stream);
+/* Backward of the duplicate pad and the cls concat (TransMIL.py:177-186): dh0 [B,1+n+dup,512] -> dhf [B,n,512]. */
+int tm_dup_cls_bwd(const float* dh0, int64_t B, int64_t n, int64_t dup, float* dhf, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,233 @@
+"""Backward kernels (csrc/backward.cu) and their host orchestration (training.py) against the backward oracle, on the CPU.
+
+The build container has no GPU, so the kernel SOURCE is compiled with g++ against tests/cuda_emu/cuda_emu.h (grid / block /
+__syncthreads executed by fibers on the host) and driven through the same C ABI and the same Python orchestration the GPU
+path uses.  This checks indexing, strides, reductions and the order of contractions; the GPU suite
+(tests/test_zz_backward_gpu.py) checks the nvcc build of the same source on the device.
+"""
+import ctypes as C
+import importlib.util
+import os
+import subprocess
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from common import ROOT, build_model, make_input
+from oracle import transmil_backward as OB
+from oracle import transmil_oracle as O
+
+EMU_DIR = os.path.join(ROOT, "tests", "cuda_emu")
+EMU_LIB = os.path.join(EMU_DIR, "_build", "libtransmil_b200_emu.so")
+SRC = os.path.join(ROOT, "transmil-deepgraft_b200", "csrc", "backward.cu")
+
+
+@pytest.fixture(scope="module")
+def T():
+    import transmil_b200 as T
+    return T
+
+
+@pytest.fixture(scope="module")
+def K(T):
+    os.makedirs(os.path.dirname(EMU_LIB), exist_ok=True)
+    deps = [SRC, os.path.join(EMU_DIR, "cuda_emu.h"), os.path.join(ROOT, "include", "transmil_b200.h")]
+    if not os.path.isfile(EMU_LIB) or os.path.getmtime(EMU_LIB) < max(os.path.getmtime(d) for d in deps):
+        subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DTM_HOST_EMU", "-x", "c++", "-I", os.path.join(ROOT, "include"),
+                        "-I", EMU_DIR, SRC, "-o", EMU_LIB, "-lpthread"], check=True)
+    lib = C.CDLL(EMU_LIB)
+    lib.tm_last_error.restype = C.c_char_p
+    from transmil_b200 import training
+    training.bind(lib)
+    return training.Kernels(lib=lib, stream=None)
+
+
+def _close(a, b, rtol=2e-4, what=""):
+    a, b = a.double(), b.double()
+    err = (a - b).abs().max().item()
+    bound = rtol * max(b.abs().max().item(), 1e-6)
+    assert err <= bound, f"{what}: max abs err {err:.3e} > {bound:.3e} (ref max {b.abs().max().item():.3e})"
+
+
+def test_every_declared_backward_symbol_is_exported(K, T):
+    from transmil_b200 import training
+    for name in training.BWD_SIGNATURES:
+        assert hasattr(K.L, name)
+    hdr = open(os.path.join(ROOT, "include", "transmil_b200.h")).read()
+    for name in training.BWD_SIGNATURES:
+        assert name + "(" in hdr, f"{name} is not declared in include/transmil_b200.h"
+
+
+@pytest.mark.parametrize("tA,tB", [(False, False), (False, True), (True, False), (True, True)])
+def test_bgemm_every_orientation(K, tA, tB):
+    g = torch.Generator().manual_seed(3)
+    nb, M, N, Kd = 3, 70, 37, 45
+    A = torch.randn(nb, *((Kd, M) if tA else (M, Kd)), generator=g)
+    B = torch.randn(nb, *((N, Kd) if tB else (Kd, N)), generator=g)
+    Lt = torch.randn(nb, M, N, generator=g)
+    out = torch.empty(nb, M, N)
+    K.gemm(A, (1, M) if tA else (Kd, 1), B, (1, Kd) if tB else (N, 1), out, M, N, Kd, N, nb, (M * Kd, N * Kd, M * N), alpha=0.5, beta=-2.0, L=Lt)
+    ref = 0.5 * (A.transpose(1, 2) if tA else A).double() @ (B.transpose(1, 2) if tB else B).double() - 2.0 * Lt.double()
+    _close(out, ref, 1e-5, "bgemm")
+
+
+def test_bias_broadcast_through_ldl_zero(K):
+    g = torch.Generator().manual_seed(4)
+    x, W, b = torch.randn(50, 24, generator=g), torch.randn(12, 24, generator=g), torch.randn(12, generator=g)
+    from transmil_b200 import training
+    _close(training._linear_fwd(K, x, W, b, 50, 24, 12), F.linear(x.double(), W.double(), b.double()), 1e-5, "linear")
+
+
+def test_softmax_rows_and_backward(K):
+    g = torch.Generator().manual_seed(5)
+    X = torch.randn(7, 300, generator=g) * 3
+    P = X.clone()
+    K.check(K.L.tm_softmax_rows(P.data_ptr(), 7, 300, None))
+    _close(P, X.double().softmax(-1), 1e-5, "softmax")
+    dP = torch.randn(7, 300, generator=g)
+    ref = OB.softmax_backward(P.double(), dP.double())
+    K.check(K.L.tm_softmax_rows_bwd(P.data_ptr(), dP.data_ptr(), 7, 300, None))
+    _close(dP, ref, 1e-5, "softmax backward")
+
+
+def test_layernorm_backward_with_row_map(K):
+    g = torch.Generator().manual_seed(6)
+    B, S, P, Cc = 2, 37, 5, 512
+    x, gamma = torch.randn(B, S, Cc, generator=g), torch.rand(Cc, generator=g) + 0.5
+    dyp = torch.randn(B, S + P, Cc, generator=g)
+    add = torch.randn(B, S, Cc, generator=g)
+    dx, gg, gb = K.ln_bwd(x, gamma, dyp, B * S, Cc, S, S + P, P, add)
+    rdx, rgg, rgb = OB.layernorm_backward(x.double(), gamma.double(), dyp[:, P:].double())
+    _close(dx, rdx + add.double(), 1e-5, "LN dx")
+    _close(gg, rgg, 1e-4, "LN dgamma")
+    _close(gb, rgb, 1e-4, "LN dbeta")
+
+
+def test_layernorm_backward_many_rows_two_stage(K):
+    g = torch.Generator().manual_seed(7)
+    R, Cc = 700, 96
+    x, gamma, dy = torch.randn(R, Cc, generator=g), torch.rand(Cc, generator=g) + 0.5, torch.randn(R, Cc, generator=g)
+    dx, gg, gb = K.ln_bwd(x, gamma, dy, R, Cc, R, R, 0, None)
+    rdx, rgg, rgb = OB.layernorm_backward(x.double(), gamma.double(), dy.double())
+    _close(dx, rdx, 1e-5, "LN dx")
+    _close(gg, rgg, 1e-4, "LN dgamma")
+    _close(gb, rgb, 1e-4, "LN dbeta")
+    _close(K.colsum(dy, R, Cc, Cc), dy.double().sum(0), 1e-4, "colsum")
+
+
+def test_gelu_forward_backward(K):
+    g = torch.Generator().manual_seed(8)
+    z, dy = torch.randn(1000, generator=g) * 2, torch.randn(1000, generator=g)
+    a, dz = torch.empty_like(z), torch.empty_like(z)
+    K.check(K.L.tm_gelu_fwd(z.data_ptr(), a.data_ptr(), 1000, None))
+    K.check(K.L.tm_gelu_bwd(z.data_ptr(), dy.data_ptr(), dz.data_ptr(), 1000, None))
+    _close(a, F.gelu(z.double()), 1e-5, "gelu")
+    _close(dz, OB.gelu_backward(z.double(), dy.double()), 1e-5, "gelu backward")
+
+
+def test_pinv_backward(K):
+    """dA of the 6-iteration pinv with the global init scalar; compared after the softmax backward, which annihilates the
+    per-row constants that ties among the (all ~1) row sums distribute differently in fp32 and fp64."""
+    g = torch.Generator().manual_seed(9)
+    nb = 2
+    A = (torch.randn(1, nb, 256, 256, generator=g) * 0.5).softmax(-1)
+    dZ = torch.randn(1, nb, 256, 256, generator=g)
+    ref = OB.softmax_backward(A.double(), OB.pinv_backward(A.double(), dZ.double()))
+    dA = torch.empty(nb, 256, 256)
+    sc = torch.empty(int(K.L.tm_pinv_bwd_scratch_floats(nb)))
+    dZw = dZ.clone()    # clobbered by the call
+    K.check(K.L.tm_pinv_bwd(A.data_ptr(), dZw.data_ptr(), nb, dA.data_ptr(), sc.data_ptr(), None))
+    K.check(K.L.tm_softmax_rows_bwd(A.data_ptr(), dA.data_ptr(), nb * 256, 256, None))
+    _close(dA.view(1, nb, 256, 256), ref, 2e-3, "pinv backward")
+
+
+def _weights(T, sd, kind, D, nc):
+    w = T.capi.Weights()
+    w.fc1_kind, w.in_features, w.n_classes = kind, D, nc
+    for f, k in (("ppeg_w7", "pos_layer.proj.weight"), ("ppeg_b7", "pos_layer.proj.bias"), ("ppeg_w5", "pos_layer.proj1.weight"),
+                 ("ppeg_b5", "pos_layer.proj1.bias"), ("ppeg_w3", "pos_layer.proj2.weight"), ("ppeg_b3", "pos_layer.proj2.bias"),
+                 ("norm_w", "norm.weight"), ("norm_b", "norm.bias"), ("fc_w", "_fc.weight"), ("fc_b", "_fc.bias")):
+        setattr(w, f, sd[k].data_ptr())
+    return w
+
+
+def test_ppeg_backward(K, T):
+    m = build_model(2, 512)
+    sd = {k: v.detach().contiguous() for k, v in m.state_dict().items()}
+    g = torch.Generator().manual_seed(10)
+    B, G = 2, 9
+    h, dy = torch.randn(B, G * G + 1, 512, generator=g), torch.randn(B, G * G + 1, 512, generator=g)
+    rdh, rg = OB.ppeg_backward({k: v.double() for k, v in sd.items()}, h.double(), G, dy.double())
+    w = _weights(T, sd, 0, 512, 2)
+    dh = torch.empty_like(h)
+    gp = {k: torch.empty_like(sd["pos_layer." + k]) for k in ("proj.weight", "proj.bias", "proj1.weight", "proj1.bias", "proj2.weight", "proj2.bias")}
+    sc = torch.empty(int(K.L.tm_ppeg_bwd_scratch_floats(B, G)))
+    K.check(K.L.tm_ppeg_bwd(C.byref(w), h.data_ptr(), dy.data_ptr(), B, G, dh.data_ptr(), gp["proj.weight"].data_ptr(), gp["proj.bias"].data_ptr(),
+                            gp["proj1.weight"].data_ptr(), gp["proj1.bias"].data_ptr(), gp["proj2.weight"].data_ptr(), gp["proj2.bias"].data_ptr(),
+                            sc.data_ptr(), None))
+    _close(dh, rdh, 1e-5, "ppeg dh")
+    for k, v in gp.items():
+        _close(v, rg["pos_layer." + k], 1e-4, "ppeg " + k)
+
+
+def test_conv33_backward(K):
+    g = torch.Generator().manual_seed(11)
+    B, Sp = 2, 256
+    dO, v, w = torch.randn(B, 8, Sp, 64, generator=g), torch.randn(B, 8, Sp, 64, generator=g), torch.randn(8, 1, 33, 1, generator=g)
+    vv = v.double().requires_grad_(True)
+    ww = w.double().requires_grad_(True)
+    F.conv2d(vv, ww, None, padding=(16, 0), groups=8).backward(dO.double())
+    dv, gw = torch.empty_like(v), torch.empty_like(w)
+    K.check(K.L.tm_conv33_bwd(dO.data_ptr(), v.data_ptr(), w.data_ptr(), B, Sp, dv.data_ptr(), gw.data_ptr(), None))
+    _close(dv, vv.grad, 1e-5, "conv dv")
+    _close(gw, ww.grad, 1e-4, "conv dw")
+
+
+def _saved_from_oracle(sd, x):
+    """What training.forward_keep keeps, taken from the forward oracle (fp32)."""
+    logits, st = O.forward(sd, x, return_stages=True)
+    p = O.plan(x.shape[1])
+    saved = {"plan": p, "h0": st["h0"], "h1": st["h1"], "h2": st["h2"], "h3": st["h3"]}
+    for name in ("layer1", "layer2"):
+        s = st[name]
+        sv = {k: s[k].contiguous() for k in ("q", "k", "v", "q_lm", "k_lm", "attn2", "Z", "W3", "merged")}
+        sv["xn"] = F.pad(s["xn"], (0, 0, p["P"], 0)).contiguous()
+        sv["M"] = (s["Z"] @ s["W3"]).contiguous()
+        saved[name] = sv
+    return logits, {k: (v.contiguous() if torch.is_tensor(v) else v) for k, v in saved.items()}
+
+
+@pytest.mark.parametrize("D,nc,n,B", [(96, 3, 300, 2), (2048, 2, 130, 1)])
+def test_whole_backward_against_oracle(K, T, D, nc, n, B):
+    """Every parameter gradient of the path: kernels + orchestration vs the float64 backward oracle (itself pinned to autograd
+    of the forward oracle by tests/test_oracle_backward.py)."""
+    from transmil_b200 import training
+    m = build_model(nc, D)
+    sd = {k: v.detach().contiguous() for k, v in m.state_dict().items()}
+    x = make_input("randn", B, n, D, 77)
+    dlogits = torch.randn(B, nc, generator=torch.Generator().manual_seed(12))
+    ref, _ = OB.backward(sd, x, dlogits.double())
+    _, saved = _saved_from_oracle(sd, x)
+    w = _weights(T, sd, m._fc1_kind, D, nc)
+    g = training.backward(K, sd, w, m._fc1_kind, x.contiguous(), saved, dlogits)
+    assert set(g) == set(ref) == set(sd)
+    for k in sorted(ref):
+        _close(g[k].reshape(ref[k].shape), ref[k], 2e-3, k)
+
+
+def test_dropout_mask_is_the_same_in_forward_and_backward(K):
+    g = torch.Generator().manual_seed(13)
+    B, S, P, Cc, p, seed = 2, 50, 6, 512, 0.7, 123456789
+    h_in, t = torch.randn(B, S, Cc, generator=g), torch.randn(B, S, Cc, generator=g)
+    y = (h_in + t).contiguous()
+    K.check(K.L.tm_dropout_resid_fwd(y.data_ptr(), h_in.data_ptr(), B * S * Cc, seed, p, None))
+    mask = ((y - h_in).abs() > 0).float()
+    keep = mask.mean().item()
+    assert abs(keep - (1 - p)) < 0.01
+    _close(y, h_in + mask * t / (1 - p), 1e-5, "dropout forward")
+    dy = torch.randn(B, S, Cc, generator=g)
+    out = torch.empty(B, S + P, Cc)
+    K.check(K.L.tm_pad_front_bwd(dy.data_ptr(), B, S, P, Cc, seed, p, out.data_ptr(), None))
+    assert out[:, :P].abs().max().item() == 0.0
+    _close(out[:, P:], dy * mask / (1 - p), 1e-6, "dropout backward")

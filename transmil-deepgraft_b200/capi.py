@@ -101,6 +101,33 @@ SIGNATURES = {
     "tm_gemm_nt": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _u32, _fp]),
 }
 
+# backward entry points (csrc/backward.cu); transmil-deepgraft_b200/training.py is their only caller
+_f32, _u64 = C.c_float, C.c_uint64
+BWD_SIGNATURES = {
+    "tm_bgemm": (C.c_int, [_fp, _fp, _fp, _fp] + [_i64] * 14 + [_f32, _f32, _fp]),
+    "tm_softmax_rows": (C.c_int, [_fp, _i64, _i64, _fp]),
+    "tm_softmax_rows_bwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp]),
+    "tm_ln_rows_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp]),
+    "tm_ln_bwd_scratch_floats": (_i64, [_i64, _i64]),
+    "tm_ln_rows_bwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _i64, _i64, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "tm_colsum_scratch_floats": (_i64, [_i64, _i64]),
+    "tm_colsum": (C.c_int, [_fp, _i64, _i64, _i64, _fp, _fp, _fp]),
+    "tm_gelu_fwd": (C.c_int, [_fp, _fp, _i64, _fp]),
+    "tm_gelu_bwd": (C.c_int, [_fp, _fp, _fp, _i64, _fp]),
+    "tm_dropout_resid_fwd": (C.c_int, [_fp, _fp, _i64, _u64, _f32, _fp]),
+    "tm_pad_front_bwd": (C.c_int, [_fp, _i64, _i64, _i64, _i64, _u64, _f32, _fp, _fp]),
+    "tm_split_heads": (C.c_int, [_fp, _i64, _i64, _fp, _fp]),
+    "tm_qkv_grad_merge": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _i64, _fp, _fp]),
+    "tm_conv33_bwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _fp]),
+    "tm_pinv_bwd_scratch_floats": (_i64, [_i64]),
+    "tm_pinv_bwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp, _fp]),
+    "tm_ppeg_bwd_scratch_floats": (_i64, [_i64, _i64]),
+    "tm_ppeg_bwd": (C.c_int, [_PW, _fp, _fp, _i64, _i64] + [_fp] * 9),
+    "tm_head_bwd": (C.c_int, [_PW, _fp, _fp, _i64, _i64, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "tm_dup_cls_bwd": (C.c_int, [_fp, _i64, _i64, _i64, _fp, _fp]),
+}
+SIGNATURES.update(BWD_SIGNATURES)
+
 _lib = None
 
 
