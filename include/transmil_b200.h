@@ -385,6 +385,26 @@ int tm_head_bwd(const tm_weights* w, const float* h3, const float* dlogits, int6
 /* Backward of the duplicate pad and the cls concat (TransMIL.py:177-186): dh0 [B,1+n+dup,512] -> dhf [B,n,512]. */
 int tm_dup_cls_bwd(const float* dh0, int64_t B, int64_t n, int64_t dup, float* dhf, void* stream);
 
+/* ---- optimizer step ----------------------------------------------------------------------------------
+ * One launch over the whole parameter set (29 tensors, 4.77 M floats) instead of one small kernel per tensor and operation. */
+#define TM_OPT_MAX_TENSORS 48
+typedef struct tm_opt_tensor {
+  float* p;            /* parameter (fast weights) */
+  const float* g;      /* gradient (unused by tm_lookahead_sync) */
+  float* m;            /* exp_avg (tm_radam_step) / slow buffer (tm_lookahead_sync) */
+  float* v;            /* exp_avg_sq (unused by tm_lookahead_sync) */
+  int64_t n;           /* elements */
+  float weight_decay;  /* L2 coefficient of this tensor's param group (0 for biases and 1-D tensors: add_weight_decay,
+                          code/MyOptimizer/optim_factory.py:25-37) */
+  float reserved;
+} tm_opt_tensor;
+/* torch.optim.RAdam step, the optimizer the reference's factory builds for opt 'radam' (code/MyOptimizer/optim_factory.py:78-80;
+ * DeepGraft/TransMIL_feat_norm_rest.yaml:49-55: lr 1e-4, wd 0.01).  `tensors` is a HOST array; step counts from 1. */
+int tm_radam_step(const tm_opt_tensor* tensors, int64_t count, int64_t step, float lr, float beta1, float beta2, float eps, void* stream);
+/* Lookahead wrapper's slow-weight update ('lookahead_radam'; code/MyOptimizer/lookahead.py:28-41):
+ * slow += alpha (fast - slow); fast = slow, with tensors[i].p = fast and tensors[i].m = slow. */
+int tm_lookahead_sync(const tm_opt_tensor* tensors, int64_t count, float alpha, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,9 +67,11 @@ def test_forward_argument_contract_and_no_cpu_fallback():
             m(torch.zeros(1, 10, 512))
         with pytest.raises(T.capi.TransmilError):
             m(data=torch.zeros(10, 512))
-    m.train()
-    with pytest.raises(NotImplementedError):
+    m.train()   # training path (library forward + backward behind autograd): CUDA only as well
+    with pytest.raises(T.capi.TransmilError, match="no CPU path"):
         m(torch.zeros(1, 10, 512))
+    with pytest.raises(NotImplementedError):
+        m(torch.zeros(1, 10, 512), return_attn=True)
 
 
 def test_load_reference_checkpoint_keys_roundtrip():

@@ -126,6 +126,17 @@ BWD_SIGNATURES = {
     "tm_head_bwd": (C.c_int, [_PW, _fp, _fp, _i64, _i64, _fp, _fp, _fp, _fp, _fp, _fp]),
     "tm_dup_cls_bwd": (C.c_int, [_fp, _i64, _i64, _i64, _fp, _fp]),
 }
+
+
+class OptTensor(C.Structure):
+    _fields_ = [("p", _fp), ("g", _fp), ("m", _fp), ("v", _fp), ("n", _i64), ("weight_decay", C.c_float), ("reserved", C.c_float)]
+
+
+TM_OPT_MAX_TENSORS = 48
+BWD_SIGNATURES.update({
+    "tm_radam_step": (C.c_int, [C.POINTER(OptTensor), _i64, _i64, _f32, _f32, _f32, _f32, _fp]),
+    "tm_lookahead_sync": (C.c_int, [C.POINTER(OptTensor), _i64, _f32, _fp]),
+})
 SIGNATURES.update(BWD_SIGNATURES)
 
 _lib = None

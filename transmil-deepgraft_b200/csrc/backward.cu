@@ -531,6 +531,47 @@ __global__ void __launch_bounds__(BT) dup_cls_bwd_kernel(const float* dh0, i64 B
   dhf[i] = o;
 }
 
+// ---- optimizer step over the whole parameter set: torch.optim.RAdam as selected by the reference's factory
+// (code/MyOptimizer/optim_factory.py:78-80) + the Lookahead wrapper (code/MyOptimizer/lookahead.py:28-41), one launch each --------
+struct OptBatch { tm_opt_tensor t[TM_OPT_MAX_TENSORS]; };
+__global__ void __launch_bounds__(BT) radam_kernel(const OptBatch b, float lr, float beta1, float beta2, float eps, float bc1,
+                                                   float bc2_sqrt, float rect, int rectified) {
+  const tm_opt_tensor t = b.t[blockIdx.y];
+  for (i64 i = (i64)blockIdx.x * BT + threadIdx.x; i < t.n; i += (i64)gridDim.x * BT) {
+    float p = t.p[i];
+    const float g = t.weight_decay != 0.f ? fmaf(t.weight_decay, p, t.g[i]) : t.g[i];
+    float m = t.m[i], v = t.v[i];
+    m = m + (1.0f - beta1) * (g - m);
+    v = beta2 * v + (1.0f - beta2) * g * g;
+    const float mh = m / bc1;
+    if (rectified) p -= mh * lr * (bc2_sqrt / (sqrtf(v) + eps)) * rect;
+    else p -= mh * lr;
+    t.p[i] = p; t.m[i] = m; t.v[i] = v;
+  }
+}
+// slow += alpha (fast - slow); fast = slow   (t.p = fast weights, t.m = slow buffer)
+__global__ void __launch_bounds__(BT) lookahead_kernel(const OptBatch b, float alpha) {
+  const tm_opt_tensor t = b.t[blockIdx.y];
+  for (i64 i = (i64)blockIdx.x * BT + threadIdx.x; i < t.n; i += (i64)gridDim.x * BT) {
+    const float s = t.m[i] + alpha * (t.p[i] - t.m[i]);
+    t.m[i] = s;
+    t.p[i] = s;
+  }
+}
+static int opt_batch(const tm_opt_tensor* ts, int64_t count, OptBatch* b, unsigned* gx) {
+  TM_CHECK_ARG(ts && count > 0 && count <= TM_OPT_MAX_TENSORS, TM_ERR_BAD_ARGUMENT, "optimizer step: 1..%d tensors per call (got %lld)",
+               TM_OPT_MAX_TENSORS, (long long)count);
+  i64 nmax = 0;
+  for (int64_t i = 0; i < count; ++i) {
+    TM_CHECK_ARG(ts[i].p && ts[i].m && ts[i].n > 0, TM_ERR_BAD_ARGUMENT, "optimizer step: tensor %lld has a NULL pointer or no elements", (long long)i);
+    b->t[i] = ts[i];
+    if (ts[i].n > nmax) nmax = ts[i].n;
+  }
+  i64 g = ceil_div(nmax, (i64)BT * 4);
+  *gx = (unsigned)(g < 1 ? 1 : (g > 296 ? 296 : g));
+  return TM_OK;
+}
+
 // one product of the pinv chain: C = alpha * op(A) op(B) + beta * L + diag * I on nb 256x256 matrices
 static int mm256(const float* A, bool tA, const float* B, bool tB, float* C, float alpha, float beta, const float* L, float diag,
                  int nb, cudaStream_t st) {
@@ -771,6 +812,33 @@ int tm_head_bwd(const tm_weights* w, const float* h3, const float* dlogits, int6
 int tm_dup_cls_bwd(const float* dh0, int64_t B, int64_t n, int64_t dup, float* dhf, void* stream) {
   TM_CHECK_ARG(dh0 && dhf && B > 0 && n > 0 && dup >= 0 && dup <= n, TM_ERR_BAD_ARGUMENT, "tm_dup_cls_bwd: bad argument");
   BW_LAUNCH(dup_cls_bwd_kernel, grid1d(B * n * TM_DIM), dim3(BT), (cudaStream_t)stream, dh0, (i64)B, (i64)n, (i64)dup, dhf);
+  return TM_OK;
+}
+
+/* torch.optim.RAdam step (the optimizer code/MyOptimizer/optim_factory.py:78-80 builds for opt 'radam'; L2 weight decay folded
+ * into the gradient per tensor) on up to TM_OPT_MAX_TENSORS tensors in one launch.  `step` is the 1-based step count. */
+int tm_radam_step(const tm_opt_tensor* tensors, int64_t count, int64_t step, float lr, float beta1, float beta2, float eps, void* stream) {
+  OptBatch b;
+  unsigned gx = 1;
+  TM_PROPAGATE(opt_batch(tensors, count, &b, &gx));
+  for (int64_t i = 0; i < count; ++i) TM_CHECK_ARG(tensors[i].g && tensors[i].v, TM_ERR_BAD_ARGUMENT, "tm_radam_step: NULL g / v");
+  TM_CHECK_ARG(step >= 1, TM_ERR_BAD_ARGUMENT, "tm_radam_step: step counts from 1");
+  const double b1t = pow((double)beta1, (double)step), b2t = pow((double)beta2, (double)step);
+  const double bc1 = 1.0 - b1t, bc2 = 1.0 - b2t;
+  const double rho_inf = 2.0 / (1.0 - (double)beta2) - 1.0;
+  const double rho_t = rho_inf - 2.0 * (double)step * b2t / bc2;
+  const int rectified = rho_t > 5.0;
+  const double rect = rectified ? sqrt((rho_t - 4.0) * (rho_t - 2.0) * rho_inf / ((rho_inf - 4.0) * (rho_inf - 2.0) * rho_t)) : 0.0;
+  BW_LAUNCH(radam_kernel, dim3(gx, (unsigned)count), dim3(BT), (cudaStream_t)stream, b, lr, beta1, beta2, eps, (float)bc1, (float)sqrt(bc2),
+            (float)rect, rectified);
+  return TM_OK;
+}
+/* Lookahead slow-weight update (code/MyOptimizer/lookahead.py:28-41): tensors[i].p = fast weights, tensors[i].m = slow buffer. */
+int tm_lookahead_sync(const tm_opt_tensor* tensors, int64_t count, float alpha, void* stream) {
+  OptBatch b;
+  unsigned gx = 1;
+  TM_PROPAGATE(opt_batch(tensors, count, &b, &gx));
+  BW_LAUNCH(lookahead_kernel, dim3(gx, (unsigned)count), dim3(BT), (cudaStream_t)stream, b, alpha);
   return TM_OK;
 }
 

@@ -113,6 +113,7 @@ class TransMIL(nn.Module):
         self.norm = norm_layer(out_features)
         self._fc = nn.Linear(out_features, self.n_classes)
         self.flags = 0          # capi.TM_FLAG_* bits OR-ed into every call
+        self.keep_graph = False  # True: differentiate the eval-mode forward too (GradCAM-style consumers); default eval = fast path
         self._ws = None         # cached device workspace (uint8 tensor)
         self._stage_key = None
 
@@ -169,9 +170,12 @@ class TransMIL(nn.Module):
             x = kwargs.get("data")          # upstream TransMIL: forward(**kwargs) with kwargs['data']
         if x is None:
             raise TypeError("forward() needs the bag tensor (positional `x` or keyword `data`)")
-        if self.training and torch.is_grad_enabled():
-            raise NotImplementedError("libtransmil_b200: the backward kernels are not built yet; "
-                                      "call model.eval() / torch.no_grad() (inference path)")
+        if torch.is_grad_enabled() and (self.training or self.keep_graph):
+            # training_step (code/models/model_interface.py:333-383): forward with every stage kept + the library's backward
+            # (csrc/backward.cu) behind a torch.autograd.Function; train mode applies the to_out Dropout(0.7)
+            if return_attn:
+                raise NotImplementedError("libtransmil_b200: return_attn=True is an inference feature (eval() / no_grad())")
+            return self._forward_train(x)
         # TransMIL.py:170-174
         if x.dim() > 3:
             x = x.squeeze(0)
@@ -211,6 +215,20 @@ class TransMIL(nn.Module):
             self._ws = None   # the lazy view owns this workspace now
             return logits, (attn, int(plan.padding))
         return logits
+
+    def _forward_train(self, x):
+        from . import training
+        if x.dim() > 3:          # TransMIL.py:170-174
+            x = x.squeeze(0)
+        elif x.dim() == 2:
+            x = x.unsqueeze(0)
+        if x.dim() != 3 or x.shape[-1] != self.in_features:
+            raise ValueError(f"expected a bag tensor [B, n, {self.in_features}], got {tuple(x.shape)}")
+        device = self.cls_token.device
+        if device.type != "cuda":
+            raise capi.TransmilError("TransMIL must be on a CUDA device (model.cuda()); there is no CPU path")
+        xd = x.detach().to(device=device, dtype=torch.float32, non_blocking=True).contiguous()   # x.float(), TransMIL.py:174
+        return training.TransMILFunction.apply(self, xd, *self.parameters())
 
     def stage(self, name):
         """Per-stage buffer of the last forward (needs flags |= TM_FLAG_KEEP_STAGES); parity tests only."""
