@@ -69,3 +69,25 @@ def load_reference_checkpoint(model, checkpoint, strict=True, map_location="cpu"
         own = set(model.state_dict().keys())
         renamed = {k: v for k, v in renamed.items() if k in own}
     return model.load_state_dict(renamed, strict=strict)
+
+
+def step(model, input):
+    """ModelInterface.step (code/models/model_interface.py:319-331): logits, Y_prob, Y_hat of one batch of bags."""
+    import torch
+    logits = model(input.float().contiguous())
+    return logits, torch.softmax(logits, dim=1), torch.argmax(logits, dim=1)
+
+
+def training_step(model, batch, loss_fn=None):
+    """ModelInterface.training_step (code/models/model_interface.py:333-383) without the Lightning bookkeeping: `batch` is
+    (input [B,n,D], label [B], anything), the loss is taken against the one-hot label (:346-347; default CrossEntropyLoss with
+    probability targets, the reference's `create_loss('CrossEntropyLoss')`).  Returns the loss (1-element tensor, :348-349);
+    `.backward()` on it runs the library's backward kernels (training.TransMILFunction)."""
+    import torch
+    input, label = batch[0], batch[1]
+    logits, Y_prob, Y_hat = step(model, input)
+    one_hot = torch.nn.functional.one_hot(label.to(logits.device), num_classes=model.n_classes).float()
+    loss = (loss_fn or torch.nn.functional.cross_entropy)(logits, one_hot)
+    if loss.ndim == 0:
+        loss = loss.unsqueeze(0)
+    return loss, Y_prob, Y_hat
