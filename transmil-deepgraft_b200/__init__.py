@@ -11,6 +11,6 @@ Layout (only what the path needs):
 """
 from . import capi
 from .ingest import StreamedInference
-from .transmil import LazyAttention, NystromAttention, PPEG, TransLayer, TransMIL, y_prob_y_hat
+from .transmil import MDMIL, LazyAttention, NystromAttention, PPEG, TransLayer, TransMIL, y_prob_y_hat
 
-__all__ = ["capi", "TransMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]
+__all__ = ["capi", "TransMIL", "MDMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]

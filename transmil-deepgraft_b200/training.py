@@ -302,4 +302,6 @@ class TransMILFunction(torch.autograd.Function):
             g = backward(K, p, model._weights(), model._fc1_kind, x, ctx.saved, dlogits, ctx.seeds,
                          TO_OUT_DROPOUT if ctx.training else 0.0)
         ctx.saved = None
+        if model.HEAD != "_fc":   # sibling models name the classifier differently (MDMIL._fc2)
+            g[model.HEAD + ".weight"], g[model.HEAD + ".bias"] = g.pop("_fc.weight"), g.pop("_fc.bias")
         return (None, None) + tuple(g[n].reshape(p[n].shape) for n in ctx.names)

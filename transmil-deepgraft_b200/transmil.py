@@ -18,7 +18,7 @@ import torch.nn as nn
 
 from . import capi
 
-__all__ = ["TransMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention"]
+__all__ = ["TransMIL", "MDMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention"]
 
 
 class NystromAttention(nn.Module):
@@ -81,6 +81,8 @@ def _fc1_1024_else_form():
 
 
 class TransMIL(nn.Module):
+    HEAD = "_fc"   # attribute / state_dict name of the classifier Linear (TransMIL.py:155); MDMIL calls it _fc2
+
     def __init__(self, n_classes, in_features, out_features=512):
         super().__init__()
         if out_features != 512:
@@ -155,7 +157,8 @@ class TransMIL(nn.Module):
         w.ppeg_w5, w.ppeg_b5 = self._ptr(p.proj1.weight, (512, 1, 5, 5)), self._ptr(p.proj1.bias)
         w.ppeg_w3, w.ppeg_b3 = self._ptr(p.proj2.weight, (512, 1, 3, 3)), self._ptr(p.proj2.bias)
         w.norm_w, w.norm_b = self._ptr(self.norm.weight, (512,)), self._ptr(self.norm.bias, (512,))
-        w.fc_w, w.fc_b = self._ptr(self._fc.weight, (self.n_classes, 512)), self._ptr(self._fc.bias)
+        head = getattr(self, self.HEAD)
+        w.fc_w, w.fc_b = self._ptr(head.weight, (self.n_classes, 512)), self._ptr(head.bias)
         return w
 
     def _workspace(self, nbytes, device):
@@ -325,6 +328,43 @@ class LazyAttention:
         if nbytes > self.MAX_DENSE_BYTES:
             raise MemoryError(f"dense attention would need {nbytes / 2**30:.1f} GiB; index rows instead")
         return self.rows(range(self.Sp))
+
+
+class MDMIL(TransMIL):
+    """Sibling model of the same path: /root/reference/code/models/MDMIL.py:60-113.
+
+    `MDMIL(n_classes)` is TransMIL's path with a fixed 1024-d single-Linear stem (MDMIL.py:63-66), the classifier named
+    `_fc2` (MDMIL.py:74) and a forward that always returns `(logits, attn2)` (MDMIL.py:77,113) -- layer 2's
+    `attn1 @ attn2_inv @ attn3` [B,8,Sp,Sp], which the reference materialises densely and this module returns as lazy
+    rows (LazyAttention).  Sub-modules are created in the reference's order (pos_layer, _fc1, cls_token, layer1, layer2,
+    norm, _fc2) so the seeded init and the state_dict keys are identical.  Same kernels, no new arithmetic.
+    In train mode (autograd on) the forward returns `(logits, None)`: the dense attention has no gradient consumer in the
+    reference and the training forward does not keep it."""
+    HEAD = "_fc2"
+
+    def __init__(self, n_classes):
+        nn.Module.__init__(self)
+        in_features, out_features = 1024, 512
+        self.pos_layer = PPEG(dim=out_features)
+        self._fc1 = nn.Sequential(nn.Linear(in_features, out_features), nn.GELU())
+        self._fc1_kind = capi.TM_FC1_SINGLE
+        self.cls_token = nn.Parameter(torch.randn(1, 1, out_features))
+        self.n_classes = n_classes
+        self.in_features = in_features
+        self.layer1 = TransLayer(dim=out_features)
+        self.layer2 = TransLayer(dim=out_features)
+        self.norm = nn.LayerNorm(out_features)
+        self._fc2 = nn.Linear(out_features, self.n_classes)
+        self.flags = 0
+        self.keep_graph = False
+        self._ws = None
+        self._stage_key = None
+
+    def forward(self, x):
+        if torch.is_grad_enabled() and (self.training or self.keep_graph):
+            return TransMIL.forward(self, x), None
+        logits, (attn, _padding) = TransMIL.forward(self, x, return_attn=True)
+        return logits, attn
 
 
 def y_prob_y_hat(logits):
