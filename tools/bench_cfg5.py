@@ -1,0 +1,92 @@
+"""BASELINE config 5: 256 synthetic bags with lengths drawn log-uniform in [1 000, 100 000] (seed 5), n_classes = 6,
+inference through the public API: host bags (pinned) -> `BagParallelInference` (longest-first placement of whole bags on ranks,
+SURVEY 8e/E1) -> `StreamedInference` on each rank (H2D of the next bag under the current forward) -> one logits gather.
+Exercises the padding to a landmark multiple and the square reshape of PPEG on every length.  One JSON line on rank 0.
+
+    python tools/bench_cfg5.py [--features 2048] [--bags 256]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 tools/bench_cfg5.py
+"""
+import argparse
+import json
+import math
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import transmil_b200 as T  # noqa: E402
+from transmil_b200 import bagdp  # noqa: E402
+
+
+def config5_lengths(n_bags, seed):
+    rng = np.random.default_rng(seed)
+    return [int(v) for v in np.exp(rng.uniform(math.log(1000), math.log(100000), n_bags))]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--bags", type=int, default=256)
+    ap.add_argument("--features", type=int, default=2048)
+    ap.add_argument("--classes", type=int, default=6)
+    ap.add_argument("--seed", type=int, default=5)
+    ap.add_argument("--f16", action="store_true", help="half-precision feature bags (read directly by fc1)")
+    a = ap.parse_args()
+    world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.manual_seed(2021)
+    model = T.TransMIL(n_classes=a.classes, in_features=a.features).eval().cuda()
+    lengths = config5_lengths(a.bags, a.seed)
+    rows = max(lengths) + 4096
+    pool = torch.rand(rows, a.features, generator=torch.Generator().manual_seed(1))
+    pool = (pool.half() if a.f16 else pool).pin_memory()
+
+    def load(i):                                   # bag i = a window of the pinned pool (distinct offsets, no extra host memory)
+        off = (i * 7919) % (rows - lengths[i] + 1)
+        return pool[off:off + lengths[i]]
+
+    run = bagdp.BagParallelInference(model)
+    warm = sorted(range(len(lengths)), key=lambda i: -lengths[i])[:2] + [0, 1]
+    for i in warm:                                 # warm-up: largest workspace first, library initialisation
+        with torch.no_grad():
+            model(load(i).cuda().unsqueeze(0))
+    torch.cuda.synchronize()
+    times = []
+    for _ in range(2):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        logits = run(lengths, load)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        times.append(float(dt))
+    parts = bagdp.assign_bags(lengths, world, a.features)
+    load_r = [sum(bagdp.bag_cost(lengths[i], a.features) for i in p) for p in parts]
+    if rank == 0:
+        t = min(times)
+        assert torch.isfinite(logits).all() and logits.shape == (a.bags, a.classes)
+        print(json.dumps({
+            "tool": "config5_variable_bags", "n_gpus": world, "bags": a.bags, "features": a.features, "classes": a.classes,
+            "dtype_in": "f16" if a.f16 else "f32", "lengths": {"min": min(lengths), "max": max(lengths), "sum": sum(lengths)},
+            "seconds": t, "slides_per_s": a.bags / t, "tokens_per_s": sum(lengths) / t,
+            "h2d_bytes": sum(lengths) * a.features * (2 if a.f16 else 4),
+            "placement": {"policy": "longest-first on least loaded rank", "max_over_ideal": max(load_r) / (sum(load_r) / world)},
+            "timing": "host clock around the whole job incl. H2D of every bag and the logits gather, barrier + synchronize on both sides, max over ranks, best of 2 passes",
+            "device": torch.cuda.get_device_name(0)}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -7,11 +7,13 @@ Layout (only what the path needs):
   plugin.py     the reference's "model name -> models/<name>.py class" loader
   sharded.py    token-sharded forward of one giant bag over torch.distributed (NCCL)
   h5bag.py      reader of the reference's HDF5 feature-bag files (features / coords) into pinned host memory, no h5py
+  bagdp.py      whole bags placed on ranks longest-first (variable-length bags), one logits gather
   ingest.py     slide-at-a-time inference loop with the next bag's H2D copy hidden behind the current forward
   build.py      nvcc build of the shared library
 """
-from . import capi, h5bag
+from . import bagdp, capi, h5bag
+from .bagdp import BagParallelInference
 from .ingest import StreamedInference
 from .transmil import MDMIL, LazyAttention, NystromAttention, PPEG, TransLayer, TransMIL, y_prob_y_hat
 
-__all__ = ["capi", "h5bag", "TransMIL", "MDMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]
+__all__ = ["capi", "h5bag", "bagdp", "BagParallelInference", "TransMIL", "MDMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]
