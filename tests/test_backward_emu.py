@@ -216,6 +216,21 @@ def test_whole_backward_against_oracle(K, T, D, nc, n, B):
         _close(g[k].reshape(ref[k].shape), ref[k], 2e-3, k)
 
 
+@pytest.mark.parametrize("D,n,B", [(768, 90, 2), (2048, 33, 1), (1024, 50, 1)])
+def test_stem_backward_of_every_fc1_form(K, T, D, n, B):
+    """fc1 backward alone for the 768-d (two LayerNorms), 2048-d and single-Linear stems vs the float64 oracle."""
+    from transmil_b200 import training
+    m = build_model(2, D)
+    sd = {k: v.detach().contiguous() for k, v in m.state_dict().items()}
+    x = make_input("randn", B, n, D, 78)
+    dh = torch.randn(B, n, 512, generator=torch.Generator().manual_seed(14))
+    _, ref = OB.fc1_backward({k: v.double() for k, v in sd.items()}, x.double(), dh.double())
+    g = training.fc1_backward(K, sd, m._fc1_kind, x.contiguous(), dh.clone())
+    assert set(g) == set(ref) == {k for k in sd if k.startswith("_fc1.")}
+    for k in sorted(ref):
+        _close(g[k].reshape(ref[k].shape), ref[k], 1e-3, k)
+
+
 def test_dropout_mask_is_the_same_in_forward_and_backward(K):
     g = torch.Generator().manual_seed(13)
     B, S, P, Cc, p, seed = 2, 50, 6, 512, 0.7, 123456789

@@ -173,7 +173,27 @@ def fc1_backward(K, p, kind, x, dhf):
         K.check(K.L.tm_gelu_bwd(z0.data_ptr(), da0.data_ptr(), z0.data_ptr(), R * F0, K.st))            # z0 <- dz0
         _linear_wgrad(K, z0, xf, g, "_fc1.0", R, D, F0)
         return g
-    raise NotImplementedError("libtransmil_b200: the backward of the 768-d stem (TransMIL.py:122-126) is not built")
+    if kind == capi.TM_FC1_768:
+        # Linear GELU [Dropout] LN(768) Linear(768,512) GELU [Dropout] LN(512) (TransMIL.py:123-126); the eval-mode graph
+        # (keep_graph): the two Dropout(0.6) are identities; train mode of this stem is refused by the forward
+        F0 = p["_fc1.0.weight"].shape[0]
+        z0 = _linear_fwd(K, xf, p["_fc1.0.weight"], p["_fc1.0.bias"], R, D, F0)
+        a0 = torch.empty_like(z0)
+        K.check(K.L.tm_gelu_fwd(z0.data_ptr(), a0.data_ptr(), R * F0, K.st))
+        a1 = torch.empty_like(z0)
+        K.check(K.L.tm_ln_rows_fwd(a0.data_ptr(), p["_fc1.3.weight"].data_ptr(), p["_fc1.3.bias"].data_ptr(), R, F0, a1.data_ptr(), K.st))
+        z4 = _linear_fwd(K, a1, p["_fc1.4.weight"], p["_fc1.4.bias"], R, F0, DIM)
+        a4 = torch.empty_like(z4)
+        K.check(K.L.tm_gelu_fwd(z4.data_ptr(), a4.data_ptr(), R * DIM, K.st))
+        da4, g["_fc1.7.weight"], g["_fc1.7.bias"] = K.ln_bwd(a4, p["_fc1.7.weight"], dhf, R, DIM, R, R, 0, None)
+        K.check(K.L.tm_gelu_bwd(z4.data_ptr(), da4.data_ptr(), z4.data_ptr(), R * DIM, K.st))           # z4 <- dz4
+        _linear_wgrad(K, z4, a1, g, "_fc1.4", R, F0, DIM)
+        da1 = K.gemm(z4, (DIM, 1), p["_fc1.4.weight"], (F0, 1), a1, R, F0, DIM, F0)                      # a1 <- da1
+        da0, g["_fc1.3.weight"], g["_fc1.3.bias"] = K.ln_bwd(a0, p["_fc1.3.weight"], da1, R, F0, R, R, 0, None)
+        K.check(K.L.tm_gelu_bwd(z0.data_ptr(), da0.data_ptr(), z0.data_ptr(), R * F0, K.st))            # z0 <- dz0
+        _linear_wgrad(K, z0, xf, g, "_fc1.0", R, D, F0)
+        return g
+    raise ValueError(f"unknown _fc1 kind {kind}")
 
 
 def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0), drop=0.0):
