@@ -74,6 +74,19 @@ def test_forward_argument_contract_and_no_cpu_fallback():
         m(torch.zeros(1, 10, 512), return_attn=True)
 
 
+def test_hooks_on_the_gradcam_layers_are_refused_loudly():
+    """train_loop.py:87 hooks model.layer2.norm; the fused path cannot serve that yet and must say so, not skip it silently."""
+    m = build_model(2, 512)
+    handle = m.layer2.norm.register_forward_hook(lambda mod, inp, out: None)
+    with pytest.raises(NotImplementedError, match="layer2.norm"):
+        m(torch.zeros(1, 10, 512))
+    handle.remove()
+    if not torch.cuda.is_available():
+        import transmil_b200 as T
+        with pytest.raises(T.capi.TransmilError):        # back to the ordinary (CUDA-only) path
+            m(torch.zeros(1, 10, 512))
+
+
 def test_load_reference_checkpoint_keys_roundtrip():
     """Consumers strip the Lightning 'model.' prefix and load_state_dict into a bare TransMIL
     (code/visualize_mil.py:165-172)."""

@@ -173,6 +173,7 @@ class TransMIL(nn.Module):
             x = kwargs.get("data")          # upstream TransMIL: forward(**kwargs) with kwargs['data']
         if x is None:
             raise TypeError("forward() needs the bag tensor (positional `x` or keyword `data`)")
+        self._refuse_hooks()
         if torch.is_grad_enabled() and (self.training or self.keep_graph):
             # training_step (code/models/model_interface.py:333-383): forward with every stage kept + the library's backward
             # (csrc/backward.cu) behind a torch.autograd.Function; train mode applies the to_out Dropout(0.7)
@@ -218,6 +219,17 @@ class TransMIL(nn.Module):
             self._ws = None   # the lazy view owns this workspace now
             return logits, (attn, int(plan.padding))
         return logits
+
+    def _refuse_hooks(self):
+        """The reference's GradCAM consumers hook `layer1.norm` / `layer2.norm` (code/train_loop.py:87,
+        code/test_visualize.py:121-127).  Those sub-modules are parameter containers here -- their forward never runs, so
+        a hook on them would silently never fire.  Refuse instead of returning a CAM of nothing (not built)."""
+        for name in ("layer1", "layer2"):
+            norm = getattr(self, name).norm
+            if norm._forward_hooks or norm._forward_pre_hooks or norm._backward_hooks:
+                raise NotImplementedError(f"libtransmil_b200: a hook is registered on {name}.norm (GradCAM-style consumer); the fused "
+                                          "path does not materialise that activation for hooks yet -- remove the hook or use "
+                                          "return_attn=True rows")
 
     def _forward_train(self, x):
         from . import training
