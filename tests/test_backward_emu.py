@@ -231,6 +231,53 @@ def test_stem_backward_of_every_fc1_form(K, T, D, n, B):
         _close(g[k].reshape(ref[k].shape), ref[k], 1e-3, k)
 
 
+def test_gradcam_style_hook_on_layer2_norm(K, T, monkeypatch):
+    """A forward hook on model.layer2.norm (code/train_loop.py:87) that keeps the activation and registers a gradient hook on it,
+    as pytorch_grad_cam does: the hook sees LayerNorm(h2) and the true d(loss)/d(activation), and every parameter gradient is
+    what the unhooked backward gives.  Kernels run through the host harness, kept stages come from the forward oracle."""
+    import contextlib
+    from transmil_b200 import training
+    D, nc, n, B = 96, 3, 130, 1
+    m = build_model(nc, D)
+    sd = {k: v.detach().contiguous() for k, v in m.state_dict().items()}
+    x = make_input("randn", B, n, D, 79)
+    dlogits = torch.randn(B, nc, generator=torch.Generator().manual_seed(15))
+    monkeypatch.setattr(training, "_kernels_for", lambda t: (contextlib.nullcontext(), K))
+    monkeypatch.setattr(training, "forward_keep", lambda model, t, tr, seeds: (*_saved_from_oracle(sd, t), None))
+    monkeypatch.setattr(training, "bind", lambda lib: lib)
+    monkeypatch.setattr(T.capi, "lib", lambda: K.L)
+    m._weights = lambda: _weights(T, sd, m._fc1_kind, D, nc)
+    seen = {}
+
+    def hook(mod, inp, out):
+        seen["module"], seen["input"], seen["act"] = mod, inp[0], out.detach().clone()
+        out.register_hook(lambda gr: seen.__setitem__("grad", gr.detach().clone()))
+
+    m.layer2.norm.register_forward_hook(hook)
+    logits = training.forward_with_norm_hooks(m, x, ["layer2"])
+    (logits * dlogits).sum().backward()
+    # reference: float64 oracle, layer 2 re-run from its LayerNorm output under autograd
+    sd64 = {k: v.double() for k, v in sd.items()}
+    ref_logits, st = O.forward(sd64, x.double(), return_stages=True, dtype=torch.float64)
+    h2 = st["h2"]
+    xn = F.layer_norm(h2, (512,), sd64["layer2.norm.weight"], sd64["layer2.norm.bias"], 1e-5).requires_grad_(True)
+    h3 = h2 + O.nystrom(sd64, "layer2.attn.", xn)
+    out = F.linear(F.layer_norm(h3, (512,), sd64["norm.weight"], sd64["norm.bias"], 1e-5)[:, 0], sd64["_fc.weight"], sd64["_fc.bias"])
+    _close(out, ref_logits, 1e-9, "oracle layer-2 replay")
+    (out * dlogits.double()).sum().backward()
+    assert seen["module"] is m.layer2.norm and seen["act"].shape == (B, n_tokens(n), 512)
+    _close(seen["input"], h2, 1e-5, "hook input (layer input h2)")
+    _close(seen["act"], xn.detach(), 1e-5, "hook output (LayerNorm(h2))")
+    _close(seen["grad"], xn.grad, 2e-3, "gradient delivered to the hooked activation")
+    ref, _ = OB.backward(sd, x, dlogits.double())
+    for k, prm in m.named_parameters():
+        _close(prm.grad, ref[k].reshape(prm.shape), 2e-3, k)
+
+
+def n_tokens(n):
+    return O.plan(n)["S"]
+
+
 def test_dropout_mask_is_the_same_in_forward_and_backward(K):
     g = torch.Generator().manual_seed(13)
     B, S, P, Cc, p, seed = 2, 50, 6, 512, 0.7, 123456789

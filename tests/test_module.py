@@ -74,17 +74,22 @@ def test_forward_argument_contract_and_no_cpu_fallback():
         m(torch.zeros(1, 10, 512), return_attn=True)
 
 
-def test_hooks_on_the_gradcam_layers_are_refused_loudly():
-    """train_loop.py:87 hooks model.layer2.norm; the fused path cannot serve that yet and must say so, not skip it silently."""
+def test_hooks_on_the_gradcam_layers_are_never_skipped_silently():
+    """train_loop.py:87 hooks model.layer2.norm.  Forward hooks are served by the autograd path (tests/test_backward_emu.py,
+    tests/test_zzz_gradcam_hooks_gpu.py); without autograd, or for other hook kinds, the forward says so instead of skipping them."""
+    import transmil_b200 as T
     m = build_model(2, 512)
     handle = m.layer2.norm.register_forward_hook(lambda mod, inp, out: None)
-    with pytest.raises(NotImplementedError, match="layer2.norm"):
+    with torch.no_grad(), pytest.raises(NotImplementedError, match="layer2.norm"):
+        m(torch.zeros(1, 10, 512))
+    if not torch.cuda.is_available():
+        with pytest.raises(T.capi.TransmilError, match="no CPU path"):      # autograd on: routed to the (CUDA-only) training path
+            m(torch.zeros(1, 10, 512))
+    handle.remove()
+    handle = m.layer1.norm.register_forward_pre_hook(lambda mod, inp: None)
+    with pytest.raises(NotImplementedError, match="only forward hooks"):
         m(torch.zeros(1, 10, 512))
     handle.remove()
-    if not torch.cuda.is_available():
-        import transmil_b200 as T
-        with pytest.raises(T.capi.TransmilError):        # back to the ordinary (CUDA-only) path
-            m(torch.zeros(1, 10, 512))
 
 
 def test_load_reference_checkpoint_keys_roundtrip():

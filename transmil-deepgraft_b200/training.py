@@ -70,7 +70,7 @@ class Kernels:
 
 
 # ---- backward ---------------------------------------------------------------------------------------------------------------
-def layer_backward(K, p, name, h_in, sv, dy, plan, seed=0, drop=0.0):
+def layer_backward(K, p, name, h_in, sv, dy, plan, seed=0, drop=0.0, keep_dxn=False):
     """Backward of TransLayer.forward (TransMIL.py:45-57): h_in + attn(norm(h_in)).  sv: the layer's kept stages.
     Returns dh_in and the gradients of the layer's six parameter tensors (oracle/transmil_backward.py nystrom_backward)."""
     B, S, _ = h_in.shape
@@ -133,6 +133,8 @@ def layer_backward(K, p, name, h_in, sv, dy, plan, seed=0, drop=0.0):
     # LayerNorm + residual
     dh, gg, gb = K.ln_bwd(h_in, p[name + ".norm.weight"], dxn, B * S, DIM, S, Sp, P, dy)
     g[name + ".norm.weight"], g[name + ".norm.bias"] = gg, gb
+    if keep_dxn:    # gradient of the LayerNorm output (front pad rows included): what a GradCAM hook on `<layer>.norm` asks for
+        g[name + "._dxn"] = dxn
     return dh, g
 
 
@@ -196,7 +198,7 @@ def fc1_backward(K, p, kind, x, dhf):
     raise ValueError(f"unknown _fc1 kind {kind}")
 
 
-def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0), drop=0.0):
+def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0), drop=0.0, keep_dxn=False):
     """Gradients of sum(logits * dlogits) for every parameter (reference state_dict keys).  p: name -> parameter tensor,
     w: capi.Weights of the same tensors, saved: stages kept by the forward.  Stage order = reverse of TransMIL.forward
     (TransMIL.py:167-211); mirrors oracle/transmil_backward.py backward()."""
@@ -215,7 +217,7 @@ def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0), drop=0.0):
                             g["norm.bias"].data_ptr(), g["_fc.weight"].data_ptr(), g["_fc.bias"].data_ptr(), K.st))
     dh3 = torch.zeros((B, S, DIM), dtype=torch.float32, device=x.device)
     dh3[:, 0] = dcls
-    dh2, gl = layer_backward(K, p, "layer2", h2, saved["layer2"], dh3, plan, seeds[1], drop)
+    dh2, gl = layer_backward(K, p, "layer2", h2, saved["layer2"], dh3, plan, seeds[1], drop, keep_dxn)
     g.update(gl)
     del dh3
     # PPEG
@@ -227,7 +229,7 @@ def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0), drop=0.0):
                             gp["proj2.weight"].data_ptr(), gp["proj2.bias"].data_ptr(), sc.data_ptr(), K.st))
     g.update({"pos_layer." + k: v for k, v in gp.items()})
     del dh2, sc
-    dh0, gl = layer_backward(K, p, "layer1", h0, saved["layer1"], dh1, plan, seeds[0], drop)
+    dh0, gl = layer_backward(K, p, "layer1", h0, saved["layer1"], dh1, plan, seeds[0], drop, keep_dxn)
     g.update(gl)
     del dh1
     # cls token + duplicate pad
@@ -315,13 +317,98 @@ class TransMILFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dlogits):
-        model, x = ctx.model, ctx.x
-        p = {n: t.detach() for n, t in model.named_parameters()}
-        with torch.cuda.device(x.device):
-            K = Kernels(stream=torch.cuda.current_stream(x.device).cuda_stream)
-            g = backward(K, p, model._weights(), model._fc1_kind, x, ctx.saved, dlogits, ctx.seeds,
-                         TO_OUT_DROPOUT if ctx.training else 0.0)
-        ctx.saved = None
-        if model.HEAD != "_fc":   # sibling models name the classifier differently (MDMIL._fc2)
-            g[model.HEAD + ".weight"], g[model.HEAD + ".bias"] = g.pop("_fc.weight"), g.pop("_fc.bias")
+        p, g = _param_grads(ctx, dlogits)
         return (None, None) + tuple(g[n].reshape(p[n].shape) for n in ctx.names)
+
+
+def _kernels_for(x):
+    """(device context, Kernels) of the tensor's device and current stream; the host harness of the tests replaces this."""
+    return torch.cuda.device(x.device), Kernels(stream=torch.cuda.current_stream(x.device).cuda_stream)
+
+
+def _param_grads(ctx, dlogits, keep_dxn=False):
+    """The library backward for what a forward kept on `ctx`: (parameters by name, gradients by name)."""
+    model, x = ctx.model, ctx.x
+    p = {n: t.detach() for n, t in model.named_parameters()}
+    dev, K = _kernels_for(x)
+    with dev:
+        g = backward(K, p, model._weights(), model._fc1_kind, x, ctx.saved, dlogits, ctx.seeds,
+                     TO_OUT_DROPOUT if ctx.training else 0.0, keep_dxn)
+    ctx.saved = None
+    if model.HEAD != "_fc":   # sibling models name the classifier differently (MDMIL._fc2)
+        g[model.HEAD + ".weight"], g[model.HEAD + ".bias"] = g.pop("_fc.weight"), g.pop("_fc.bias")
+    return p, g
+
+
+# ---- GradCAM-style hooks on `<layer>.norm` (SURVEY 8f/N1; consumers: code/train_loop.py:87, code/test_visualize.py:121-127) -----
+class _Holder:
+    """Links the two autograd nodes of a hooked forward."""
+
+    def __init__(self):
+        self.ctx, self.inputs, self.grads, self.params = None, {}, None, None
+
+
+class _HookedFunction(torch.autograd.Function):
+    """TransMILFunction that also returns the LayerNorm outputs of the hooked layers (rows of `xn` behind the front pad,
+    [B,S,512]) as autograd outputs, so that a consumer can keep them and register gradient hooks on them."""
+
+    @staticmethod
+    def forward(ctx, model, x, holder, hooked, *params):
+        bind(capi.lib())
+        training = model.training
+        if training and model._fc1_kind == capi.TM_FC1_768:
+            raise NotImplementedError("libtransmil_b200: training the 768-d stem (Dropout(0.6) inside _fc1) is not built")
+        seeds = tuple(int(s) for s in torch.randint(0, 2 ** 62, (2,))) if training else (0, 0)
+        with _kernels_for(x)[0]:
+            logits, saved, _w = forward_keep(model, x, training, seeds)
+        ctx.model, ctx.x, ctx.saved, ctx.seeds, ctx.training = model, x, saved, seeds, training
+        ctx.names = [n for n, _ in model.named_parameters()]
+        ctx.hooked, ctx.P, ctx.holder = hooked, int(saved["plan"]["P"]), holder
+        holder.ctx = ctx
+        holder.inputs = {"layer1": saved["h0"], "layer2": saved["h2"]}
+        acts = tuple(saved[name]["xn"][:, ctx.P:].clone() for name in hooked)
+        return (logits,) + acts
+
+    @staticmethod
+    def backward(ctx, dlogits, *dacts):
+        holder = ctx.holder
+        if holder.grads is not None:                    # _AttachGrad ran the library backward already
+            p, g = holder.params, holder.grads
+            holder.grads = holder.params = None
+        else:
+            p, g = _param_grads(ctx, dlogits)
+        return (None, None, None, None) + tuple(g[n].reshape(p[n].shape) for n in ctx.names)
+
+
+class _AttachGrad(torch.autograd.Function):
+    """Identity on logits that makes the hooked activations part of the graph: its backward runs the library backward once,
+    hands d(loss)/d(activation) to autograd (tensor hooks on the activations fire with the true gradient) and leaves the
+    parameter gradients for _HookedFunction.backward, which runs right after it."""
+
+    @staticmethod
+    def forward(ctx, logits, holder, *acts):
+        ctx.holder = holder
+        return logits.clone()
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        holder = ctx.holder
+        main = holder.ctx
+        holder.params, holder.grads = _param_grads(main, dlogits.contiguous(), keep_dxn=True)
+        dacts = tuple(holder.grads[name + "._dxn"][:, main.P:].contiguous() for name in main.hooked)
+        return (dlogits, None) + dacts
+
+
+def forward_with_norm_hooks(model, x, hooked):
+    """Forward of the autograd path with the forward hooks of `<layer>.norm` honoured for the layers in `hooked`: each hook
+    is called as `hook(norm_module, (layer input [B,S,512],), LayerNorm output [B,S,512])`, the way torch calls it in the
+    reference, where TransLayer runs `self.norm(x)` (TransMIL.py:47).  Hooks that return a replacement output are refused."""
+    holder = _Holder()
+    outs = _HookedFunction.apply(model, x, holder, tuple(hooked), *model.parameters())
+    logits, acts = outs[0], outs[1:]
+    for name, act in zip(hooked, acts):
+        norm = getattr(model, name).norm
+        for hook in list(norm._forward_hooks.values()):
+            if hook(norm, (holder.inputs[name],), act) is not None:
+                raise NotImplementedError("libtransmil_b200: a forward hook on %s.norm returned a replacement output" % name)
+    return _AttachGrad.apply(logits, holder, *acts)

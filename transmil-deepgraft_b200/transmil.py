@@ -173,8 +173,8 @@ class TransMIL(nn.Module):
             x = kwargs.get("data")          # upstream TransMIL: forward(**kwargs) with kwargs['data']
         if x is None:
             raise TypeError("forward() needs the bag tensor (positional `x` or keyword `data`)")
-        self._refuse_hooks()
-        if torch.is_grad_enabled() and (self.training or self.keep_graph):
+        hooked = self._hooked_norms()
+        if torch.is_grad_enabled() and (self.training or self.keep_graph or hooked):
             # training_step (code/models/model_interface.py:333-383): forward with every stage kept + the library's backward
             # (csrc/backward.cu) behind a torch.autograd.Function; train mode applies the to_out Dropout(0.7)
             if return_attn:
@@ -220,16 +220,22 @@ class TransMIL(nn.Module):
             return logits, (attn, int(plan.padding))
         return logits
 
-    def _refuse_hooks(self):
+    def _hooked_norms(self):
         """The reference's GradCAM consumers hook `layer1.norm` / `layer2.norm` (code/train_loop.py:87,
-        code/test_visualize.py:121-127).  Those sub-modules are parameter containers here -- their forward never runs, so
-        a hook on them would silently never fire.  Refuse instead of returning a CAM of nothing (not built)."""
+        code/test_visualize.py:121-127).  Those sub-modules are parameter containers here -- their forward never runs.
+        With autograd on, forward hooks on them are honoured by the training path (training.forward_with_norm_hooks:
+        activation and its gradient, which is what GradCAM reads); anything else is refused rather than silently skipped."""
+        hooked = []
         for name in ("layer1", "layer2"):
             norm = getattr(self, name).norm
-            if norm._forward_hooks or norm._forward_pre_hooks or norm._backward_hooks:
-                raise NotImplementedError(f"libtransmil_b200: a hook is registered on {name}.norm (GradCAM-style consumer); the fused "
-                                          "path does not materialise that activation for hooks yet -- remove the hook or use "
-                                          "return_attn=True rows")
+            if norm._forward_pre_hooks or norm._backward_hooks or getattr(norm, "_backward_pre_hooks", None):
+                raise NotImplementedError(f"libtransmil_b200: only forward hooks are supported on {name}.norm")
+            if norm._forward_hooks:
+                if not torch.is_grad_enabled():
+                    raise NotImplementedError(f"libtransmil_b200: a forward hook is registered on {name}.norm; hooks are served by "
+                                              "the autograd path only (call the model with gradients enabled, as GradCAM does)")
+                hooked.append(name)
+        return hooked
 
     def _forward_train(self, x):
         from . import training
@@ -243,6 +249,9 @@ class TransMIL(nn.Module):
         if device.type != "cuda":
             raise capi.TransmilError("TransMIL must be on a CUDA device (model.cuda()); there is no CPU path")
         xd = x.detach().to(device=device, dtype=torch.float32, non_blocking=True).contiguous()   # x.float(), TransMIL.py:174
+        hooked = self._hooked_norms()
+        if hooked:
+            return training.forward_with_norm_hooks(self, xd, hooked)
         return training.TransMILFunction.apply(self, xd, *self.parameters())
 
     def stage(self, name):
@@ -373,7 +382,7 @@ class MDMIL(TransMIL):
         self._stage_key = None
 
     def forward(self, x):
-        if torch.is_grad_enabled() and (self.training or self.keep_graph):
+        if torch.is_grad_enabled() and (self.training or self.keep_graph or self._hooked_norms()):
             return TransMIL.forward(self, x), None
         logits, (attn, _padding) = TransMIL.forward(self, x, return_attn=True)
         return logits, attn
