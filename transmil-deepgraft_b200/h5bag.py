@@ -16,7 +16,6 @@ layout) and files written by tests/h5_writer.py (chunked / filtered layouts), wh
 """
 import mmap
 import os
-import struct
 import zlib
 
 import numpy as np
