@@ -134,3 +134,19 @@ def test_reference_sized_bag_reads_in_few_copies(tmp_path):
     p = W.write_h5(tmp_path / "big.h5", {"features": (x, dict(chunks=(1, 64), maxshape=(None, 64), btree_cap=64))})
     bag, _ = h5bag.read_bag(p, pin=False)
     assert torch.equal(bag, torch.from_numpy(x))
+
+
+def test_threaded_prefetch_keeps_order_and_content(tmp_path):
+    paths, arrays = [], []
+    for i, n in enumerate([40, 1, 300, 7, 120, 64, 5, 200, 33]):
+        x, c = _bag(n, 32, np.float32, 20 + i)
+        paths.append(W.write_h5(tmp_path / f"s{i}.h5", {"features": (x, dict(chunks=(1, 32), maxshape=(None, 32))), "coords": c}))
+        arrays.append((x, c))
+    for workers in (0, 1, 3):
+        got = list(h5bag.iter_bags(paths, pin=False, workers=workers, with_coords=True))
+        assert len(got) == len(arrays)
+        for (bag, xy), (x, c) in zip(got, arrays):
+            assert torch.equal(bag, torch.from_numpy(x)) and torch.equal(xy, torch.from_numpy(c))
+    it = h5bag.iter_bags(paths + [tmp_path / "missing.h5"], pin=False, workers=2)
+    with pytest.raises(FileNotFoundError):
+        list(it)
