@@ -126,3 +126,27 @@ def test_reference_checkpoint_loads_with_the_model_prefix(tmp_path):
     with pytest.raises(RuntimeError):
         plugin.load_reference_checkpoint(build_model(3, 1024, seed=1), ckpt)
     plugin.load_reference_checkpoint(build_model(3, 1024, seed=1), ckpt, strict=False)
+
+
+def test_validation_step_mirror_follows_the_reference():
+    """model_interface.py:432-470 + utils/utils.py:242-247, with a host stand-in for the model call."""
+    from transmil_b200 import plugin
+
+    class Stub(torch.nn.Module):
+        n_classes = 3
+
+        def forward(self, x):
+            assert not torch.is_grad_enabled() and x.dtype == torch.float32 and x.is_contiguous()
+            return x.sum(1)[:, :3]
+
+    x = torch.randn(2, 5, 4, dtype=torch.float64)
+    label = torch.tensor([2, 0])
+    out = plugin.validation_step(Stub(), (x, label, (("slide_a", "slide_b"), None, ("p1", "p2"))))
+    logits = x.float().sum(1)[:, :3]
+    assert torch.equal(out["logits"], logits) and torch.equal(out["Y_hat"], logits.argmax(1))
+    assert torch.allclose(out["Y_prob"], logits.softmax(1)) and out["label"].dtype == torch.int32
+    # the reference's loop form of the loss
+    sm = [torch.softmax(logits[i], dim=0) for i in range(2)]
+    ref = -torch.sum(torch.tensor([torch.log(sm[i][label[i]]) for i in range(2)])) / 2
+    assert torch.allclose(out["loss"], ref) and not out["loss"].requires_grad
+    assert out["name"] == ("slide_a", "slide_b") and out["patient"] == ("p1", "p2")

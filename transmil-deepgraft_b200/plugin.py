@@ -91,3 +91,26 @@ def training_step(model, batch, loss_fn=None):
     if loss.ndim == 0:
         loss = loss.unsqueeze(0)
     return loss, Y_prob, Y_hat
+
+
+def cross_entropy_torch(x, y):
+    """code/utils/utils.py:242-247: mean over the batch of -log softmax(x_i)[y_i], as a detached scalar (the reference builds
+    it with torch.tensor(...), so it carries no graph)."""
+    import torch
+    y = torch.as_tensor(y, device=x.device).long().reshape(-1)
+    return -torch.log_softmax(x.detach().float(), dim=1).gather(1, y[:, None]).sum() / y.shape[0]
+
+
+def validation_step(model, batch):
+    """ModelInterface.validation_step (code/models/model_interface.py:432-470) without the Lightning bookkeeping: `batch` is
+    (input, label, (wsi_name, coords, patient)); returns the dict the reference appends to `validation_step_outputs` (:470):
+    detached logits / Y_prob / Y_hat, `label.int()`, slide name, patient and the `cross_entropy_torch` loss (:446).  Runs the
+    inference path (no autograd) whatever mode the module is in, as Lightning's validation loop does."""
+    import torch
+    input, label, (wsi_name, _, patient) = batch
+    with torch.no_grad():
+        logits, Y_prob, Y_hat = step(model, input)
+    logits, Y_prob, Y_hat = logits.detach(), Y_prob.detach(), Y_hat.detach()
+    loss = cross_entropy_torch(logits, label)
+    return {"logits": logits, "Y_prob": Y_prob, "Y_hat": Y_hat, "label": torch.as_tensor(label).int(), "name": wsi_name,
+            "patient": patient, "loss": loss}
