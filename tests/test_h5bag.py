@@ -150,3 +150,33 @@ def test_threaded_prefetch_keeps_order_and_content(tmp_path):
     it = h5bag.iter_bags(paths + [tmp_path / "missing.h5"], pin=False, workers=2)
     with pytest.raises(FileNotFoundError):
         list(it)
+
+
+@pytest.mark.parametrize("variant", list(VARIANTS))
+def test_row_ranges_touch_only_their_chunks(tmp_path, variant):
+    x, _ = _bag(501, 96, np.float32, 9)
+    p = W.write_h5(tmp_path / "r.h5", {"features": (x, VARIANTS[variant])})
+    with h5bag.FeatureFile(p) as f:
+        ds = f["features"]
+        for r0, r1 in [(0, 501), (0, 1), (500, 501), (13, 77), (66, 99), (7, 7), (33, 330), (495, 501)]:
+            assert np.array_equal(ds.read_rows(r0, r1), x[r0:r1]), (r0, r1)
+            assert np.array_equal(ds[r0:r1], x[r0:r1])
+        assert np.array_equal(ds[-5:], x[-5:]) and np.array_equal(ds[::2], x[::2]) and np.array_equal(ds[3], x[3])
+        with pytest.raises(IndexError):
+            ds.read_rows(10, 502)
+    ranges = [(400, 501), (0, 37)]
+    got = h5bag.read_bag_rows(p, ranges, pin=False)
+    assert torch.equal(got, torch.from_numpy(np.concatenate([x[a:b] for a, b in ranges])))
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_shard_plan_reads_only_its_rows_of_a_file(tmp_path, world):
+    """ShardPlan.take_from_file == ShardPlan.take on the full bag, for every rank of a token-sharded bag."""
+    from transmil_b200 import sharded
+    n, D = 5000, 32
+    x, _ = _bag(n, D, np.float32, 10)
+    p = W.write_h5(tmp_path / "giant.h5", {"features": (x, dict(chunks=(1, D), maxshape=(None, D)))})
+    plan = sharded.ShardPlan(n, world)
+    full = torch.from_numpy(x)
+    for rank in range(world):
+        assert torch.equal(plan.take_from_file(p, rank, pin=False), plan.take(full, rank))

@@ -20,7 +20,7 @@ import zlib
 
 import numpy as np
 
-__all__ = ["H5FormatError", "FeatureFile", "Dataset", "read_bag", "iter_bags"]
+__all__ = ["H5FormatError", "FeatureFile", "Dataset", "read_bag", "read_bag_rows", "iter_bags"]
 
 SIGNATURE = b"\x89HDF\r\n\x1a\n"
 MSG_DATASPACE, MSG_DATATYPE, MSG_FILL_OLD, MSG_FILL, MSG_LAYOUT, MSG_FILTERS = 0x1, 0x3, 0x4, 0x5, 0x8, 0xB
@@ -324,48 +324,67 @@ class Dataset:
 
     # ---- reads ------------------------------------------------------------------------------------------------------
     def read_direct(self, out):
+        """The whole dataset into a caller-owned array."""
+        return self.read_rows(0, self.shape[0] if self.shape else 0, out)
+
+    def read_rows(self, r0, r1, out=None):
+        """Rows [r0, r1) of the leading axis into `out` (shape (r1-r0,) + shape[1:]; allocated when None).  Only the chunks
+        that hold those rows are touched: a rank of a token-sharded bag reads its own rows of a 1.6 GB file, not the file."""
+        if not self.shape:
+            raise H5FormatError("scalar datasets are not supported")
+        n = self.shape[0]
+        if not (0 <= r0 <= r1 <= n):
+            raise IndexError(f"rows [{r0}, {r1}) outside a dataset of {n} rows")
+        want = (r1 - r0,) + tuple(self.shape[1:])
+        if out is None:
+            out = np.empty(want, self.dtype.newbyteorder("="))
         if not isinstance(out, np.ndarray) or not out.flags.c_contiguous or not out.flags.writeable:
-            raise ValueError("read_direct needs a writeable C-contiguous numpy array")
-        if tuple(out.shape) != tuple(self.shape):
-            raise ValueError(f"destination has shape {tuple(out.shape)}, dataset '{self.name}' has {tuple(self.shape)}")
+            raise ValueError("read_direct / read_rows need a writeable C-contiguous numpy array")
+        if tuple(out.shape) != want:
+            raise ValueError(f"destination has shape {tuple(out.shape)}, rows [{r0}, {r1}) of dataset '{self.name}' have {want}")
         buf, kind = self._buf, self._layout[0]
-        count = int(np.prod(self.shape, dtype=np.int64))
-        if count == 0:
+        per_row = int(np.prod(self.shape[1:], dtype=np.int64))
+        if out.size == 0:
             return out
         if kind in ("compact", "contiguous"):
             addr = self._layout[1]
             if kind == "contiguous" and addr == buf.undef:      # never written: fill value (0)
                 out[...] = 0
                 return out
-            np.copyto(out, buf.array(addr, self.dtype, count).reshape(self.shape), casting="unsafe")
+            src = buf.array(addr + r0 * per_row * self.dtype.itemsize, self.dtype, (r1 - r0) * per_row)
+            np.copyto(out, src.reshape(want), casting="unsafe")
             return out
         chunks, isz = self.chunks, self.dtype.itemsize
         celems = int(np.prod(chunks, dtype=np.int64))
         cbytes = celems * isz
         offs, addrs, sizes, masks = self._chunk_list()
         keep = (offs < np.asarray(self.shape, np.int64)).all(axis=1)      # drop chunks left behind by a shrink
+        keep &= (offs[:, 0] < r1) & (offs[:, 0] + chunks[0] > r0)         # chunks that hold rows of the range
         offs, addrs, sizes, masks = offs[keep], addrs[keep], sizes[keep], masks[keep]
         grid = [-(-s // c) for s, c in zip(self.shape, chunks)]
+        grid[0] = (r1 - 1) // chunks[0] - r0 // chunks[0] + 1
         if len(addrs) < int(np.prod(grid, dtype=np.int64)):
             out[...] = 0                                         # unallocated chunks read as the fill value (0)
         if len(addrs) == 0:
             return out
         row_chunks = all(c == s for c, s in zip(chunks[1:], self.shape[1:]))
-        if row_chunks and not self._filters:
+        aligned = r0 % chunks[0] == 0 and (r1 % chunks[0] == 0 or r1 == n)
+        if row_chunks and aligned and not self._filters:
             # chunks span whole rows (the reference's (1, D) chunks): consecutive chunks that are also adjacent in the file
             # (h5py appends them in order) are one contiguous run of the output -> one copy per run, not per chunk
-            flat = out.reshape(self.shape[0], -1)
+            flat = out.reshape(r1 - r0, -1)
             rows = offs[:, 0]
             brk = np.flatnonzero((np.diff(addrs) != cbytes) | (np.diff(rows) != chunks[0])) + 1
             starts = np.concatenate(([0], brk)).tolist()
             ends = np.concatenate((brk, [len(addrs)])).tolist()
-            per_row = flat.shape[1]
             for a, b in zip(starts, ends):
-                r0 = int(rows[a])
-                r1 = min(r0 + (b - a) * chunks[0], self.shape[0])
-                src = buf.array(int(addrs[a]), self.dtype, (b - a) * celems)[:(r1 - r0) * per_row]
-                np.copyto(flat[r0:r1], src.reshape(r1 - r0, per_row), casting="unsafe")
+                c0 = int(rows[a])
+                c1 = min(c0 + (b - a) * chunks[0], r1)
+                src = buf.array(int(addrs[a]), self.dtype, (b - a) * celems)[:(c1 - c0) * per_row]
+                np.copyto(flat[c0 - r0:c1 - r0], src.reshape(c1 - c0, per_row), casting="unsafe")
             return out
+        lo = (r0,) + (0,) * (len(self.shape) - 1)
+        hi = (r1,) + tuple(self.shape[1:])
         for i in range(len(addrs)):
             o = offs[i].tolist()
             if self._filters:
@@ -373,15 +392,20 @@ class Dataset:
                 block = np.frombuffer(data, self.dtype, celems).reshape(chunks)
             else:
                 block = buf.array(int(addrs[i]), self.dtype, celems).reshape(chunks)
-            sel = tuple(slice(a, min(a + c, s)) for a, c, s in zip(o, chunks, self.shape))
-            cut = tuple(slice(0, s.stop - s.start) for s in sel)
-            np.copyto(out[sel], block[cut], casting="unsafe")
+            beg = [max(a, l) for a, l in zip(o, lo)]
+            end = [min(a + c, h) for a, c, h in zip(o, chunks, hi)]
+            dst = tuple(slice(b - l, e - l) for b, e, l in zip(beg, end, lo))
+            cut = tuple(slice(b - a, e - a) for b, e, a in zip(beg, end, o))
+            np.copyto(out[dst], block[cut], casting="unsafe")
         return out
 
     def __getitem__(self, idx):
+        if isinstance(idx, slice) and idx.step in (None, 1) and self.shape:
+            r0, r1, _ = idx.indices(self.shape[0])
+            return self.read_rows(r0, max(r0, r1))
         full = np.empty(self.shape, self.dtype.newbyteorder("="))
         self.read_direct(full)
-        if idx is Ellipsis or idx == () or idx == slice(None):
+        if idx is Ellipsis or idx == ():
             return full
         return full[idx]
 
@@ -481,6 +505,25 @@ def read_bag(path, pin=None, dtype=None, features="features", coords="coords", o
         ds.read_direct(bag.numpy())
         xy = torch.from_numpy(f[coords][:]) if coords in f else None
     return bag, xy
+
+
+def read_bag_rows(path, ranges, pin=None, dtype=None, features="features"):
+    """Concatenation of the row ranges [(a, b), ...] of one bag's `features`, read range by range into one (pinned) host
+    tensor -- what a rank of the token-sharded path holds of a giant bag (`ShardPlan.take`: its own rows plus the duplicated
+    head rows it recomputes), without reading the rest of the file."""
+    import torch
+    if pin is None:
+        pin = torch.cuda.is_available()
+    ranges = [(int(a), int(b)) for a, b in ranges]
+    with FeatureFile(path) as f:
+        ds = f[features]
+        want = dtype if dtype is not None else torch.from_numpy(np.empty(0, ds.dtype.newbyteorder("="))).dtype
+        out = torch.empty((sum(b - a for a, b in ranges),) + tuple(ds.shape[1:]), dtype=want, pin_memory=bool(pin))
+        pos = 0
+        for a, b in ranges:
+            ds.read_rows(a, b, out[pos:pos + b - a].numpy())
+            pos += b - a
+    return out
 
 
 def iter_bags(paths, pin=None, dtype=None, with_coords=False, workers=0, ahead=2):

@@ -90,6 +90,12 @@ class ShardPlan:
             x = x[0]
         return torch.cat([x[a:b] for a, b in self.shards[rank].x_ranges], dim=0)
 
+    def take_from_file(self, path, rank, pin=None, dtype=None):
+        """`take` for a bag that lives in one of the reference's feature files (code/datasets/feature_dataloader.py:252-254):
+        only this rank's rows are read (h5bag.read_bag_rows), straight into pinned host memory."""
+        from . import h5bag
+        return h5bag.read_bag_rows(path, self.shards[rank].x_ranges, pin=pin, dtype=dtype)
+
 
 # ---------------------------------------------------------------------------------------------------------------------
 class CudaOps:
