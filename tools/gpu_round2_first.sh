@@ -16,3 +16,4 @@ timeout 300 python tools/bench_cfg5.py --features 1024 --f16 > gpurun_out/cfg5_1
 timeout 400 python tools/bench_torch_eager.py --n 50000 --features 1024 > gpurun_out/torch_eager_50k_1024.jsonl 2> gpurun_out/eager.err; echo "eager exit $?"
 timeout 300 python tools/bench_torch_eager.py --n 20000 --features 2048 > gpurun_out/torch_eager_20k_2048.jsonl 2>> gpurun_out/eager.err
 ls -la gpurun_out
+timeout 400 python tools/bench_files.py > gpurun_out/files_to_logits.jsonl 2> gpurun_out/files.err; echo "files exit $?"
