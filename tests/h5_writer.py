@@ -115,9 +115,12 @@ def _chunk_btree(f, entries, rank, cap):
 
 
 def _write_dataset(f, arr, chunks=None, maxshape=None, shuffle=False, deflate=None, btree_cap=64, interleave=False,
-                   split_header=False, skip_chunks=()):
+                   split_header=False, skip_chunks=(), fillvalue=None):
     arr = np.ascontiguousarray(arr)
     msgs = [_dataspace(arr.shape, maxshape), _datatype(arr.dtype)]
+    if fillvalue is not None:                       # fill value message version 2: alloc time 2, write time 0, defined, size, value
+        raw = np.asarray(fillvalue, arr.dtype).tobytes()
+        msgs.append(_msg(0x5, struct.pack("<BBBBI", 2, 2, 0, 1, len(raw)) + raw))
     if chunks is None:
         addr = f.alloc(arr.tobytes()) if arr.size else UNDEF
         msgs.append(_msg(0x8, struct.pack("<BBQQ", 3, 1, addr, arr.nbytes)))
@@ -153,7 +156,7 @@ def _write_dataset(f, arr, chunks=None, maxshape=None, shuffle=False, deflate=No
 
 def write_h5(path, datasets, userblock=0, **kw):
     """datasets: name -> array, or name -> (array, dict of per-dataset options: chunks, maxshape, shuffle, deflate,
-    btree_cap, interleave, split_header, skip_chunks)."""
+    btree_cap, interleave, split_header, skip_chunks, fillvalue)."""
     f = _File(userblock)
     f.alloc(b"\0" * 96)                                              # superblock, patched at the end
     links = {}

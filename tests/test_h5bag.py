@@ -82,6 +82,13 @@ def test_unallocated_chunks_read_as_fill_value_and_empty_dataset(tmp_path):
     want[8:12] = 0
     want[36:40] = 0
     assert np.array_equal(got, want)
+    p = W.write_h5(tmp_path / "f.h5", {"features": (x, dict(chunks=(4, 8), skip_chunks=((2, 0),), fillvalue=-1.5))})
+    with h5bag.FeatureFile(p) as f:
+        assert f["features"].fillvalue == np.float32(-1.5)
+        got = f["features"][:]
+    want = x.copy()
+    want[8:12] = -1.5
+    assert np.array_equal(got, want)
 
 
 def test_read_bag_fills_a_caller_owned_host_tensor(tmp_path):

@@ -243,6 +243,7 @@ class Dataset:
         self._buf, self.name = buf, name
         self.shape = self.dtype = self.maxshape = None
         self.chunks, self._filters, self._layout = None, [], None
+        self.fillvalue, fills = 0, []
         for mtype, _flags, p, size in _messages(buf, addr):
             if mtype == MSG_DATASPACE:
                 self.shape, self.maxshape = _parse_dataspace(buf, p)
@@ -252,10 +253,34 @@ class Dataset:
                 self._filters = _parse_filters(buf, p)
             elif mtype == MSG_LAYOUT:
                 self._parse_layout(p, size)
+            elif mtype in (MSG_FILL, MSG_FILL_OLD):
+                fills.append((mtype, p, size))
         if self.shape is None or self.dtype is None or self._layout is None:
             raise H5FormatError(f"'{name}' is not a dataset (dataspace / datatype / layout message missing)")
         if self._layout[0] == "chunked" and self._layout[3] != self.dtype.itemsize:
             raise H5FormatError("chunk element size disagrees with the datatype")
+        for mtype, p, size in fills:                # what unallocated chunks / never-written datasets read as (default 0)
+            raw = self._fill_bytes(mtype, p, size)
+            if raw is not None and len(raw) == self.dtype.itemsize:
+                self.fillvalue = np.frombuffer(raw, self.dtype, 1)[0]
+
+    def _fill_bytes(self, mtype, p, size):
+        buf = self._buf
+        if mtype == MSG_FILL_OLD:                   # size (4), value
+            n = buf.uint(p, 4)
+            return bytes(buf.bytes(p + 4, n)) if 0 < n <= size - 4 else None
+        ver = buf.uint(p, 1)
+        if ver in (1, 2):                           # version, alloc time, write time, defined, [size (4), value]
+            if ver == 2 and buf.uint(p + 3, 1) == 0:
+                return None
+            n = buf.uint(p + 4, 4) if size >= 8 else 0
+            return bytes(buf.bytes(p + 8, n)) if 0 < n <= size - 8 else None
+        if ver == 3:                                # version, flags (bit 5: value defined), [size (4), value]
+            if not buf.uint(p + 1, 1) & 0x20:
+                return None
+            n = buf.uint(p + 2, 4)
+            return bytes(buf.bytes(p + 6, n)) if 0 < n <= size - 6 else None
+        return None
 
     def _parse_layout(self, p, size):
         buf = self._buf
@@ -349,7 +374,7 @@ class Dataset:
         if kind in ("compact", "contiguous"):
             addr = self._layout[1]
             if kind == "contiguous" and addr == buf.undef:      # never written: fill value (0)
-                out[...] = 0
+                out[...] = self.fillvalue
                 return out
             src = buf.array(addr + r0 * per_row * self.dtype.itemsize, self.dtype, (r1 - r0) * per_row)
             np.copyto(out, src.reshape(want), casting="unsafe")
@@ -364,7 +389,7 @@ class Dataset:
         grid = [-(-s // c) for s, c in zip(self.shape, chunks)]
         grid[0] = (r1 - 1) // chunks[0] - r0 // chunks[0] + 1
         if len(addrs) < int(np.prod(grid, dtype=np.int64)):
-            out[...] = 0                                         # unallocated chunks read as the fill value (0)
+            out[...] = self.fillvalue                            # unallocated chunks read as the fill value (default 0)
         if len(addrs) == 0:
             return out
         row_chunks = all(c == s for c, s in zip(chunks[1:], self.shape[1:]))
