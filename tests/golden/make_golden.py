@@ -45,7 +45,8 @@ CASES = [
     (1024, 2, 6000, 1, "rand", "reference"),     # BASELINE config 1 (Camelyon, CPU-runnable)
     (2048, 3, 6000, 1, "randn", "reference"),    # TransMIL.py:216 __main__ smoke shape
     (2048, 2, 20000, 1, "rand", "oracle"),       # BASELINE config 2 bag size
-]
+    (2048, 2, 1000, 64, "rand", "reference"),    # the reference's default training batch: 64 bags x 1000 patches
+]                                                # (feature_dataloader.py:27,388-401); appended with --append
 
 
 def make_input(gen, B, n, D, seed):
@@ -62,8 +63,17 @@ def main():
     torch.set_num_threads(os.cpu_count())
     torch.set_float32_matmul_precision("highest")
     out = {"weight_seed": WEIGHT_SEED, "cases": []}
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "transmil_golden.json")
+    if "--append" in sys.argv:      # keep the cases already in the fixture byte for byte, compute only the new tail of CASES
+        with open(path) as f:
+            out = json.load(f)
+        assert out["weight_seed"] == WEIGHT_SEED and len(out["cases"]) <= len(CASES)
     models = {}
     for i, (D, nc, n, B, gen, source) in enumerate(CASES):
+        if i < len(out["cases"]):
+            c = out["cases"][i]
+            assert (c["in_features"], c["n_classes"], c["n"], c["B"], c["gen"], c["source"]) == (D, nc, n, B, gen, source)
+            continue
         key = (D, nc)
         if key not in models:
             models[key] = ref_loader.build_reference(nc, D, seed=WEIGHT_SEED)
@@ -101,7 +111,6 @@ def main():
         }
         out["cases"].append(case)
         print(i, D, nc, n, B, gen, source, case["logits"][0])
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "transmil_golden.json")
     with open(path, "w") as f:
         json.dump(out, f, indent=1)
     print("wrote", path, os.path.getsize(path), "bytes")

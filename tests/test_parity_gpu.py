@@ -35,7 +35,8 @@ def _close(a, b, atol, rtol=0.0):
     return err
 
 
-@pytest.mark.parametrize("case", GOLD["cases"], ids=lambda c: f"D{c['in_features']}-n{c['n']}-B{c['B']}")
+@pytest.mark.parametrize("case", [c for c in GOLD["cases"] if c["B"] <= 4],      # the 64-bag batch: tests/test_zzz_batch64_gpu.py
+                         ids=lambda c: f"D{c['in_features']}-n{c['n']}-B{c['B']}")
 @pytest.mark.parametrize("engine", ["default", "simt"])
 def test_logits_match_golden(T, case, engine):
     """Logits within 1e-3 and Y_prob within 1e-4 of the fp32 reference (BASELINE north_star)."""

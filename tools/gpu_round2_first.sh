@@ -6,7 +6,7 @@
 set -x
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_zzz_mdmil_gpu.py tests/test_zzz_h5_ingest_gpu.py tests/test_zzz_stem768_backward_gpu.py \
-    tests/test_zzz_gradcam_hooks_gpu.py tests/test_zzz_sharp_softmax_gpu.py -s -m gpu -q > gpurun_out/pytest_new.log 2>&1; echo "new tests exit $?" | tee -a gpurun_out/pytest_new.log
+    tests/test_zzz_gradcam_hooks_gpu.py tests/test_zzz_sharp_softmax_gpu.py tests/test_zzz_batch64_gpu.py -s -m gpu -q > gpurun_out/pytest_new.log 2>&1; echo "new tests exit $?" | tee -a gpurun_out/pytest_new.log
 tail -15 gpurun_out/pytest_new.log
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_gpu.log
 tail -4 gpurun_out/pytest_gpu.log
