@@ -317,6 +317,10 @@ int64_t tm_attn_rows_scratch_floats(int64_t B, int64_t Sp, int64_t n_rows);
 /* dst[i] = half(src[i]) (round to nearest, saturating): fp16 operand copies of the GEMM weights. */
 int tm_cvt_f16(const float* src, void* dst, int64_t n, void* stream);
 
+/* dst[i] = float(src[i]) for IEEE fp16 src (exact): the backward reads the tensor-core forward's fp16 stages (q, k, v, xn, merged)
+ * through its fp32 contraction entry points. */
+int tm_cvt_f32(const void* src, float* dst, int64_t n, void* stream);
+
 /* dst[i] = tf32-rounded (round to nearest, ties away: cvt.rna.tf32.f32) src[i]; dst may alias src. */
 int tm_round_tf32(const float* src, float* dst, int64_t n, void* stream);
 
@@ -337,6 +341,19 @@ int tm_gemm_nt(const float* A, const float* W, float* C, int64_t M, int64_t N, i
 int tm_bgemm(const float* A, const float* B, float* C, const float* L, int64_t M, int64_t N, int64_t K, int64_t sam, int64_t sak,
              int64_t sbk, int64_t sbn, int64_t ldc, int64_t ldl, int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC,
              int64_t strideL, float alpha, float beta, void* stream);
+/* tm_bgemm with caller-owned scratch.  On sm_100 the product runs on the tensor cores (csrc/bgemm_tc.cu: tcgen05.mma kind::tf32,
+ * fp32 accumulation in TMEM; operand tiles of any transposition are brought to the K-major shared-memory layout by cp.async
+ * loader warps).  Weight gradients (small M x N, K = every token of the batch) are split along K into fp32 partials that a
+ * second kernel sums in a fixed order; `scratch` holds tm_bgemm_scratch_floats(M, N, K, batch) floats for them (0 = this
+ * shape is not split; a NULL / short scratch disables the split). */
+int64_t tm_bgemm_scratch_floats(int64_t M, int64_t N, int64_t K, int64_t batch);
+int tm_bgemm_ex(const float* A, const float* B, float* C, const float* L, int64_t M, int64_t N, int64_t K, int64_t sam, int64_t sak,
+                int64_t sbk, int64_t sbn, int64_t ldc, int64_t ldl, int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC,
+                int64_t strideL, float alpha, float beta, float* scratch, int64_t scratch_floats, void* stream);
+/* Engine of tm_bgemm / tm_bgemm_ex and of the products inside tm_pinv_bwd: 0 = tcgen05, tf32 operands (default on sm_100),
+ * 1 = fp32 CUDA-core kernel (the on-device cross-check of the former).  Returns the previous value; any other argument only
+ * queries.  TM_BGEMM=simt in the environment selects 1 at load time. */
+int tm_bgemm_engine(int engine);
 /* In-place row softmax (attn1 / attn3 are recomputed by the backward, not kept by the forward). */
 int tm_softmax_rows(float* X, int64_t rows, int64_t len, void* stream);
 /* dP <- P * (dP - sum(dP * P, -1)): backward of P = softmax(S, -1), in place on dP. */

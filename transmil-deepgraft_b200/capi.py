@@ -66,6 +66,7 @@ SIGNATURES = {
     "tm_fc1_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
     "tm_ln_pad_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _fp, _u32, _fp]),
     "tm_cvt_f16": (C.c_int, [_fp, _fp, _i64, _fp]),
+    "tm_cvt_f32": (C.c_int, [_fp, _fp, _i64, _fp]),
     "tm_round_tf32": (C.c_int, [_fp, _fp, _i64, _fp]),
     "tm_qkv_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp, _fp, _fp, _u32, _fp]),
     "tm_landmarks_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _fp, _fp, _fp]),
@@ -105,6 +106,9 @@ SIGNATURES = {
 _f32, _u64 = C.c_float, C.c_uint64
 BWD_SIGNATURES = {
     "tm_bgemm": (C.c_int, [_fp, _fp, _fp, _fp] + [_i64] * 14 + [_f32, _f32, _fp]),
+    "tm_bgemm_ex": (C.c_int, [_fp, _fp, _fp, _fp] + [_i64] * 14 + [_f32, _f32, _fp, _i64, _fp]),
+    "tm_bgemm_scratch_floats": (_i64, [_i64, _i64, _i64, _i64]),
+    "tm_bgemm_engine": (C.c_int, [C.c_int]),
     "tm_softmax_rows": (C.c_int, [_fp, _i64, _i64, _fp]),
     "tm_softmax_rows_bwd": (C.c_int, [_fp, _fp, _i64, _i64, _fp]),
     "tm_ln_rows_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp]),

@@ -125,9 +125,28 @@ __global__ void __launch_bounds__(BT) bgemm_kernel(const BGemm p) {
   }
 }
 
-static int bgemm(const BGemm& p, int batch, cudaStream_t st) {
+#ifndef TM_HOST_EMU
+// tcgen05 engine of the same contract (bgemm_tc.cu): tf32 operands, fp32 accumulate
+i64 bgemm_tc_scratch_floats(i64 M, i64 N, i64 K, i64 batch);
+int bgemm_tc(const float* A, const float* B, float* C, const float* L, i64 M, i64 N, i64 K, i64 sam, i64 sak, i64 sbk, i64 sbn, i64 ldc,
+             i64 ldl, i64 batch, i64 strA, i64 strB, i64 strC, i64 strL, float alpha, float beta, float diag, float* scratch,
+             i64 scratch_floats, cudaStream_t st);
+// 0 = tensor cores when the device has them (default), 1 = fp32 CUDA-core kernel (the on-device cross-check); TM_BGEMM=simt
+// in the environment sets the initial value.
+static int g_bgemm_engine = [] { const char* e = getenv("TM_BGEMM"); return (e && strcmp(e, "simt") == 0) ? 1 : 0; }();
+static bool bgemm_use_tc() { return g_bgemm_engine == 0 && tc_available(); }
+#endif
+
+static int bgemm(const BGemm& p, int batch, cudaStream_t st, float* scratch = nullptr, i64 scratch_floats = 0) {
   TM_CHECK_ARG(p.M > 0 && p.N > 0 && p.K > 0 && batch > 0, TM_ERR_BAD_SHAPE, "tm_bgemm: empty problem %dx%dx%d x%d", p.M, p.N, p.K, batch);
   TM_CHECK_ARG(p.A && p.B && p.C, TM_ERR_BAD_ARGUMENT, "tm_bgemm: NULL operand");
+#ifndef TM_HOST_EMU
+  if (bgemm_use_tc())
+    return bgemm_tc(p.A, p.B, p.C, p.L, p.M, p.N, p.K, p.sam, p.sak, p.sbk, p.sbn, p.ldc, p.ldl, batch, p.strA, p.strB, p.strC, p.strL,
+                    p.alpha, p.beta, p.diag, scratch, scratch_floats, st);
+#else
+  (void)scratch; (void)scratch_floats;
+#endif
   dim3 grid((unsigned)ceil_div(p.M, GT), (unsigned)ceil_div(p.N, GT), (unsigned)batch);
   TM_CHECK_ARG(grid.y <= 65535u && grid.z <= 65535u, TM_ERR_BAD_SHAPE, "tm_bgemm: grid too large (N=%d batch=%d)", p.N, batch);
   BW_LAUNCH(bgemm_kernel, grid, dim3(BT), st, p);
@@ -609,6 +628,41 @@ int tm_bgemm(const float* A, const float* B, float* C, const float* L, int64_t M
   p.strA = strideA; p.strB = strideB; p.strC = strideC; p.strL = strideL;
   p.alpha = alpha; p.beta = beta; p.diag = 0.f;
   return bgemm(p, (int)batch, (cudaStream_t)stream);
+}
+
+/* tm_bgemm with caller-owned scratch for split-K (weight gradients: small M x N, K = every token of the batch):
+ * scratch holds tm_bgemm_scratch_floats(M, N, K, batch) floats (0 = this shape is not split). */
+int64_t tm_bgemm_scratch_floats(int64_t M, int64_t N, int64_t K, int64_t batch) {
+#ifndef TM_HOST_EMU
+  if (bgemm_use_tc() && M > 0 && N > 0 && K > 0 && batch > 0) return bgemm_tc_scratch_floats(M, N, K, batch);
+#endif
+  (void)M; (void)N; (void)K; (void)batch;
+  return 0;
+}
+int tm_bgemm_ex(const float* A, const float* B, float* C, const float* L, int64_t M, int64_t N, int64_t K, int64_t sam, int64_t sak,
+                int64_t sbk, int64_t sbn, int64_t ldc, int64_t ldl, int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC,
+                int64_t strideL, float alpha, float beta, float* scratch, int64_t scratch_floats, void* stream) {
+  TM_CHECK_ARG(M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_bgemm: dimension too large");
+  BGemm p;
+  memset(&p, 0, sizeof(p));
+  p.A = A; p.B = B; p.C = C; p.L = L;
+  p.M = (int)M; p.N = (int)N; p.K = (int)K;
+  p.sam = sam; p.sak = sak; p.sbk = sbk; p.sbn = sbn; p.ldc = ldc; p.ldl = ldl;
+  p.strA = strideA; p.strB = strideB; p.strC = strideC; p.strL = strideL;
+  p.alpha = alpha; p.beta = beta; p.diag = 0.f;
+  return bgemm(p, (int)batch, (cudaStream_t)stream, scratch, scratch_floats);
+}
+/* Engine of tm_bgemm / tm_bgemm_ex / tm_pinv_bwd's products: 0 = tcgen05 (tf32 operands; default on sm_100), 1 = fp32 CUDA cores.
+ * Returns the previous value. */
+int tm_bgemm_engine(int engine) {
+#ifndef TM_HOST_EMU
+  const int prev = g_bgemm_engine;
+  if (engine == 0 || engine == 1) g_bgemm_engine = engine;
+  return prev;
+#else
+  (void)engine;
+  return 1;
+#endif
 }
 
 int tm_softmax_rows(float* X, int64_t rows, int64_t len, void* stream) {

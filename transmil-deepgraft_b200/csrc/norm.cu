@@ -122,6 +122,14 @@ __global__ void __launch_bounds__(256) cvt_f16_kernel(const float* __restrict__ 
   }
 }
 
+__global__ void __launch_bounds__(256) cvt_f32_kernel(const __half* __restrict__ src, float* __restrict__ dst, long long n4) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    const uint2 u = reinterpret_cast<const uint2*>(src)[i];
+    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+    reinterpret_cast<float4*>(dst)[i] = make_float4(a.x, a.y, b.x, b.y);
+  }
+}
+
 // One launch for every per-forward operand copy of the parameters: tf32-rounded / fp16 copies of the GEMM weights and the
 // packed PPEG filter (effective 7x7 + bias, see ppeg.cu).  Block b serves job j with first_block[j] <= b < first_block[j+1];
 // the blocks after the last job pack the PPEG filter.
@@ -247,6 +255,17 @@ extern "C" int tm_cvt_f16(const float* src, void* dst, int64_t n, void* stream) 
   long long blocks = tmil::ceil_div(n / 4, 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
   tmil::cvt_f16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__half*)dst, n / 4);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+extern "C" int tm_cvt_f32(const void* src, float* dst, int64_t n, void* stream) {
+  TM_CHECK_ARG(src && dst && n >= 0 && n % 4 == 0 && tmil::aligned16(dst) && (reinterpret_cast<uintptr_t>(src) & 7u) == 0, TM_ERR_BAD_ALIGNMENT,
+               "tm_cvt_f32: n must be a multiple of 4, dst 16-byte and src 8-byte aligned");
+  if (n == 0) return TM_OK;
+  long long blocks = tmil::ceil_div(n / 4, 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  tmil::cvt_f32_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __half*)src, dst, n / 4);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

@@ -6,7 +6,9 @@ libtransmil_b200 (include/transmil_b200.h) with the intermediates the backward n
 contractions written out in oracle/transmil_backward.py, executed by the `tm_*_bwd` / `tm_bgemm` kernels of
 csrc/backward.cu.  `TransMILFunction` ties both into autograd so `loss.backward()` / optimizers / DDP see ordinary `.grad`s.
 
-This is the first correct backward (fp32 CUDA-core kernels); tensor-core (tcgen05) backward contractions are the next step.
+The contractions of the backward run on the tensor cores (csrc/bgemm_tc.cu: tcgen05, tf32 operands, fp32 accumulate; every
+transposition form) and the forward of a training step is the tcgen05 engine of the inference path with its stages kept; the
+fp32 CUDA-core engine of both stays selectable as the on-device cross-check (tm_bgemm_engine, FORWARD_ENGINE).
 There is no CPU or PyTorch fallback: every arithmetic step is a library call.  (`Kernels(lib=...)` lets the CPU tests inject
 the host build of the SAME kernel source, tests/cuda_emu -- test infrastructure, never loaded here.)
 """
@@ -48,9 +50,12 @@ class Kernels:
     def gemm(self, A, a_str, B, b_str, C_, M, N, K, ldc, batch=1, strides=(0, 0, 0), alpha=1.0, beta=0.0, L=None, ldl=None,
              strideL=None):
         """C[z][m,n] = alpha * sum_k A[z][m*sam + k*sak] * B[z][k*sbk + n*sbn] + beta * L[z][m*ldl + n]."""
-        self.check(self.L.tm_bgemm(A.data_ptr(), B.data_ptr(), C_.data_ptr(), L.data_ptr() if L is not None else None, M, N, K,
-                                   a_str[0], a_str[1], b_str[0], b_str[1], ldc, ldc if ldl is None else ldl, batch, strides[0],
-                                   strides[1], strides[2], strides[2] if strideL is None else strideL, alpha, beta, self.st))
+        nsc = int(self.L.tm_bgemm_scratch_floats(M, N, K, batch))    # split-K partials of the tensor-core engine (0 = none)
+        sc = self.new(A, nsc) if nsc else None
+        self.check(self.L.tm_bgemm_ex(A.data_ptr(), B.data_ptr(), C_.data_ptr(), L.data_ptr() if L is not None else None, M, N, K,
+                                      a_str[0], a_str[1], b_str[0], b_str[1], ldc, ldc if ldl is None else ldl, batch, strides[0],
+                                      strides[1], strides[2], strides[2] if strideL is None else strideL, alpha, beta,
+                                      sc.data_ptr() if nsc else None, nsc, self.st))
         return C_
 
     def colsum(self, X, rows, cols, ld, out=None):
@@ -240,8 +245,107 @@ def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0), drop=0.0, keep_dxn=
     return g
 
 
-# ---- forward with kept stages (GPU: fp32 per-kernel entry points of the library) ------------------------------------------------
+# ---- forward with kept stages ---------------------------------------------------------------------------------------------------
+# "tc": the tcgen05 engine of the inference path (tf32 fc1, fp16 q/k/v/xn/merged, fp16 pinv chain) with every stage kept;
+# "simt": the fp32 CUDA-core engine (the on-device cross-check).  tests/test_zz_backward_gpu.py runs both.
+FORWARD_ENGINE = "tc"
+
+
 def forward_keep(model, x, training, seeds):
+    if FORWARD_ENGINE == "tc" and capi.lib().tm_device_supported() == 1 and not (int(model.flags) & capi.TM_FLAG_SIMT_ONLY):
+        return forward_keep_tc(model, x, training, seeds)
+    return forward_keep_simt(model, x, training, seeds)
+
+
+def forward_keep_tc(model, x, training, seeds):
+    """TransMIL.forward (TransMIL.py:167-211) through the per-kernel TENSOR-CORE entry points (the kernels tm_transmil_fwd
+    strings together for inference), every stage the backward reads kept in its own tensor.  The fp16 stages (q, k, v, xn,
+    merged) are handed to the backward as exact fp32 copies (tm_cvt_f32): the gradient is taken at the values the forward
+    actually used.  Training mode applies the to_out Dropout(0.7) with the library's counter-based mask (seed per layer)."""
+    L = capi.lib()
+    dev = x.device
+    st = torch.cuda.current_stream(dev).cuda_stream
+    ck = capi.check
+    w = model._weights()
+    B, n, D = x.shape
+    plan = capi.make_plan(n).as_dict()
+    S, Sp, P, l, G = plan["S"], plan["Sp"], plan["P"], plan["l"], plan["G"]
+    f32 = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+    f16 = lambda *s: torch.empty(s, dtype=torch.float16, device=dev)
+    flags = capi.TM_FLAG_TF32_OPERANDS | capi.TM_FLAG_F16_ACT
+    keep = []   # operand copies of the GEMM weights must outlive the launches that read them
+
+    def tf32_copy(t):
+        o = torch.empty_like(t)
+        ck(L.tm_round_tf32(t.data_ptr(), o.data_ptr(), t.numel(), st))
+        keep.append(o)
+        return o.data_ptr()
+
+    def f16_copy(t):
+        o = torch.empty(t.shape, dtype=torch.float16, device=dev)
+        ck(L.tm_cvt_f16(t.data_ptr(), o.data_ptr(), t.numel(), st))
+        keep.append(o)
+        return o.data_ptr()
+
+    def up(t):
+        o = torch.empty(t.shape, dtype=torch.float32, device=dev)
+        ck(L.tm_cvt_f32(t.data_ptr(), o.data_ptr(), t.numel(), st))
+        return o
+
+    f = model._fc1
+    wt = capi.Weights.from_buffer_copy(w)
+    wt.fc1_w0 = tf32_copy(f[0].weight)
+    F0 = {capi.TM_FC1_SINGLE: 0, capi.TM_FC1_2048: 1024, capi.TM_FC1_768: 768}[model._fc1_kind]
+    if model._fc1_kind == capi.TM_FC1_2048:
+        wt.fc1_w1 = tf32_copy(f[3].weight)
+    elif model._fc1_kind == capi.TM_FC1_768:
+        wt.fc1_w1 = tf32_copy(f[4].weight)
+    h0 = f32(B, S, DIM)
+    scratch = f32(max(1, B * n * F0))
+    ck(L.tm_fc1_fwd(C.byref(wt), x.data_ptr(), B, n, h0.data_ptr(), scratch.data_ptr(), flags, st))
+    del scratch
+    saved = {"plan": plan, "h0": h0}
+
+    def layer(name, lw, mod, h_in, seed):
+        qkv16, out16 = f16_copy(mod.attn.to_qkv.weight), f16_copy(mod.attn.to_out[0].weight)
+        xn = f16(B, Sp, DIM)
+        ck(L.tm_ln_pad_fwd(h_in.data_ptr(), lw.norm_w, lw.norm_b, B, S, P, xn.data_ptr(), flags, st))
+        q, k, v = f16(B, H, Sp, DH), f16(B, H, Sp, DH), f16(B, H, Sp, DH)
+        ck(L.tm_qkv16_fwd(xn.data_ptr(), qkv16, B, Sp, q.data_ptr(), k.data_ptr(), v.data_ptr(), flags, st))
+        q_lm, k_lm, qlm16, klm16 = f32(B, H, LM, DH), f32(B, H, LM, DH), f16(B, H, LM, DH), f16(B, H, LM, DH)
+        ck(L.tm_landmarks16_fwd(q.data_ptr(), k.data_ptr(), B, Sp, l, q_lm.data_ptr(), k_lm.data_ptr(), qlm16.data_ptr(),
+                                klm16.data_ptr(), st))
+        attn2, Z = f32(B, H, LM, LM), f32(B, H, LM, LM)
+        sc = f32(int(L.tm_pinv_scratch_floats(B)))
+        ck(L.tm_pinv_fwd(q_lm.data_ptr(), k_lm.data_ptr(), B, attn2.data_ptr(), Z.data_ptr(), sc.data_ptr(), flags, st))
+        W3 = f32(B, H, LM, DH)
+        sc = f32(int(L.tm_attn3v_tc_scratch_floats(B, Sp)))
+        ck(L.tm_attn3v_tc_fwd(qlm16.data_ptr(), k.data_ptr(), v.data_ptr(), B, Sp, W3.data_ptr(), sc.data_ptr(), flags, st))
+        M, mt16 = f32(B, H, LM, DH), f16(B, H, DH, LM)
+        ck(L.tm_zw16_fwd(Z.data_ptr(), W3.data_ptr(), B, M.data_ptr(), mt16.data_ptr(), st))
+        merged = f16(B, Sp, DIM)
+        ck(L.tm_nystrom_out_tc_fwd(q.data_ptr(), klm16.data_ptr(), mt16.data_ptr(), v.data_ptr(), lw.conv_w, B, Sp,
+                                   merged.data_ptr(), flags, st))
+        h_out = f32(B, S, DIM)
+        ck(L.tm_to_out_residual_fwd(merged.data_ptr(), out16, lw.out_b, h_in.data_ptr(), B, S, P, h_out.data_ptr(), flags, st))
+        if training:
+            ck(L.tm_dropout_resid_fwd(h_out.data_ptr(), h_in.data_ptr(), B * S * DIM, seed, TO_OUT_DROPOUT, st))
+        saved[name] = dict(xn=up(xn), q=up(q), k=up(k), v=up(v), q_lm=q_lm, k_lm=k_lm, attn2=attn2, Z=Z, W3=W3, M=M, merged=up(merged))
+        return h_out
+
+    h1 = layer("layer1", w.layer1, model.layer1, h0, seeds[0])
+    h2 = f32(B, S, DIM)
+    packed = f32(DIM * 50)
+    ck(L.tm_ppeg_fwd(C.byref(w), h1.data_ptr(), B, G, h2.data_ptr(), packed.data_ptr(), st))
+    h3 = layer("layer2", w.layer2, model.layer2, h2, seeds[1])
+    logits = f32(B, model.n_classes)
+    ck(L.tm_head_fwd(C.byref(w), h3.data_ptr(), B, S, logits.data_ptr(), st))
+    saved.update(h1=h1, h2=h2, h3=h3)
+    del keep
+    return logits, saved, w
+
+
+def forward_keep_simt(model, x, training, seeds):
     """TransMIL.forward (TransMIL.py:167-211) through the per-kernel fp32 entry points, keeping what the backward reads.
     Training mode applies the to_out Dropout(0.7) with the library's counter-based mask (seed per layer)."""
     L = capi.lib()
