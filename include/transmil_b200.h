@@ -350,9 +350,10 @@ int64_t tm_bgemm_scratch_floats(int64_t M, int64_t N, int64_t K, int64_t batch);
 int tm_bgemm_ex(const float* A, const float* B, float* C, const float* L, int64_t M, int64_t N, int64_t K, int64_t sam, int64_t sak,
                 int64_t sbk, int64_t sbn, int64_t ldc, int64_t ldl, int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC,
                 int64_t strideL, float alpha, float beta, float* scratch, int64_t scratch_floats, void* stream);
-/* Engine of tm_bgemm / tm_bgemm_ex and of the products inside tm_pinv_bwd: 0 = tcgen05, tf32 operands (default on sm_100),
- * 1 = fp32 CUDA-core kernel (the on-device cross-check of the former).  Returns the previous value; any other argument only
- * queries.  TM_BGEMM=simt in the environment selects 1 at load time. */
+/* Engine of tm_bgemm / tm_bgemm_ex and of the products inside tm_pinv_bwd: 0 = tcgen05, tf32 operands (default on sm_100;
+ * operand tiles by TMA when base and pitches are 16-byte aligned, else by cp.async loader warps), 1 = fp32 CUDA-core kernel
+ * (the on-device cross-check of the former), 2 = tcgen05 fed by the loader warps only (cross-check of the TMA feed).
+ * Returns the previous value; any other argument only queries.  TM_BGEMM=simt in the environment selects 1 at load time. */
 int tm_bgemm_engine(int engine);
 /* In-place row softmax (attn1 / attn3 are recomputed by the backward, not kept by the forward). */
 int tm_softmax_rows(float* X, int64_t rows, int64_t len, void* stream);
@@ -385,8 +386,11 @@ int tm_split_heads(const float* merged, int64_t B, int64_t Sp, float* out, void*
  * ('... (n l) d -> ... n d' sum / l), of q *= 64^-0.5 and of the head split, in one pass. */
 int tm_qkv_grad_merge(const float* dq, const float* dk, const float* dv, const float* dq_lm, const float* dk_lm, int64_t B, int64_t Sp,
                       int64_t l, float* dqkv, void* stream);
-/* res_conv backward: dO, v [B,8,Sp,64] -> dv [B,8,Sp,64], g_w [8,1,33,1]. */
-int tm_conv33_bwd(const float* dO, const float* v, const float* conv_w, int64_t B, int64_t Sp, float* dv, float* g_w, void* stream);
+/* res_conv backward: dO, v [B,8,Sp,64] -> dv [B,8,Sp,64], g_w [8,1,33,1].  scratch: tm_conv33_bwd_scratch_floats(B, Sp) floats
+ * (per-block tap sums, added in a fixed order by a second kernel). */
+int64_t tm_conv33_bwd_scratch_floats(int64_t B, int64_t Sp);
+int tm_conv33_bwd(const float* dO, const float* v, const float* conv_w, int64_t B, int64_t Sp, float* dv, float* g_w, float* scratch,
+                  void* stream);
 /* moore_penrose_iter_pinv backward (6 iterations, init scalar = global max row sum x max column sum over every bag and
  * head): A = attn2 [nb,256,256] with nb = B*8, dZ = gradient of Z (clobbered) -> dA.  The iterates are recomputed. */
 int64_t tm_pinv_bwd_scratch_floats(int64_t nb);

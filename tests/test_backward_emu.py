@@ -179,7 +179,7 @@ def test_conv33_backward(K):
     ww = w.double().requires_grad_(True)
     F.conv2d(vv, ww, None, padding=(16, 0), groups=8).backward(dO.double())
     dv, gw = torch.empty_like(v), torch.empty_like(w)
-    K.check(K.L.tm_conv33_bwd(dO.data_ptr(), v.data_ptr(), w.data_ptr(), B, Sp, dv.data_ptr(), gw.data_ptr(), None))
+    K.check(K.L.tm_conv33_bwd(dO.data_ptr(), v.data_ptr(), w.data_ptr(), B, Sp, dv.data_ptr(), gw.data_ptr(), None, None))
     _close(dv, vv.grad, 1e-5, "conv dv")
     _close(gw, ww.grad, 1e-4, "conv dw")
 

@@ -39,13 +39,15 @@ def _run(L, T, A, a_str, B, b_str, C, M, N, K, batch, strides, alpha=1.0, beta=0
 
 
 FORMS = [(False, False), (False, True), (True, False), (True, True)]   # (A stored [K,M], B stored [N,K])
+FEEDS = {"tma": 0, "cpasync": 2}                                        # tm_bgemm_engine codes of the two operand feeds
 
 
+@pytest.mark.parametrize("feed", ["tma", "cpasync"])
 @pytest.mark.parametrize("tA,tB", FORMS)
 @pytest.mark.parametrize("M,N,K,batch", [(128, 64, 32, 1), (256, 256, 256, 8), (1280, 64, 256, 3), (256, 64, 1280, 4),
                                          (130, 100, 68, 2), (77, 300, 1000, 1), (512, 512, 8192, 1), (1536, 512, 4096, 1),
                                          (1000, 512, 1024, 1), (256, 1280, 64, 5)])
-def test_bgemm_tc_all_forms(built_lib, tA, tB, M, N, K, batch):
+def test_bgemm_tc_all_forms(built_lib, tA, tB, M, N, K, batch, feed):
     import transmil_b200 as T
     L = T.capi.lib()
     g = torch.Generator().manual_seed(M + 3 * N + 5 * K + batch + (2 if tA else 0) + (1 if tB else 0))
@@ -58,7 +60,7 @@ def test_bgemm_tc_all_forms(built_lib, tA, tB, M, N, K, batch):
     scale = ref.abs().max().item()
     C_tc = torch.full((batch, M, N), float("nan"), device="cuda")
     C_simt = torch.empty((batch, M, N), device="cuda")
-    _run(L, T, A_st, a_str, B_st, b_str, C_tc, M, N, K, batch, (sA, sB))
+    _run(L, T, A_st, a_str, B_st, b_str, C_tc, M, N, K, batch, (sA, sB), engine=FEEDS[feed])
     _run(L, T, A_st, a_str, B_st, b_str, C_simt, M, N, K, batch, (sA, sB), engine=1)
     assert torch.isfinite(C_tc).all()
     e_simt = (C_simt.cpu().double() - ref).abs().max().item() / scale
@@ -123,7 +125,7 @@ def test_pinv_bwd_engines_agree(built_lib):
     dZ0 = (torch.randn(nb, 256, 256, generator=g) * 1e-3).cuda()
     st = torch.cuda.current_stream().cuda_stream
     outs = []
-    for engine in (1, 0):
+    for engine in (1, 0, 2):
         prev = L.tm_bgemm_engine(engine)
         dZ = dZ0.clone()
         dA = torch.empty_like(A2)
@@ -132,6 +134,8 @@ def test_pinv_bwd_engines_agree(built_lib):
         torch.cuda.synchronize()
         L.tm_bgemm_engine(prev)
         outs.append(dA)
-    rel = (outs[0] - outs[1]).abs().max().item() / outs[0].abs().max().item()
-    assert torch.isfinite(outs[1]).all()
-    assert rel < 5e-3, f"pinv backward, tf32 tensor cores vs fp32: {rel:.3e}"
+    for o in outs[1:]:
+        rel = (outs[0] - o).abs().max().item() / outs[0].abs().max().item()
+        assert torch.isfinite(o).all()
+        assert rel < 5e-3, f"pinv backward, tf32 tensor cores vs fp32: {rel:.3e}"
+    assert torch.equal(outs[1], outs[2]), "TMA feed and loader-warp feed must give the same bits (same operands, same order)"

@@ -44,7 +44,7 @@ def test_hook_on_layer2_norm_sees_activation_and_gradient(built_lib):
     out = F.linear(F.layer_norm(h3, (512,), sd64["norm.weight"], sd64["norm.bias"], 1e-5)[:, 0], sd64["_fc.weight"], sd64["_fc.bias"])
     (out * dlogits.double()).sum().backward()
     assert seen["act"].shape == (B, O.plan(n)["S"], 512) and seen["act"].is_cuda
-    _close(seen["act"], xn, 1e-4, "hooked activation")
+    _close(seen["act"], xn, 1e-3, "hooked activation")   # the tensor-core forward keeps LayerNorm's output as fp16 (11-bit mantissa)
     _close(seen["grad"], xn.grad, 5e-3, "gradient of the hooked activation")
     ref, _ = OB.backward(sd, x, dlogits.double())
     for k, p in m.named_parameters():

@@ -9,11 +9,12 @@ Layout (only what the path needs):
   h5bag.py      reader of the reference's HDF5 feature-bag files (features / coords) into pinned host memory, no h5py
   bagdp.py      whole bags placed on ranks longest-first (variable-length bags), one logits gather
   ingest.py     slide-at-a-time inference loop with the next bag's H2D copy hidden behind the current forward
+  training.py   forward with kept stages + the library's backward behind torch.autograd (training_step)
   build.py      nvcc build of the shared library
 """
-from . import bagdp, capi, h5bag
+from . import bagdp, capi, h5bag, training
 from .bagdp import BagParallelInference
 from .ingest import StreamedInference
 from .transmil import MDMIL, LazyAttention, NystromAttention, PPEG, TransLayer, TransMIL, y_prob_y_hat
 
-__all__ = ["capi", "h5bag", "bagdp", "BagParallelInference", "TransMIL", "MDMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]
+__all__ = ["capi", "h5bag", "bagdp", "training", "BagParallelInference", "TransMIL", "MDMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]

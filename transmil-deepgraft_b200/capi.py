@@ -122,7 +122,8 @@ BWD_SIGNATURES = {
     "tm_pad_front_bwd": (C.c_int, [_fp, _i64, _i64, _i64, _i64, _u64, _f32, _fp, _fp]),
     "tm_split_heads": (C.c_int, [_fp, _i64, _i64, _fp, _fp]),
     "tm_qkv_grad_merge": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _i64, _fp, _fp]),
-    "tm_conv33_bwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _fp]),
+    "tm_conv33_bwd_scratch_floats": (_i64, [_i64, _i64]),
+    "tm_conv33_bwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _fp, _fp]),
     "tm_pinv_bwd_scratch_floats": (_i64, [_i64]),
     "tm_pinv_bwd": (C.c_int, [_fp, _fp, _i64, _fp, _fp, _fp]),
     "tm_ppeg_bwd_scratch_floats": (_i64, [_i64, _i64]),

@@ -71,6 +71,7 @@ struct BGemm {
   i64 sam, sak, sbk, sbn, ldc, ldl;
   i64 strA, strB, strC, strL;
   float alpha, beta, diag;
+  float* C2; float alpha2, diag2;   // optional second output from the same product: C2 = alpha2 * op(A) op(B) + diag2 * I (ldc / strC of C)
 };
 constexpr int GT = 64, GK = 16;
 
@@ -111,6 +112,7 @@ __global__ void __launch_bounds__(BT) bgemm_kernel(const BGemm p) {
   }
   const float* L = p.L != nullptr ? p.L + z * p.strL : nullptr;
   float* C = p.C + z * p.strC;
+  float* C2 = p.C2 != nullptr ? p.C2 + z * p.strC : nullptr;
   for (int i = 0; i < 4; ++i) {
     const int r = m0 + ty * 4 + i;
     if (r >= p.M) continue;
@@ -121,6 +123,7 @@ __global__ void __launch_bounds__(BT) bgemm_kernel(const BGemm p) {
       if (L != nullptr) o = fmaf(p.beta, L[(i64)r * p.ldl + c], o);
       if (r == c) o += p.diag;
       C[(i64)r * p.ldc + c] = o;
+      if (C2 != nullptr) C2[(i64)r * p.ldc + c] = p.alpha2 * acc[i][j] + (r == c ? p.diag2 : 0.f);
     }
   }
 }
@@ -129,12 +132,20 @@ __global__ void __launch_bounds__(BT) bgemm_kernel(const BGemm p) {
 // tcgen05 engine of the same contract (bgemm_tc.cu): tf32 operands, fp32 accumulate
 i64 bgemm_tc_scratch_floats(i64 M, i64 N, i64 K, i64 batch);
 int bgemm_tc(const float* A, const float* B, float* C, const float* L, i64 M, i64 N, i64 K, i64 sam, i64 sak, i64 sbk, i64 sbn, i64 ldc,
-             i64 ldl, i64 batch, i64 strA, i64 strB, i64 strC, i64 strL, float alpha, float beta, float diag, float* scratch,
-             i64 scratch_floats, cudaStream_t st);
+             i64 ldl, i64 batch, i64 strA, i64 strB, i64 strC, i64 strL, float alpha, float beta, float diag, float* C2, float alpha2,
+             float diag2, float* scratch, i64 scratch_floats, cudaStream_t st);
 // 0 = tensor cores when the device has them (default), 1 = fp32 CUDA-core kernel (the on-device cross-check); TM_BGEMM=simt
 // in the environment sets the initial value.
 static int g_bgemm_engine = [] { const char* e = getenv("TM_BGEMM"); return (e && strcmp(e, "simt") == 0) ? 1 : 0; }();
-static bool bgemm_use_tc() { return g_bgemm_engine == 0 && tc_available(); }
+extern int g_bgemm_force_cpasync;
+// device-tuned versions of the HBM-bound kernels (backward_fast.cu); the plain ones below stay the cross-check (engine 1)
+i64 conv33_bwd_fast_scratch_floats(i64 B, i64 Sp);
+int conv33_bwd_fast(const float* dO, const float* v, const float* conv_w, i64 B, i64 Sp, float* dv, float* g_w, float* scratch, cudaStream_t st);
+bool softmax_rows_fast_ok(const void* a, const void* b, i64 len);
+int softmax_rows_fast(float* X, i64 rows, i64 len, cudaStream_t st);
+int softmax_rows_bwd_fast(const float* P, float* dP, i64 rows, i64 len, cudaStream_t st);
+int ppeg_wgrad_fast(const float* h_in, const float* dy, i64 B, i64 G, float* partial, float* gsum, cudaStream_t st);
+static bool bgemm_use_tc() { return g_bgemm_engine != 1 && tc_available(); }
 #endif
 
 static int bgemm(const BGemm& p, int batch, cudaStream_t st, float* scratch = nullptr, i64 scratch_floats = 0) {
@@ -143,7 +154,7 @@ static int bgemm(const BGemm& p, int batch, cudaStream_t st, float* scratch = nu
 #ifndef TM_HOST_EMU
   if (bgemm_use_tc())
     return bgemm_tc(p.A, p.B, p.C, p.L, p.M, p.N, p.K, p.sam, p.sak, p.sbk, p.sbn, p.ldc, p.ldl, batch, p.strA, p.strB, p.strC, p.strL,
-                    p.alpha, p.beta, p.diag, scratch, scratch_floats, st);
+                    p.alpha, p.beta, p.diag, p.C2, p.alpha2, p.diag2, scratch, scratch_floats, st);
 #else
   (void)scratch; (void)scratch_floats;
 #endif
@@ -593,10 +604,11 @@ static int opt_batch(const tm_opt_tensor* ts, int64_t count, OptBatch* b, unsign
 
 // one product of the pinv chain: C = alpha * op(A) op(B) + beta * L + diag * I on nb 256x256 matrices
 static int mm256(const float* A, bool tA, const float* B, bool tB, float* C, float alpha, float beta, const float* L, float diag,
-                 int nb, cudaStream_t st) {
+                 int nb, cudaStream_t st, float* C2 = nullptr, float alpha2 = 0.f, float diag2 = 0.f) {
   BGemm p;
   memset(&p, 0, sizeof(p));
   p.A = A; p.B = B; p.C = C; p.L = L;
+  p.C2 = C2; p.alpha2 = alpha2; p.diag2 = diag2;
   p.M = p.N = p.K = LMK;
   p.sam = tA ? 1 : LMK; p.sak = tA ? LMK : 1;
   p.sbk = tB ? 1 : LMK; p.sbn = tB ? LMK : 1;
@@ -652,12 +664,16 @@ int tm_bgemm_ex(const float* A, const float* B, float* C, const float* L, int64_
   p.alpha = alpha; p.beta = beta; p.diag = 0.f;
   return bgemm(p, (int)batch, (cudaStream_t)stream, scratch, scratch_floats);
 }
-/* Engine of tm_bgemm / tm_bgemm_ex / tm_pinv_bwd's products: 0 = tcgen05 (tf32 operands; default on sm_100), 1 = fp32 CUDA cores.
- * Returns the previous value. */
+/* Engine of tm_bgemm / tm_bgemm_ex / tm_pinv_bwd's products: 0 = tcgen05 (tf32 operands; default on sm_100; operands fed by TMA
+ * when they obey the tensor-map rules, by cp.async loader warps otherwise), 1 = fp32 CUDA cores, 2 = tcgen05 with the loader
+ * warps only (cross-check of the TMA feed).  Returns the previous value. */
 int tm_bgemm_engine(int engine) {
 #ifndef TM_HOST_EMU
   const int prev = g_bgemm_engine;
-  if (engine == 0 || engine == 1) g_bgemm_engine = engine;
+  if (engine >= 0 && engine <= 2) {
+    g_bgemm_engine = engine;
+    g_bgemm_force_cpasync = engine == 2;
+  }
   return prev;
 #else
   (void)engine;
@@ -667,11 +683,17 @@ int tm_bgemm_engine(int engine) {
 
 int tm_softmax_rows(float* X, int64_t rows, int64_t len, void* stream) {
   TM_CHECK_ARG(X && rows > 0 && len > 0 && rows < (1ll << 31) && len < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_softmax_rows: bad shape");
+#ifndef TM_HOST_EMU
+  if (g_bgemm_engine != 1 && softmax_rows_fast_ok(X, nullptr, len)) return softmax_rows_fast(X, rows, len, (cudaStream_t)stream);
+#endif
   BW_LAUNCH(softmax_rows_kernel, dim3((unsigned)rows), dim3(BT), (cudaStream_t)stream, X, (int)len);
   return TM_OK;
 }
 int tm_softmax_rows_bwd(const float* P, float* dP, int64_t rows, int64_t len, void* stream) {
   TM_CHECK_ARG(P && dP && rows > 0 && len > 0 && rows < (1ll << 31) && len < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_softmax_rows_bwd: bad shape");
+#ifndef TM_HOST_EMU
+  if (g_bgemm_engine != 1 && softmax_rows_fast_ok(P, dP, len)) return softmax_rows_bwd_fast(P, dP, rows, len, (cudaStream_t)stream);
+#endif
   BW_LAUNCH(softmax_rows_bwd_kernel, dim3((unsigned)rows), dim3(BT), (cudaStream_t)stream, P, dP, (int)len);
   return TM_OK;
 }
@@ -753,10 +775,25 @@ int tm_qkv_grad_merge(const float* dq, const float* dk, const float* dv, const f
   return TM_OK;
 }
 
-/* res_conv backward (Conv2d(8,8,(33,1),groups=8) along the padded token axis): dO, v [B,8,Sp,64]; dv [B,8,Sp,64]; g_w [8,1,33,1] */
-int tm_conv33_bwd(const float* dO, const float* v, const float* conv_w, int64_t B, int64_t Sp, float* dv, float* g_w, void* stream) {
+int64_t tm_conv33_bwd_scratch_floats(int64_t B, int64_t Sp) {
+#ifndef TM_HOST_EMU
+  if (B > 0 && Sp > 0) return conv33_bwd_fast_scratch_floats(B, Sp);
+#endif
+  (void)B; (void)Sp;
+  return 1;
+}
+/* res_conv backward (Conv2d(8,8,(33,1),groups=8) along the padded token axis): dO, v [B,8,Sp,64]; dv [B,8,Sp,64]; g_w [8,1,33,1];
+ * scratch: tm_conv33_bwd_scratch_floats(B, Sp) floats (per-block tap sums of the device-tuned kernel; may be NULL: plain kernels) */
+int tm_conv33_bwd(const float* dO, const float* v, const float* conv_w, int64_t B, int64_t Sp, float* dv, float* g_w, float* scratch,
+                  void* stream) {
   TM_CHECK_ARG(dO && v && conv_w && dv && g_w && B > 0 && Sp > 0, TM_ERR_BAD_ARGUMENT, "tm_conv33_bwd: bad argument");
   cudaStream_t st = (cudaStream_t)stream;
+#ifndef TM_HOST_EMU
+  if (g_bgemm_engine != 1 && scratch != nullptr && aligned16(dO) && aligned16(v))
+    return conv33_bwd_fast(dO, v, conv_w, B, Sp, dv, g_w, scratch, st);
+#else
+  (void)scratch;
+#endif
   BW_LAUNCH(conv33_bwd_data_kernel, grid1d(B * TM_HEADS * Sp * TM_DHEAD), dim3(BT), st, dO, conv_w, (i64)B, (i64)Sp, dv);
   BW_LAUNCH(conv33_bwd_weight_kernel, dim3(TM_HEADS * TM_CONV_TAPS), dim3(BT), st, dO, v, (i64)B, (i64)Sp, g_w);
   return TM_OK;
@@ -788,8 +825,7 @@ int tm_pinv_bwd(const float* A, float* dZ, int64_t nb64, float* dA, float* scrat
   BW_LAUNCH(pinv_scalars_kernel, dim3(1), dim3(BT), st, (const float*)rows, (const float*)cols, (i64)nb * LMK, sc);
   BW_LAUNCH(scale_transpose_kernel, grid1d(n), dim3(BT), st, A, (const float*)sc, n, Zs);
   auto chain = [&](const float* Z) -> int {   // XZ, T1, T2, T3 of one iteration
-    TM_PROPAGATE(mm256(A, false, Z, false, XZ, 1.f, 0.f, nullptr, 0.f, nb, st));
-    BW_LAUNCH(scale_add_diag_kernel, grid1d(n), dim3(BT), st, (const float*)XZ, -1.f, 7.f, n, T1);   // T1 = 7I - XZ
+    TM_PROPAGATE(mm256(A, false, Z, false, XZ, 1.f, 0.f, nullptr, 0.f, nb, st, T1, -1.f, 7.f));      // XZ = A Z and T1 = 7I - XZ
     TM_PROPAGATE(mm256(XZ, false, T1, false, T2, -1.f, 0.f, nullptr, 15.f, nb, st));    // T2 = 15I - XZ T1
     TM_PROPAGATE(mm256(XZ, false, T2, false, T3, -1.f, 0.f, nullptr, 13.f, nb, st));    // T3 = 13I - XZ T2
     return TM_OK;
@@ -845,8 +881,17 @@ int tm_ppeg_bwd(const tm_weights* w, const float* h_in, const float* dy, int64_t
   float* cs_scratch = gsum + 50 * TM_DIM;
   BW_LAUNCH(ppeg_pack_kernel, grid1d(TM_DIM * 49), dim3(BT), st, w->ppeg_w7, w->ppeg_w5, w->ppeg_w3, weff);
   BW_LAUNCH(ppeg_bwd_data_kernel, grid1d(B * (G * G + 1) * TM_DIM), dim3(BT), st, dy, (const float*)weff, (i64)B, (i64)G, dh);
+#ifndef TM_HOST_EMU
+  if (g_bgemm_engine != 1) {
+    // the device-tuned kernel leaves at most COLSUM_MAX_CHUNKS partials [50][512] at `partial` and their sum at its end
+    gsum = partial + COLSUM_MAX_CHUNKS * 50 * TM_DIM;
+    TM_PROPAGATE(ppeg_wgrad_fast(h_in, dy, B, G, partial, gsum, st));
+  } else
+#endif
+  {
   BW_LAUNCH(ppeg_bwd_weight_kernel, dim3(50, (unsigned)nch), dim3(TM_DIM), st, h_in, dy, (i64)B, (i64)G, per_chunk, partial);
   TM_PROPAGATE(colsum(partial, nch, 50 * TM_DIM, 50 * TM_DIM, gsum, cs_scratch, st));
+  }
   BW_LAUNCH(ppeg_unpack_grad_kernel, grid1d(TM_DIM * 49), dim3(BT), st, (const float*)gsum, g_w7, g_b7, g_w5, g_b5, g_w3, g_b3);
   return TM_OK;
 }

@@ -71,6 +71,23 @@ int make_tmap_3d(CUtensorMap* out, const float* base, uint64_t batch, uint64_t r
   return TM_OK;
 }
 
+// fp32 [batch, rows, cols] (cols contiguous) with the 32-byte-atom 128B swizzle: the shared-memory form of an MN-major tf32
+// tcgen05 operand (rows = k, cols = m or n).  box = [1, box_rows, 32 floats].
+int make_tmap_3d_mn32(CUtensorMap* out, const float* base, uint64_t batch, uint64_t rows, uint64_t cols, uint64_t batch_stride, uint64_t ld,
+                      uint32_t box_rows) {
+  TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "TMA tensor maps need an sm_100 device and driver");
+  TM_CHECK_ARG(aligned16(base) && (ld * sizeof(float)) % 16 == 0 && (batch_stride * sizeof(float)) % 16 == 0, TM_ERR_BAD_ALIGNMENT,
+               "TMA operand must be 16-byte aligned with 16-byte pitches");
+  cuuint64_t dims[3] = {cols, rows, batch};
+  cuuint64_t strides[2] = {ld * sizeof(float), batch_stride * sizeof(float)};
+  cuuint32_t box[3] = {32, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TM_CHECK_ARG(r == CUDA_SUCCESS, TM_ERR_CUDA, "cuTensorMapEncodeTiled(3d, 128B swizzle / 32B atom) failed with %d", (int)r);
+  return TM_OK;
+}
+
 int make_tmap_3d_f16(CUtensorMap* out, const void* base, uint64_t batch, uint64_t rows, uint64_t cols, uint64_t batch_stride, uint64_t ld,
                      uint32_t box_rows, uint32_t box_cols) {
   TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "TMA tensor maps need an sm_100 device and driver");

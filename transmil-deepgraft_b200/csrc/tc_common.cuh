@@ -280,6 +280,9 @@ int make_tmap_2d(CUtensorMap* out, const float* base, uint64_t rows, uint64_t co
 // 3-D: [batch, rows, cols] with strides (batch_stride, ld, 1); box = [1, box_rows, box_cols]
 int make_tmap_3d(CUtensorMap* out, const float* base, uint64_t batch, uint64_t rows, uint64_t cols, uint64_t batch_stride, uint64_t ld,
                  uint32_t box_rows, uint32_t box_cols);
+// 3-D fp32 [batch, rows, cols] with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, box = [1, box_rows, 32]: MN-major tf32 operand boxes
+int make_tmap_3d_mn32(CUtensorMap* out, const float* base, uint64_t batch, uint64_t rows, uint64_t cols, uint64_t batch_stride, uint64_t ld,
+                      uint32_t box_rows);
 // 3-D fp16 tensor [batch, rows, cols] (cols contiguous), box = [1, box_rows, box_cols]; box_cols * 2 bytes must be 128 (SWIZZLE_128B).
 // Out-of-range rows (negative or >= rows) are zero-filled: the conv halo of the attention kernels relies on it.
 int make_tmap_3d_f16(CUtensorMap* out, const void* base, uint64_t batch, uint64_t rows, uint64_t cols, uint64_t batch_stride, uint64_t ld,

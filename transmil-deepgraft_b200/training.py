@@ -97,7 +97,9 @@ def layer_backward(K, p, name, h_in, sv, dy, plan, seed=0, drop=0.0, keep_dxn=Fa
     del dOm, dyp
     # res_conv
     dv, g_Wc = new(B, H, Sp, DH), new(H, 1, 33, 1)
-    K.check(K.L.tm_conv33_bwd(dO.data_ptr(), v.data_ptr(), Wc.data_ptr(), B, Sp, dv.data_ptr(), g_Wc.data_ptr(), K.st))
+    sc = new(int(K.L.tm_conv33_bwd_scratch_floats(B, Sp)))
+    K.check(K.L.tm_conv33_bwd(dO.data_ptr(), v.data_ptr(), Wc.data_ptr(), B, Sp, dv.data_ptr(), g_Wc.data_ptr(), sc.data_ptr(), K.st))
+    del sc
     g[name + ".attn.res_conv.weight"] = g_Wc
     # attn1 = softmax(q k_lm^T) [nb,Sp,256], attn3 = softmax(q_lm k^T) [nb,256,Sp]: recomputed, not kept by the forward
     sQ, sL, s1, s3, s2 = Sp * DH, LM * DH, Sp * LM, LM * Sp, LM * LM
