@@ -60,6 +60,7 @@ def parse():
                          "token-sharded across all ranks (BASELINE config 4, strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the sub-objects torch_eager / train_step / cfg5 / token_shard")
     ap.add_argument("--clock-hold", type=float, default=1.5, help="seconds of extra identical steps run under the clock sampler")
     return ap.parse_args()
 
@@ -80,29 +81,44 @@ def make_bag(a, rank):
 
 # ---- algorithmic cost model (DESIGN.md "Kernels") -------------------
 def stage_cost(a):
+    """stage -> (algorithmic FLOPs, algorithmic HBM bytes) of ONE launch.  Bytes use the element sizes the tensor-core engine
+    really stores: fp32 for the bag, the residual stream h and the fc1 scratch; fp16 for xn, q, k, v, merged (SIMT engine: fp32
+    everywhere).  Minimal association, halo re-reads and weights not credited."""
     from oracle.transmil_oracle import plan
     p = plan(a.n)
     B, n, D, S, Sp = a.bags, a.n, a.features, p["S"], p["Sp"]
     F0 = {2048: 1024, 768: 768}.get(D, 0)
+    e16 = 4 if a.simt else 2
     c = {}
     if F0:
-        c["fc1_gemm0"] = ("tensor", 2.0 * B * n * D * F0)
-        c["fc1_ln"] = ("hbm", 2.0 * B * n * F0 * 4)
-        c["fc1_gemm1"] = ("tensor", 2.0 * B * n * F0 * 512)
+        c["fc1_gemm0"] = (2.0 * B * n * D * F0, 4.0 * B * n * (D + F0))
+        c["fc1_ln"] = (0.0, 2.0 * B * n * F0 * 4)
+        c["fc1_gemm1"] = (2.0 * B * n * F0 * 512, 4.0 * B * (n * F0 + S * 512))
     else:
-        c["fc1_gemm1"] = ("tensor", 2.0 * B * n * D * 512)
-    c["ln_pad"] = ("hbm", 1.0 * B * (S + Sp) * 512 * 4)
-    c["qkv"] = ("tensor", 2.0 * B * Sp * 512 * 1536)
-    c["landmarks"] = ("hbm", 2.0 * B * Sp * 512 * 4)
-    c["pinv"] = ("tensor", B * 8 * (2.0 * 256 * 256 * 64 + 6 * 4 * 2.0 * 256 ** 3))
-    c["attn3v"] = ("tensor", 2 * (2.0 * B * Sp * 256 * 512))
-    c["zw"] = ("tensor", B * 8 * 2.0 * 256 * 256 * 64)
-    c["nystrom_out"] = ("tensor", 2 * (2.0 * B * Sp * 256 * 512) + 2.0 * 33 * B * Sp * 512)
-    c["to_out"] = ("tensor", 2.0 * B * S * 512 * 512)
-    c["ppeg"] = ("hbm", 2.0 * B * S * 512 * 4)
-    c["head"] = ("hbm", 512.0 * 4 * B)
-    c["fc1_tail"] = ("hbm", 512.0 * 4 * B)
+        c["fc1_gemm1"] = (2.0 * B * n * D * 512, 4.0 * B * (n * D + S * 512))
+    c["ln_pad"] = (0.0, 1.0 * B * 512 * (S * 4 + Sp * e16))
+    c["qkv"] = (2.0 * B * Sp * 512 * 1536, 1.0 * B * Sp * 512 * e16 * 4)
+    c["landmarks"] = (0.0, 2.0 * B * Sp * 512 * e16)
+    c["pinv"] = (B * 8 * (2.0 * 256 * 256 * 64 + 6 * 4 * 2.0 * 256 ** 3), B * 8 * (2 * 256 * 64 + 2 * 256 * 256) * 4.0)
+    c["attn3v"] = (2 * (2.0 * B * Sp * 256 * 512), 2.0 * B * Sp * 512 * e16)
+    c["zw"] = (B * 8 * 2.0 * 256 * 256 * 64, B * 8 * (256 * 256 + 2 * 256 * 64) * 4.0)
+    c["nystrom_out"] = (2 * (2.0 * B * Sp * 256 * 512) + 2.0 * 33 * B * Sp * 512, 3.0 * B * Sp * 512 * e16)
+    c["to_out"] = (2.0 * B * S * 512 * 512, 1.0 * B * 512 * (Sp * e16 + 2 * S * 4))
+    c["ppeg"] = (2.0 * 49 * B * S * 512, 2.0 * B * S * 512 * 4)
+    c["head"] = (2.0 * 512 * a.classes * B, 512.0 * 4 * B)
+    c["fc1_tail"] = (0.0, 512.0 * 4 * B)
     return c
+
+
+def stage_roofline(cost, ms_per_launch, pk):
+    """Both roofline fractions of one stage; `bound` = the roof that sets the larger ideal time."""
+    flops, nbytes = cost
+    t = ms_per_launch / 1e3
+    tf, gb = flops / t / 1e12, nbytes / t / 1e9
+    bound = "tensor" if flops / (pk["tensor"] * 1e12) >= nbytes / (pk["hbm"] * 1e9) else "hbm"
+    return {"bound": bound, "achieved": tf if bound == "tensor" else gb, "unit": "TFLOP/s" if bound == "tensor" else "GB/s",
+            "frac": (tf / pk["tensor"]) if bound == "tensor" else (gb / pk["hbm"]),
+            "tflops": tf, "frac_tensor": tf / pk["tensor"], "gbs": gb, "frac_hbm": gb / pk["hbm"]}
 
 
 def peaks():
@@ -117,7 +133,10 @@ def peaks():
 def ncu_traffic(a, stage):
     """dram bytes per launch of `stage` from the committed `ncu --set full` capture of this workload (None for other workloads)."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as f:
+        path = os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")
+        if not os.path.isfile(path):
+            path = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+        with open(path) as f:
             t = json.load(f)
         w = t["workload"]
         if (w["n"], w["in_features"], w["bags"]) != (a.n, a.features, a.bags):
@@ -211,74 +230,192 @@ def cpu_baseline(a):
     for _ in range(reps):
         O.forward(sd, x)
     dt = (time.perf_counter() - t0) / reps
-    return ref, {"value": a.bags / dt, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_bag": 1e3 * dt / a.bags,
-                 "sample": f"{reps} pass(es) over the bench bag ({a.bags}x{a.n}x{a.features}) through oracle/transmil_oracle.py after 1 warm-up"}
+    out = {"value": a.bags / dt, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_bag": 1e3 * dt / a.bags,
+           "sample": f"{reps} pass(es) over the bench bag ({a.bags}x{a.n}x{a.features}) through oracle/transmil_oracle.py after 1 warm-up"}
+    if cores != 8:     # the reference's own setting: torch.set_num_threads(8), code/train.py:93
+        torch.set_num_threads(8)
+        O.forward(sd, x)
+        reps8 = max(1, min(3, int(10.0 / max(dt, 1e-3))))
+        t0 = time.perf_counter()
+        for _ in range(reps8):
+            O.forward(sd, x)
+        dt8 = (time.perf_counter() - t0) / reps8
+        out["threads_8"] = {"value": a.bags / dt8, "ms_per_bag": 1e3 * dt8 / a.bags, "cores": 8,
+                            "note": "torch.set_num_threads(8), the reference's own setting (code/train.py:93)"}
+        torch.set_num_threads(cores)
+    return ref, out
 
 
-def run_token_sharded(a, rank, local_rank, world, dev, model, barrier):
-    """BASELINE config 4: one bag per step, token-sharded over all ranks (transmil-deepgraft_b200/sharded.py).  Each rank
-    holds only its rows of the bag (device-resident for `value`; pinned host rows copied in for `e2e`)."""
+def token_shard_measure(n, features, classes, steps, warmup, rank, world, dev, barrier, with_oracle=True, with_e2e=True):
+    """BASELINE config 4: ONE bag per step, token-sharded over all ranks (transmil-deepgraft_b200/sharded.py).  Every rank
+    holds only its rows of the bag.  Every rank of the group calls this; returns the result dict on rank 0 (None elsewhere).
+    world == 1 gives the N = 1 point of the strong-scaling curve: the ordinary whole-graph forward of the same bag."""
     import torch.distributed as dist
     import transmil_b200 as T
     from transmil_b200.sharded import TokenShardedTransMIL
+    L = T.capi.lib()
+    torch.manual_seed(WEIGHT_SEED)
+    model = T.TransMIL(n_classes=classes, in_features=features).eval().to(dev)
+    g = torch.Generator().manual_seed(4321)
+    x_full = torch.rand(1, n, features, generator=g)          # the same bag on every rank
+    res = {"workload": f"BASELINE config 4: ONE synthetic bag of {n} x {features} fp32 patch features per step, token-sharded over {world} "
+                       "GPU(s) (landmark allreduce + attn3.v partial allgather/merge + conv and PPEG halos), eval forward",
+           "n": n, "in_features": features, "n_gpus": world, "scaling": "strong", "steps": steps}
+    with torch.no_grad():
+        # single-GPU time of the same bag (rank 0): the denominator of the speed-up and the unsharded parity reference
+        plain = None
+        single_ms = 0.0
+        if rank == 0:
+            xd = x_full.to(dev)
+            for _ in range(max(warmup, 3)):
+                plain = model(xd)
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                plain = model(xd)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            single_ms = e0.elapsed_time(e1) / steps
+            del xd
+        if world > 1:
+            sharded = TokenShardedTransMIL(model)
+            plan = sharded.plan(n)
+            x_host = plan.take(x_full, rank).contiguous().pin_memory()
+            x_dev = x_host.to(dev)
+            for _ in range(max(warmup, 3)):
+                logits = sharded(x_dev, n=n)
+            barrier()
+            L.tm_reset_launch_count()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+            for _ in range(steps):
+                logits = sharded(x_dev, n=n)
+            ev1.record()
+            barrier()
+            ms = ev0.elapsed_time(ev1) / steps
+            launches = int(L.tm_launch_count())
+            e2e_ms = 0.0
+            if with_e2e:
+                for _ in range(2):
+                    sharded(x_host, n=n).cpu()
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(steps):
+                    sharded(x_host, n=n).cpu()
+                e1.record()
+                barrier()
+                e2e_ms = e0.elapsed_time(e1) / steps
+            t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, e2e_ms = float(t[0]), float(t[1])
+            nr = torch.ones(1, device=dev)
+            dist.all_reduce(nr)
+            res.update({"ms_per_step": ms, "launches_per_step_rank0": launches / steps, "comm_nranks_seen": int(nr.item()),
+                        "collectives": "NCCL through torch.distributed: per layer 1 allreduce (landmark sums), 1 allgather (attn3.v partials), "
+                                       "v halo; PPEG halo between the layers; logits broadcast"})
+            if with_e2e:
+                res["e2e"] = {"ms_per_step": e2e_ms, "h2d_bytes_per_step": int(x_host.numel() * 4 * world), "d2h_bytes_per_step": classes * 4 * world,
+                              "api": "TokenShardedTransMIL(model)(x_rows_pinned_host, n) -> logits.cpu() on every rank"}
+        else:
+            logits = plain
+            res.update({"ms_per_step": single_ms, "comm_nranks_seen": 1})
+    if rank != 0:
+        return None
+    res["single_gpu_ms_per_step"] = single_ms
+    res["speedup_vs_single_gpu"] = single_ms / res["ms_per_step"] if res["ms_per_step"] > 0 else None
+    res["tokens_per_s"] = n / (res["ms_per_step"] / 1e3)
+    par = {"max_abs_dlogit_vs_unsharded": float((logits - plain).abs().max())}
+    if with_oracle:
+        from oracle import transmil_oracle as O
+        torch.set_num_threads(os.cpu_count())
+        torch.set_float32_matmul_precision("highest")
+        ref = O.forward({k: v.detach().cpu() for k, v in model.state_dict().items()}, x_full)
+        got = logits.detach().cpu()
+        par["max_abs_dlogit_vs_oracle"] = float((got - ref).abs().max())
+        par["max_abs_dprob_vs_oracle"] = float((torch.softmax(got, 1) - torch.softmax(ref, 1)).abs().max())
+    res["parity"] = par
+    return res
+
+
+def run_token_sharded(a, rank, local_rank, world, dev, model, barrier):
+    """`--shard tokens`: the config-4 measurement as the headline of the line (`"scaling": "strong"`)."""
+    import torch.distributed as dist
     if a.bags != 1:
         raise SystemExit("--shard tokens runs one bag per step")
     if not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29577")
         dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
-    L = T.capi.lib()
-    sharded = TokenShardedTransMIL(model)
-    plan = sharded.plan(a.n)
-    x_host = plan.take(make_bag(a, 0), rank).contiguous().pin_memory()     # the same bag on every rank, this rank's rows
-    x_dev = x_host.to(dev)
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    for _ in range(max(a.warmup, 3)):
-        logits = sharded(x_dev, n=a.n)
-    barrier()
-    L.tm_reset_launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(a.steps):
-        logits = sharded(x_dev, n=a.n)
-    ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    launches = int(L.tm_launch_count())
-    for _ in range(2):
-        sharded(x_host, n=a.n).cpu()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(a.steps):
-        sharded(x_host, n=a.n).cpu()
-    e1.record()
-    barrier()
-    e2e_ms = e0.elapsed_time(e1)
-    clocks = None
-    if sampler:
-        clocks = sampler.stop()
-    t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_ms = float(t[0]), float(t[1])
-    with torch.no_grad():
-        plain = model(make_bag(a, 0).to(dev)) if rank == 0 else None
+    r = token_shard_measure(a.n, a.features, a.classes, a.steps, a.warmup, rank, world, dev, barrier, with_oracle=not a.no_cpu_baseline)
+    clocks = sampler.stop() if sampler else None
     if rank == 0:
-        value = a.steps / (ms / 1e3)
         cfg = workload_config(a, world)
-        cfg["workload"] = (f"BASELINE config 4: ONE synthetic bag of {a.n} x {a.features} fp32 patch features per step, token-sharded over "
-                           f"{world} GPU(s) (landmark allreduce + attn3.v allgather/merge + conv and PPEG halos), n_classes={a.classes}, eval forward")
+        cfg["workload"] = r["workload"]
         cfg["parallelism"] = f"token-shard{world}"
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
-                "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        line = {"metric": METRIC, "value": 1e3 / r["ms_per_step"], "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+                "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32 storage; tf32 (fc1) / fp16 tensor-core contractions with f32 accumulate", "data": "synthetic", "config": cfg,
-                "tokens_per_s": value * a.n, "ms_per_bag": ms / a.steps, "gpu_launches": launches, "clocks": clocks,
-                "e2e": {"value": a.steps / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(x_host.numel() * 4 * world),
-                        "d2h_bytes_per_step": a.classes * 4 * world, "ms_per_step": e2e_ms / a.steps,
-                        "api": "TokenShardedTransMIL(model)(x_rows_pinned_host, n) -> logits.cpu() on every rank"},
-                "parity": {"max_abs_dlogit_vs_unsharded": float((logits - plain).abs().max())}}
+                "tokens_per_s": r["tokens_per_s"], "ms_per_bag": r["ms_per_step"], "gpu_launches": int(r.get("launches_per_step_rank0", 0) * a.steps),
+                "clocks": clocks, "parity": r["parity"], "token_shard": r}
+        if "e2e" in r:
+            line["e2e"] = dict(r["e2e"], value=1e3 / r["e2e"]["ms_per_step"], unit=UNIT)
         print(json.dumps(line), flush=True)
     dist.destroy_process_group()
+
+
+def run_extras(a, rank, world, dev, barrier, model, x_dev, oracle_logits):
+    """Sub-objects of the JSON line for the BASELINE configs the headline does not cover.  Run AFTER every
+    timed region of the headline; each part is independent and a failure is recorded, not raised.  Every rank calls this (the
+    training allreduce, config 5's gather and the token-sharded bag are collective)."""
+    out = {}
+    tools = os.path.join(ROOT, "tools")
+    if tools not in sys.path:
+        sys.path.insert(0, tools)
+
+    def part(name, fn, collective=True):
+        try:
+            if collective or rank == 0:
+                r = fn()
+                if rank == 0 and r is not None:
+                    out[name] = r
+        except Exception as e:                      # noqa: BLE001 -- a measurement tool must not take the headline down
+            if rank == 0:
+                out[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        barrier()
+
+    # D6: stock torch eager on the same bag (rank 0 only; the other ranks wait at the barrier)
+    def eager():
+        import bench_torch_eager
+        with torch.no_grad():
+            return bench_torch_eager.measure(model, x_dev, steps=5, warmup=2, oracle_logits=oracle_logits)
+    part("torch_eager", eager, collective=False)
+
+    # config 2: training step (reference-default batch and one 20 000-patch bag), gradient allreduce over NCCL at N > 1
+    def train():
+        import bench_train
+        r = {}
+        for key, (bags, patches) in (("batch64x1000x2048", (64, 1000)), ("bag1x20000x2048", (1, 20000))):
+            r[key] = bench_train.measure(bags, patches, 2048, 2, steps=5, warmup=3, rank=rank, world=world, dev=dev)
+            torch.cuda.empty_cache()
+        return r
+    part("train_step", train)
+
+    # config 5: 256 variable-length bags, n_classes = 6, whole bags placed longest-first
+    def cfg5():
+        import bench_cfg5
+        return bench_cfg5.measure(256, 2048, 6, 5, rank=rank, world=world, with_parity=True)
+    part("cfg5", cfg5)
+
+    # config 4: one 200 000 x 2048 bag token-sharded over all ranks (N = 1: the single-GPU point of the curve)
+    def shard():
+        torch.cuda.empty_cache()
+        return token_shard_measure(200000, 2048, 2, steps=5, warmup=3, rank=rank, world=world, dev=dev, barrier=barrier,
+                                   with_oracle=True, with_e2e=False)
+    part("token_shard", shard)
+    return out
 
 
 def main():
@@ -415,6 +552,20 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms_max, e2e_serial_max = float(t[0]), float(t[1]), float(t[2])
 
+    # parity of THIS run's logits against the CPU oracle (rank 0's bag; at every world size), and the CPU baseline (N = 1 only)
+    ref = cb = None
+    if rank == 0 and not a.no_cpu_baseline:
+        if world == 1:
+            ref, cb = cpu_baseline(a)
+        else:
+            from oracle import transmil_oracle as O
+            torch.set_num_threads(os.cpu_count())
+            torch.set_float32_matmul_precision("highest")
+            ref = O.forward(cpu_state_dict(a), make_bag(a, 0))
+    extras = {}
+    if not a.no_extras:
+        extras = run_extras(a, rank, world, dev, barrier, model, x_dev, ref)
+
     if rank == 0:
         total_bags = a.steps * a.bags * world
         value = total_bags / (ms / 1e3)
@@ -425,43 +576,48 @@ def main():
                 "tokens_per_s": value * a.n, "ms_per_bag": ms / (a.steps * a.bags),
                 "gpu_launches": launches, "clocks": clocks}
         if e2e_ms is not None:
+            h2d = a.bags * a.n * a.features * 4
             line["e2e"] = {"value": total_bags / (e2e_ms_max / 1e3), "unit": UNIT,
-                           "h2d_bytes_per_step": a.bags * a.n * a.features * 4, "d2h_bytes_per_step": a.bags * a.classes * 4,
+                           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": a.bags * a.classes * 4,
                            "ms_per_step": e2e_ms_max / a.steps,
+                           "h2d_gbs_per_gpu": h2d / (e2e_ms_max / a.steps / 1e3) / 1e9,
+                           "bound": "host->device copy (PCIe): the copy of slide i+1 runs under the forward of slide i, a step costs "
+                                    "max(copy, forward) = the copy; with N GPUs the host side of the copies is shared",
                            "api": "StreamedInference(model)(pinned host bags) -> host logits, one slide at a time: every step copies "
                                   "its 50k x D bag host->device and its logits back; the copy of slide i+1 overlaps the forward of slide i",
                            "serial": {"value": total_bags / (e2e_serial_max / 1e3), "ms_per_step": e2e_serial_max / a.steps,
                                       "api": "model(x_pinned_host).cpu() per step, copy then compute"},
                            "f16_features": f16}
-        # roofline of the dominant stage
+        # roofline of the dominant stage; every stage with both fractions
         cost = stage_cost(a)
         pk = peaks()
         per_stage = {k: {"ms_per_launch": v[0] / v[1], "launches_per_step": v[1] / a.steps, "share": v[0] / stage_ms} for k, v in stages.items()}
         line["stage_pass_ms_per_step"] = stage_ms / a.steps
         if per_stage:
             top = max(per_stage, key=lambda k: per_stage[k]["share"])
-            bound, alg = cost[top]
-            dur_s = per_stage[top]["ms_per_launch"] / 1e3
-            achieved = alg / dur_s / (1e12 if bound == "tensor" else 1e9)
-            line["roofline"] = {"kernel": top, "bound": bound, "achieved": achieved, "peak": pk[bound],
-                                "unit": "TFLOP/s" if bound == "tensor" else "GB/s", "frac": achieved / pk[bound],
-                                "traffic": ncu_traffic(a, top), "peak_source": pk["src"], "algorithmic_per_launch": alg,
+            rl = stage_roofline(cost[top], per_stage[top]["ms_per_launch"], pk)
+            line["roofline"] = {"kernel": top, "bound": rl["bound"], "achieved": rl["achieved"], "peak": pk[rl["bound"]],
+                                "unit": rl["unit"], "frac": rl["frac"], "traffic": ncu_traffic(a, top), "peak_source": pk["src"],
+                                "algorithmic_per_launch": cost[top][0] if rl["bound"] == "tensor" else cost[top][1],
                                 "ms_per_launch": per_stage[top]["ms_per_launch"],
                                 "timing": "CUDA events on the launch stream at stage boundaries, K steps of the same workload run "
                                           "right after the timed region with the two-stream pinv/attn3v overlap off"}
             detail = {}
             for k, v in per_stage.items():
-                b, alg_k = cost[k]
-                ach = alg_k / (v["ms_per_launch"] / 1e3) / (1e12 if b == "tensor" else 1e9)
-                detail[k] = {"ms_per_launch": round(v["ms_per_launch"], 5), "share": round(v["share"], 4), "bound": b,
-                             "achieved": round(ach, 2), "frac": round(ach / pk[b], 4)}
+                r = stage_roofline(cost[k], v["ms_per_launch"], pk)
+                detail[k] = {"ms_per_launch": round(v["ms_per_launch"], 5), "share": round(v["share"], 4), "bound": r["bound"],
+                             "achieved": round(r["achieved"], 2), "frac": round(r["frac"], 4),
+                             "tflops": round(r["tflops"], 2), "frac_tensor": round(r["frac_tensor"], 4),
+                             "gbs": round(r["gbs"], 1), "frac_hbm": round(r["frac_hbm"], 4)}
             line["stages"] = detail
-        if not a.no_cpu_baseline and world == 1:
-            ref, cb = cpu_baseline(a)
+        if cb is not None:
             line["cpu_baseline"] = cb
+        if ref is not None:
             got = logits.detach().cpu()
             line["parity"] = {"max_abs_dlogit": float((got - ref).abs().max()),
-                              "max_abs_dprob": float((torch.softmax(got, 1) - torch.softmax(ref, 1)).abs().max())}
+                              "max_abs_dprob": float((torch.softmax(got, 1) - torch.softmax(ref, 1)).abs().max()),
+                              "vs": "oracle/transmil_oracle.py (fp32) on rank 0's bag; gates 1e-3 / 1e-4"}
+        line.update(extras)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -118,8 +118,8 @@ const char* tm_version(void);
 const char* tm_last_error(void);
 /* 1 when the current device is sm_100 (tcgen05/TMA kernels usable). */
 int tm_device_supported(void);
-/* Number of kernel launches issued by this library on the calling thread
- * since the last tm_reset_launch_count(). */
+/* Number of kernel launches issued by this library in this process (any thread: torch.autograd
+ * runs the backward on its own) since the last tm_reset_launch_count(). */
 int64_t tm_launch_count(void);
 void tm_reset_launch_count(void);
 

@@ -82,6 +82,56 @@ def test_lookahead_rule(K):
             assert (pa - pb).abs().max().item() <= 2e-6 * max(1.0, pb.abs().max().item()), f"step {step + 1} {n}"
 
 
+def test_state_dict_round_trip_resumes_mid_training(K):
+    """save after 8 steps (past one Lookahead sync), load into a fresh optimizer, continue: identical to an
+    uninterrupted run -- the per-parameter `step` (bias correction / rectification) and the slow buffers survive."""
+    from transmil_b200 import optim
+    import copy
+    args = SimpleNamespace(opt="lookahead_radam", lr=1e-2, weight_decay=0.01)
+    a, b = _twin_models()
+    oa, ob = optim.create_optimizer(args, a, lib=K.L), optim.create_optimizer(args, b, lib=K.L)
+    for step in range(8):
+        _fake_grads((a, b), step)
+        oa.step(); ob.step()
+    sd = copy.deepcopy(ob.state_dict())
+    assert set(sd) == {"state", "slow_state", "param_groups"} and len(sd["slow_state"]) == len(list(b.parameters()))
+    assert all(float(st["step"]) == 8.0 for st in sd["state"].values())
+    assert sd["param_groups"][0]["lookahead_step"] == 8
+    c = build_model(2, 1024, seed=4); c.train()
+    c.load_state_dict(b.state_dict())
+    oc = optim.create_optimizer(args, c, lib=K.L)
+    oc.load_state_dict(sd)
+    for step in range(8, 14):
+        _fake_grads((a, c), step)
+        oa.step(); oc.step()
+        for (n, pa), pc in zip(a.named_parameters(), c.parameters()):
+            assert torch.equal(pa, pc), f"step {step + 1} {n}"
+
+
+def test_torch_radam_checkpoint_loads_and_schedulers_accept_the_wrapper(K):
+    from transmil_b200 import optim
+    a, b = _twin_models()
+    ours = optim.create_optimizer(SimpleNamespace(opt="radam", lr=1e-2, weight_decay=0.01), a, lib=K.L)
+    ref = torch.optim.RAdam(optim.add_weight_decay(b, 0.01), lr=1e-2, weight_decay=0.0)
+    for step in range(7):
+        _fake_grads((b,), step)
+        ref.step()
+    a.load_state_dict(b.state_dict())
+    import copy
+    ours.load_state_dict(copy.deepcopy(ref.state_dict()))   # a checkpoint of the optimizer the reference builds (a copy, as torch.load
+                                                            # gives: state_dict() itself hands out the live `step` tensors)
+    for step in range(7, 10):
+        _fake_grads((a, b), step)
+        ours.step(); ref.step()
+        for (n, pa), pb in zip(a.named_parameters(), b.parameters()):
+            assert (pa - pb).abs().max().item() <= 2e-6 * max(1.0, pb.abs().max().item()), f"step {step + 1} {n}"
+    la = optim.create_optimizer(SimpleNamespace(opt="lookahead_radam", lr=1e-2, weight_decay=0.01), a, lib=K.L)
+    assert isinstance(la, torch.optim.Optimizer)
+    sched = torch.optim.lr_scheduler.ReduceLROnPlateau(la, mode="min", factor=0.5, patience=0)     # model_interface.py:873
+    sched.step(1.0); sched.step(2.0)
+    assert all(abs(g["lr"] - 5e-3) < 1e-12 for g in la.base.param_groups)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))

@@ -107,6 +107,51 @@ class StockTransMIL(nn.Module):
         return self._fc(self.norm(h)[:, 0])
 
 
+def measure(ours, x, steps=5, warmup=2, modes=("fp32", "tf32", "bf16"), oracle_logits=None):
+    """D6 for bench.py: the stock-torch module with the weights of `ours` on the device bag x [B,n,D]; median ms per step of each
+    precision mode (L2 flushed between iterations), the logit gap to the library and, when given, to the CPU oracle."""
+    dev = x.device
+    stock = StockTransMIL(ours).eval().to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    prev_prec, prev_cudnn = torch.get_float32_matmul_precision(), torch.backends.cudnn.allow_tf32
+
+    def timed(fn):
+        for _ in range(warmup):
+            fn()
+        ms = []
+        for _ in range(steps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            out = fn()
+            e1.record()
+            torch.cuda.synchronize(dev)
+            ms.append(e0.elapsed_time(e1))
+        return sorted(ms)[len(ms) // 2], out
+
+    res = {"what": "SURVEY 8d/D6: the same forward as a plain torch eager module (cuBLAS / cuDNN / ATen, dense [Sp,Sp] attention not "
+                   "materialised) on this GPU; tf32 = torch.set_float32_matmul_precision('high'), the reference's setting (code/train.py:94)",
+           "torch": torch.__version__, "modes": {}}
+    try:
+        with torch.no_grad():
+            lib_ms, lib_logits = timed(lambda: ours(x))
+            res["library_ms_per_step"] = lib_ms
+            for mode in modes:
+                torch.set_float32_matmul_precision("highest" if mode == "fp32" else "high")
+                torch.backends.cudnn.allow_tf32 = mode != "fp32"
+                fn = (lambda: torch.autocast("cuda", torch.bfloat16)(stock)(x)) if mode == "bf16" else (lambda: stock(x))
+                ms, logits = timed(fn)
+                m = {"ms_per_step": ms, "library_speedup": ms / lib_ms,
+                     "max_abs_dlogit_vs_library": float((logits.float() - lib_logits).abs().max())}
+                if oracle_logits is not None:
+                    m["max_abs_dlogit_vs_oracle"] = float((logits.float().cpu() - oracle_logits).abs().max())
+                res["modes"][mode] = m
+    finally:
+        torch.set_float32_matmul_precision(prev_prec)
+        torch.backends.cudnn.allow_tf32 = prev_cudnn
+    return res
+
+
 def main():
     sys.path.insert(0, ROOT)
     import transmil_b200 as T

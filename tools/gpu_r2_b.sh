@@ -13,3 +13,5 @@ cat gpurun_out/train_*.json; tail -5 gpurun_out/train.err
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/train_launches.csv \
     python tools/bench_train.py --steps 1 --warmup 1 > gpurun_out/train_ncu.log 2>&1; echo "train ncu exit $?"
 ls -la gpurun_out
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/train_launches_20k.csv \
+    python tools/bench_train.py --bags 1 --patches 20000 --steps 1 --warmup 1 > gpurun_out/train_ncu20k.log 2>&1; echo "train ncu 20k exit $?"

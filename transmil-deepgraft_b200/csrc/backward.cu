@@ -145,6 +145,12 @@ bool softmax_rows_fast_ok(const void* a, const void* b, i64 len);
 int softmax_rows_fast(float* X, i64 rows, i64 len, cudaStream_t st);
 int softmax_rows_bwd_fast(const float* P, float* dP, i64 rows, i64 len, cudaStream_t st);
 int ppeg_wgrad_fast(const float* h_in, const float* dy, i64 B, i64 G, float* partial, float* gsum, cudaStream_t st);
+i64 ln512_bwd_fast_scratch_floats();
+int ln512_bwd_fast(const float* x, const float* gamma, const float* dy, i64 rows, i64 rows_per_bag, i64 dy_bag_rows, i64 dy_row_off,
+                   const float* add, float* dx, float* g_gamma, float* g_beta, float* scratch, cudaStream_t st);
+int qkv_grad_merge_fast(const float* dq, const float* dk, const float* dv, const float* dq_lm, const float* dk_lm, i64 B, i64 Sp, i64 l,
+                        float* dqkv, cudaStream_t st);
+int ppeg_dgrad_fast(const tm_weights* w, const float* dy, i64 B, i64 G, float* dh, float* packed, cudaStream_t st);
 static bool bgemm_use_tc() { return g_bgemm_engine != 1 && tc_available(); }
 #endif
 
@@ -704,7 +710,13 @@ int tm_ln_rows_fwd(const float* x, const float* gamma, const float* beta, int64_
   return TM_OK;
 }
 
-int64_t tm_ln_bwd_scratch_floats(int64_t rows, int64_t C) { return 2 * rows + 2 * C * (colsum_chunks(rows) + 1); }
+int64_t tm_ln_bwd_scratch_floats(int64_t rows, int64_t C) {
+  int64_t n = 2 * rows + 2 * C * (colsum_chunks(rows) + 1);
+#ifndef TM_HOST_EMU
+  if (C == TM_DIM && n < ln512_bwd_fast_scratch_floats()) n = ln512_bwd_fast_scratch_floats();
+#endif
+  return n;
+}
 /* LayerNorm backward over rows of x [rows,C]; dy row of x row r = (r / rows_per_bag) * dy_bag_rows + dy_row_off + r % rows_per_bag.
  * dx = (add ? add : 0) + dLN; g_gamma, g_beta [C].  scratch: tm_ln_bwd_scratch_floats(rows, C). */
 int tm_ln_rows_bwd(const float* x, const float* gamma, const float* dy, int64_t rows, int64_t C, int64_t rows_per_bag,
@@ -714,6 +726,10 @@ int tm_ln_rows_bwd(const float* x, const float* gamma, const float* dy, int64_t 
   TM_CHECK_ARG(rows > 0 && C > 0 && rows < (1ll << 31) && rows_per_bag > 0 && rows % rows_per_bag == 0, TM_ERR_BAD_SHAPE,
                "tm_ln_rows_bwd: bad shape rows=%lld C=%lld rows_per_bag=%lld", (long long)rows, (long long)C, (long long)rows_per_bag);
   cudaStream_t st = (cudaStream_t)stream;
+#ifndef TM_HOST_EMU
+  if (g_bgemm_engine != 1 && C == TM_DIM && aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(gamma) && (add == nullptr || aligned16(add)))
+    return ln512_bwd_fast(x, gamma, dy, rows, rows_per_bag, dy_bag_rows, dy_row_off, add, dx, g_gamma, g_beta, scratch, st);
+#endif
   float* stats = scratch;
   float* partial = scratch + 2 * rows;
   const i64 nch = colsum_chunks(rows);
@@ -770,6 +786,10 @@ int tm_qkv_grad_merge(const float* dq, const float* dk, const float* dv, const f
                       int64_t l, float* dqkv, void* stream) {
   TM_CHECK_ARG(dq && dk && dv && dq_lm && dk_lm && dqkv, TM_ERR_BAD_ARGUMENT, "tm_qkv_grad_merge: NULL pointer");
   TM_CHECK_ARG(B > 0 && Sp > 0 && l > 0 && Sp == l * LMK, TM_ERR_BAD_SHAPE, "tm_qkv_grad_merge: Sp=%lld l=%lld", (long long)Sp, (long long)l);
+#ifndef TM_HOST_EMU
+  if (g_bgemm_engine != 1 && aligned16(dq) && aligned16(dk) && aligned16(dv) && aligned16(dq_lm) && aligned16(dk_lm) && aligned16(dqkv))
+    return qkv_grad_merge_fast(dq, dk, dv, dq_lm, dk_lm, B, Sp, l, dqkv, (cudaStream_t)stream);
+#endif
   BW_LAUNCH(qkv_grad_merge_kernel, grid1d(B * Sp * 3 * TM_DIM), dim3(BT), (cudaStream_t)stream, dq, dk, dv, dq_lm, dk_lm, (i64)B, (i64)Sp,
             (i64)l, dqkv);
   return TM_OK;
@@ -879,8 +899,16 @@ int tm_ppeg_bwd(const tm_weights* w, const float* h_in, const float* dy, int64_t
   const i64 per_chunk = ceil_div(total, nch);
   float* gsum = partial + nch * 50 * TM_DIM;
   float* cs_scratch = gsum + 50 * TM_DIM;
+#ifndef TM_HOST_EMU
+  if (g_bgemm_engine != 1 && tc_available() && aligned16(dy) && aligned16(dh)) {
+    // flipped packed filter: behind the COLSUM_MAX_CHUNKS partials and their sum (the tail region is free on this path)
+    TM_PROPAGATE(ppeg_dgrad_fast(w, dy, B, G, dh, partial + (COLSUM_MAX_CHUNKS + 1) * 50 * TM_DIM, st));
+  } else
+#endif
+  {
   BW_LAUNCH(ppeg_pack_kernel, grid1d(TM_DIM * 49), dim3(BT), st, w->ppeg_w7, w->ppeg_w5, w->ppeg_w3, weff);
   BW_LAUNCH(ppeg_bwd_data_kernel, grid1d(B * (G * G + 1) * TM_DIM), dim3(BT), st, dy, (const float*)weff, (i64)B, (i64)G, dh);
+  }
 #ifndef TM_HOST_EMU
   if (g_bgemm_engine != 1) {
     // the device-tuned kernel leaves at most COLSUM_MAX_CHUNKS partials [50][512] at `partial` and their sum at its end

@@ -4,7 +4,9 @@
 // shuffles and two-stage deterministic reductions (no atomics), and are what a training step launches on sm_100.
 //   conv33_bwd_fast      res_conv backward: dv and the 33 tap gradients from ONE pass over dO and v (halo tiles in smem)
 //   ppeg_wgrad_fast      PPEG filter gradients: 49 taps + bias per channel from smem halo tiles, fixed-order reduction
-//   softmax_rows_*_fast  row softmax / its backward with one warp per row (rows of <= 1024: attn1, attn2)
+//   softmax_rows_*_fast  row softmax / its backward with one warp per row (rows of <= 2048 elements)
+//   ln512_bwd_fast       LayerNorm(512) backward with one warp per row + per-block parameter-gradient partials
+//   qkv_grad_merge_fast  landmark-mean / q-scale / head-merge pass, 16 bytes per thread
 #include "common.cuh"
 
 namespace tmil {
@@ -166,13 +168,14 @@ __global__ void __launch_bounds__(256) softmax_rows_bwd_fast_kernel(const float*
 }
 
 bool softmax_rows_fast_ok(const void* a, const void* b, i64 len) {
-  return len % 4 == 0 && len <= 1024 && aligned16(a) && (b == nullptr || aligned16(b));
+  return len % 4 == 0 && len <= 2048 && aligned16(a) && (b == nullptr || aligned16(b));
 }
 int softmax_rows_fast(float* X, i64 rows, i64 len, cudaStream_t st) {
   const unsigned grid = (unsigned)ceil_div(rows, 8);
   if (len <= 256) softmax_rows_fast_kernel<2><<<grid, 256, 0, st>>>(X, rows, (int)len);
   else if (len <= 512) softmax_rows_fast_kernel<4><<<grid, 256, 0, st>>>(X, rows, (int)len);
-  else softmax_rows_fast_kernel<8><<<grid, 256, 0, st>>>(X, rows, (int)len);
+  else if (len <= 1024) softmax_rows_fast_kernel<8><<<grid, 256, 0, st>>>(X, rows, (int)len);
+  else softmax_rows_fast_kernel<16><<<grid, 256, 0, st>>>(X, rows, (int)len);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
@@ -180,7 +183,134 @@ int softmax_rows_bwd_fast(const float* P, float* dP, i64 rows, i64 len, cudaStre
   const unsigned grid = (unsigned)ceil_div(rows, 8);
   if (len <= 256) softmax_rows_bwd_fast_kernel<2><<<grid, 256, 0, st>>>(P, dP, rows, (int)len);
   else if (len <= 512) softmax_rows_bwd_fast_kernel<4><<<grid, 256, 0, st>>>(P, dP, rows, (int)len);
-  else softmax_rows_bwd_fast_kernel<8><<<grid, 256, 0, st>>>(P, dP, rows, (int)len);
+  else if (len <= 1024) softmax_rows_bwd_fast_kernel<8><<<grid, 256, 0, st>>>(P, dP, rows, (int)len);
+  else softmax_rows_bwd_fast_kernel<16><<<grid, 256, 0, st>>>(P, dP, rows, (int)len);
+  TM_LAUNCH_CHECK();
+  return TM_OK;
+}
+
+// ---- LayerNorm(512) backward, one warp per row ------------------------------------------------------------------------------------
+// Same contract as ln_rows_bwd_kernel + ln_param_grad_kernel of backward.cu for C = 512: dx = (add ? add : 0) + dLN(dy); the
+// parameter gradients leave as per-block partials partial[block][2][512] (sum dy*xhat, sum dy), added by chunk_sum_kernel.
+__global__ void __launch_bounds__(256) ln512_bwd_fast_kernel(const float* __restrict__ X, const float* __restrict__ gamma,
+                                                            const float* __restrict__ dY, i64 rows, i64 rows_per_bag, i64 dy_bag_rows,
+                                                            i64 dy_row_off, const float* __restrict__ add, float* __restrict__ dX,
+                                                            float* __restrict__ partial, int rows_per_block) {
+  __shared__ float red[8][2][TM_DIM];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float4 gm[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) gm[i] = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
+  float4 ag[4], ab[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) ag[i] = ab[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const i64 r_begin = (i64)blockIdx.x * rows_per_block;
+  const i64 r_end = r_begin + rows_per_block < rows ? r_begin + rows_per_block : rows;
+  for (i64 r = r_begin + warp; r < r_end; r += 8) {
+    const i64 bag = r / rows_per_bag, i0 = r - bag * rows_per_bag;
+    const float4* x = reinterpret_cast<const float4*>(X + r * TM_DIM);
+    const float4* dy = reinterpret_cast<const float4*>(dY + (bag * dy_bag_rows + dy_row_off + i0) * TM_DIM);
+    float4 xv[4], dv[4];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      xv[i] = x[lane + 32 * i];
+      dv[i] = dy[lane + 32 * i];
+      s += (xv[i].x + xv[i].y) + (xv[i].z + xv[i].w);
+    }
+    const float mean = warp_sum(s) * (1.0f / TM_DIM);
+    float v = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      xv[i].x -= mean; xv[i].y -= mean; xv[i].z -= mean; xv[i].w -= mean;
+      v = fmaf(xv[i].x, xv[i].x, v); v = fmaf(xv[i].y, xv[i].y, v); v = fmaf(xv[i].z, xv[i].z, v); v = fmaf(xv[i].w, xv[i].w, v);
+    }
+    const float rstd = rsqrtf(warp_sum(v) * (1.0f / TM_DIM) + 1e-5f);
+    float g1 = 0.f, g2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      xv[i].x *= rstd; xv[i].y *= rstd; xv[i].z *= rstd; xv[i].w *= rstd;      // xhat
+      ag[i].x = fmaf(dv[i].x, xv[i].x, ag[i].x); ag[i].y = fmaf(dv[i].y, xv[i].y, ag[i].y);
+      ag[i].z = fmaf(dv[i].z, xv[i].z, ag[i].z); ag[i].w = fmaf(dv[i].w, xv[i].w, ag[i].w);
+      ab[i].x += dv[i].x; ab[i].y += dv[i].y; ab[i].z += dv[i].z; ab[i].w += dv[i].w;
+      dv[i].x *= gm[i].x; dv[i].y *= gm[i].y; dv[i].z *= gm[i].z; dv[i].w *= gm[i].w;   // g = dy * gamma
+      g1 += (dv[i].x + dv[i].y) + (dv[i].z + dv[i].w);
+      g2 = fmaf(dv[i].x, xv[i].x, g2); g2 = fmaf(dv[i].y, xv[i].y, g2); g2 = fmaf(dv[i].z, xv[i].z, g2); g2 = fmaf(dv[i].w, xv[i].w, g2);
+    }
+    g1 = warp_sum(g1) * (1.0f / TM_DIM);
+    g2 = warp_sum(g2) * (1.0f / TM_DIM);
+    float4* dx = reinterpret_cast<float4*>(dX + r * TM_DIM);
+    const float4* ad = add != nullptr ? reinterpret_cast<const float4*>(add + r * TM_DIM) : nullptr;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float4 o = make_float4(rstd * (dv[i].x - g1 - xv[i].x * g2), rstd * (dv[i].y - g1 - xv[i].y * g2),
+                             rstd * (dv[i].z - g1 - xv[i].z * g2), rstd * (dv[i].w - g1 - xv[i].w * g2));
+      if (ad != nullptr) { const float4 a4 = ad[lane + 32 * i]; o.x += a4.x; o.y += a4.y; o.z += a4.z; o.w += a4.w; }
+      dx[lane + 32 * i] = o;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    reinterpret_cast<float4*>(red[warp][0])[lane + 32 * i] = ag[i];
+    reinterpret_cast<float4*>(red[warp][1])[lane + 32 * i] = ab[i];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * TM_DIM; i += 256) {
+    float sacc = 0.f;
+#pragma unroll
+    for (int wi = 0; wi < 8; ++wi) sacc += (&red[wi][0][0])[i];
+    partial[(i64)blockIdx.x * 2 * TM_DIM + i] = sacc;
+  }
+}
+__global__ void __launch_bounds__(256) chunk_sum_kernel(const float* __restrict__ partial, int chunks, i64 width, float* __restrict__ out);
+
+constexpr int LN_MAX_BLOCKS = 512;
+i64 ln512_bwd_fast_scratch_floats() { return (i64)(LN_MAX_BLOCKS + 1) * 2 * TM_DIM; }
+// scratch: ln512_bwd_fast_scratch_floats() floats
+int ln512_bwd_fast(const float* x, const float* gamma, const float* dy, i64 rows, i64 rows_per_bag, i64 dy_bag_rows, i64 dy_row_off,
+                   const float* add, float* dx, float* g_gamma, float* g_beta, float* scratch, cudaStream_t st) {
+  i64 blocks = ceil_div(rows, 64);
+  if (blocks > LN_MAX_BLOCKS) blocks = LN_MAX_BLOCKS;
+  const int rpb = (int)ceil_div(rows, blocks);
+  blocks = ceil_div(rows, rpb);
+  ln512_bwd_fast_kernel<<<(unsigned)blocks, 256, 0, st>>>(x, gamma, dy, rows, rows_per_bag, dy_bag_rows, dy_row_off, add, dx, scratch, rpb);
+  TM_LAUNCH_CHECK();
+  float* both = scratch + (i64)LN_MAX_BLOCKS * 2 * TM_DIM;
+  chunk_sum_kernel<<<(unsigned)ceil_div(2 * TM_DIM, 256), 256, 0, st>>>(scratch, (int)blocks, (i64)2 * TM_DIM, both);
+  TM_LAUNCH_CHECK();
+  TM_CUDA(cudaMemcpyAsync(g_gamma, both, TM_DIM * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  TM_CUDA(cudaMemcpyAsync(g_beta, both + TM_DIM, TM_DIM * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return TM_OK;
+}
+
+// ---- dqkv[b,t,:] = [ (dq + dq_lm[group]/l) * 64^-0.5 | dk + dk_lm[group]/l | dv ], four columns per thread ---------------------------
+__global__ void __launch_bounds__(256) qkv_grad_merge_fast_kernel(const float* __restrict__ dq, const float* __restrict__ dk,
+                                                                 const float* __restrict__ dv, const float* __restrict__ dq_lm,
+                                                                 const float* __restrict__ dk_lm, i64 B, i64 Sp, i64 l,
+                                                                 float* __restrict__ dqkv) {
+  const i64 i = (i64)blockIdx.x * 256 + threadIdx.x;        // float4 index into [B,Sp,1536]
+  if (i >= B * Sp * (3 * TM_DIM / 4)) return;
+  const int c4 = (int)(i % (3 * TM_DIM / 4));
+  const i64 t = (i / (3 * TM_DIM / 4)) % Sp, b = i / ((3 * TM_DIM / 4) * Sp);
+  const int c3 = c4 * 4, which = c3 / TM_DIM, cc = c3 % TM_DIM, h = cc / TM_DHEAD, d = cc % TM_DHEAD;
+  const i64 hm = ((b * TM_HEADS + h) * Sp + t) * TM_DHEAD + d;
+  const i64 lm = ((b * TM_HEADS + h) * TM_LANDMARKS + t / l) * TM_DHEAD + d;
+  const float inv_l = 1.0f / (float)l;
+  float4 o;
+  if (which == 2) {
+    o = __ldg(reinterpret_cast<const float4*>(dv + hm));
+  } else {
+    const float4 a = __ldg(reinterpret_cast<const float4*>((which == 0 ? dq : dk) + hm));
+    const float4 m = __ldg(reinterpret_cast<const float4*>((which == 0 ? dq_lm : dk_lm) + lm));
+    const float sc = which == 0 ? 0.125f : 1.0f;
+    o = make_float4((a.x + m.x * inv_l) * sc, (a.y + m.y * inv_l) * sc, (a.z + m.z * inv_l) * sc, (a.w + m.w * inv_l) * sc);
+  }
+  reinterpret_cast<float4*>(dqkv)[i] = o;
+}
+int qkv_grad_merge_fast(const float* dq, const float* dk, const float* dv, const float* dq_lm, const float* dk_lm, i64 B, i64 Sp, i64 l,
+                        float* dqkv, cudaStream_t st) {
+  const i64 n4 = B * Sp * (3 * TM_DIM / 4);
+  qkv_grad_merge_fast_kernel<<<(unsigned)ceil_div(n4, 256), 256, 0, st>>>(dq, dk, dv, dq_lm, dk_lm, B, Sp, l, dqkv);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
@@ -265,6 +395,30 @@ int ppeg_wgrad_fast(const float* h_in, const float* dy, i64 B, i64 G, float* par
   chunk_sum_kernel<<<(unsigned)ceil_div(50 * TM_DIM, 256), 256, 0, st>>>(partial, chunks, (i64)50 * TM_DIM, gsum);
   TM_LAUNCH_CHECK();
   return TM_OK;
+}
+
+// ---- PPEG data gradient = the forward PPEG kernel (ppeg.cu: FFMA2, TMA halo boxes) with the filter flipped -----------------------
+// dh[y,x] = dy[y,x] + sum_{i,j} w[i,j] dy[y+3-i, x+3-j] = x + correlation of dy with w'[i,j] = w[6-i, 6-j]; no bias term.
+int ppeg_fwd_prepacked(const tm_weights* w, const float* h_in, int64_t B, int64_t G, float* h_out, float* packed, cudaStream_t st);
+
+__global__ void __launch_bounds__(256) ppeg_pack_flipped_kernel(const float* __restrict__ w7, const float* __restrict__ w5,
+                                                               const float* __restrict__ w3, float* __restrict__ packed) {
+  const int i = blockIdx.x * 256 + threadIdx.x;   // (tap', channel), tap' 49 = bias
+  if (i >= 50 * TM_DIM) return;
+  const int tp = i / TM_DIM, c = i - tp * TM_DIM;
+  if (tp == 49) { packed[i] = 0.f; return; }
+  const int t = 48 - tp, dy = t / 7, dx = t - dy * 7;
+  float v = w7[c * 49 + t];
+  if (dy >= 1 && dy <= 5 && dx >= 1 && dx <= 5) v += w5[c * 25 + (dy - 1) * 5 + (dx - 1)];
+  if (dy >= 2 && dy <= 4 && dx >= 2 && dx <= 4) v += w3[c * 9 + (dy - 2) * 3 + (dx - 2)];
+  packed[i] = v;
+}
+// packed: 50 * 512 floats of scratch
+int ppeg_dgrad_fast(const tm_weights* w, const float* dy, i64 B, i64 G, float* dh, float* packed, cudaStream_t st) {
+  ppeg_pack_flipped_kernel<<<(unsigned)ceil_div(50 * TM_DIM, 256), 256, 0, st>>>(w->ppeg_w7, w->ppeg_w5, w->ppeg_w3, packed);
+  TM_LAUNCH_CHECK();
+  pdl_plain_next();
+  return ppeg_fwd_prepacked(w, dy, B, G, dh, packed, st);
 }
 
 }  // namespace tmil

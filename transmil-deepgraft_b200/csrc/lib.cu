@@ -6,18 +6,20 @@
 #include <utility>
 #include <vector>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace tmil {
 static thread_local char g_err[512] = "";
-static thread_local int64_t g_launches = 0;
+static std::atomic<int64_t> g_launches{0};   // process-wide: autograd runs the backward on its own thread
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
-void count_launch(int n) { g_launches += n; }
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 // ---- per-stage CUDA-event profiler (bench.py's roofline numbers) -----------
 static const char* kStageNames[ST_COUNT] = {"fc1_gemm0", "fc1_ln", "fc1_gemm1", "fc1_tail", "ln_pad", "qkv", "landmarks",
@@ -69,8 +71,8 @@ extern "C" {
 
 const char* tm_version(void) { return "transmil_b200 0.1 (sm_100a)"; }
 const char* tm_last_error(void) { return tmil::g_err; }
-int64_t tm_launch_count(void) { return tmil::g_launches; }
-void tm_reset_launch_count(void) { tmil::g_launches = 0; }
+int64_t tm_launch_count(void) { return tmil::g_launches.load(std::memory_order_relaxed); }
+void tm_reset_launch_count(void) { tmil::g_launches.store(0, std::memory_order_relaxed); }
 
 int tm_profile_enable(int on) {
   tmil::g_prof_on = on != 0;
