@@ -175,10 +175,49 @@ def test_dense_attention_small_vs_oracle(T):
     _close(attn.rows(rows), ref[:, :, rows], 2e-6, rtol=2e-2)
 
 
+@pytest.mark.parametrize("n,D,nc", [(50000, 1024, 2), (50000, 2048, 2), (100000, 2048, 6), (200000, 1024, 2), (200000, 2048, 2)])
+def test_full_size_logits_against_oracle(T, n, D, nc):
+    """BASELINE configs 3, 4 and the upper end of config 5 (100 000 x 2048, n_classes = 6) against the CPU oracle on the same
+    seeded bag: the north_star gates, not properties.  (The oracle does a 50 k bag in under a second and a 200 k bag in a few
+    seconds on the box's host cores; the reference module itself cannot run these sizes -- its dense attention would need
+    81 GB / 1.3 TB)"""
+    m = _gpu_model(nc, D)
+    x = make_input("rand", 1, n, D, 1000 + n % 997)
+    with torch.no_grad():
+        logits = m(x.cuda())
+    ref = O.forward({k: v.cpu() for k, v in m.state_dict().items()}, x)
+    _close(logits, ref, LOGIT_TOL)
+    _close(torch.softmax(logits, 1), torch.softmax(ref, 1), PROB_TOL)
+    assert (logits.argmax(1).cpu() == ref.argmax(1)).all()
+
+
+@pytest.mark.parametrize("n,D", [(50000, 1024), (200000, 1024)])
+def test_full_size_engines_agree_stage_by_stage(T, n, D):
+    """The tensor-core engine against the fp32 CUDA-core engine ON THE DEVICE at BASELINE sizes, stage by stage (budgets relative
+    to each stage's largest entry, from tools/stage_budget.py): localises a regression that the logits gate would only see as
+    a number."""
+    x = make_input("rand", 1, n, D, 78).cuda()
+    stages = {}
+    for engine, flags in (("tc", 0), ("simt", T.capi.TM_FLAG_SIMT_ONLY)):
+        m = _gpu_model(2, D, T.capi.TM_FLAG_KEEP_STAGES | flags)
+        with torch.no_grad():
+            logits = m(x)
+        stages[engine] = {k: m.stage(k).float().clone() for k in ("h0", "q_lm1", "attn21", "Z1", "W31", "h1", "h2", "Z", "W3")}
+        stages[engine]["h3cls"] = m.stage("h3")[:, 0].clone()
+        stages[engine]["logits"] = logits.clone()
+        del m
+    budget = {"h0": 2e-3, "q_lm1": 2e-3, "attn21": 2e-3, "Z1": 5e-3, "W31": 2e-3, "h1": 2e-3, "h2": 2e-3, "Z": 5e-3, "W3": 2e-3, "h3cls": 2e-3}
+    for k, rel in budget.items():
+        a, b = stages["tc"][k].double(), stages["simt"][k].double()
+        err, mx = (a - b).abs().max().item(), b.abs().max().item()
+        assert err <= rel * mx, f"{k}: tensor-core vs fp32 engine {err:.3e} > {rel:.0e} x {mx:.3e}"
+    _close(stages["tc"]["logits"], stages["simt"]["logits"], LOGIT_TOL)
+
+
 @pytest.mark.parametrize("n,D", [(50000, 1024), (200000, 1024)])
 def test_full_size_properties(T, n, D):
-    """BASELINE-size bags (the oracle would take minutes / the reference cannot run at all):
-    size-independent properties of the path.
+    """BASELINE-size bags: size-independent properties of the path (the comparison with the oracle is
+    test_full_size_logits_against_oracle above).
       * logits finite, Y_prob sums to 1;
       * the path is invariant to what happens behind the duplicate pad: a bag whose first `dup`
         patches are repeated at the tail by hand and shortened accordingly gives the same h0;

@@ -181,6 +181,26 @@ def test_sharded_forward_one_rank_matches_unsharded_and_oracle(built_lib, one_ra
     assert (got - plain).abs().max().item() < 2e-4
 
 
+def test_sharded_path_follows_parameter_updates(built_lib, one_rank_group):
+    """the operand copies of the GEMM weights are re-derived when a parameter changes after TokenShardedTransMIL was
+    built (load_state_dict / optimizer step), with and without a captured graph."""
+    from transmil_b200.sharded import TokenShardedTransMIL
+    m = build_model(2, 1024).cuda()
+    x = make_input("rand", 1, 3000, 1024, 21)
+    for graph in (False, True):
+        sharded = TokenShardedTransMIL(m, cuda_graph=graph)
+        first = sharded(x).cpu()
+        sharded(x)
+        other = build_model(2, 1024, seed=77).state_dict()
+        m.load_state_dict(other)
+        with torch.no_grad():
+            plain = m(x.cuda()).cpu()
+        got = sharded(x).cpu()
+        assert not torch.equal(got, first)
+        assert (got - plain).abs().max().item() < 2e-4, "the sharded path kept operand copies of the old weights"
+        m.load_state_dict(build_model(2, 1024).state_dict())
+
+
 @pytest.mark.parametrize("world", [2, 4])
 def test_sharded_forward_multi_gpu(built_lib, world):
     if torch.cuda.device_count() < world:

@@ -108,12 +108,27 @@ class CudaOps:
         if self.dev.type != "cuda":
             raise capi.TransmilError("token-sharded TransMIL needs the model on a CUDA device; there is no CPU path")
         self.flags = capi.TM_FLAG_TF32_OPERANDS | capi.TM_FLAG_F16_ACT
-        self.w = model._weights()
         self._st = lambda: torch.cuda.current_stream(self.dev).cuda_stream
-        # operand copies of the GEMM weights (what tm_transmil_fwd derives into its workspace)
         self._keep = []
         self._side = None
         self._arena_key, self._arena, self._arena_pos = None, [], 0
+        self._weights_key = None
+        self.refresh_weights()
+        self.packed = self.f32(50 * DIM)
+        self.pinv_scratch = self.f32(int(self.L.tm_pinv_scratch_floats(1)))
+
+    def refresh_weights(self):
+        """Operand copies of the GEMM weights (tf32-rounded fc1, fp16 to_qkv / to_out: what tm_transmil_fwd derives into its
+        workspace on every call), re-derived whenever a parameter changed since they were made -- load_state_dict, an optimizer
+        step or a replaced tensor (keyed on data_ptr and the tensors' version counters), so the sharded path never mixes old
+        operand copies with new norm / bias / conv tensors."""
+        model = self.m
+        key = tuple((p.data_ptr(), p._version) for p in model.parameters())
+        if key == self._weights_key:
+            return
+        self._weights_key = key
+        self._keep = []
+        self.w = model._weights()
         f = model._fc1
         self.w.fc1_w0 = self._tf32(f[0].weight)
         if model._fc1_kind == capi.TM_FC1_2048:
@@ -126,8 +141,6 @@ class CudaOps:
             self.layers[name] = dict(
                 norm_w=layer.norm.weight, norm_b=layer.norm.bias, qkv16=self._f16(layer.attn.to_qkv.weight),
                 out16=self._f16(layer.attn.to_out[0].weight), out_b=layer.attn.to_out[0].bias, conv_w=layer.attn.res_conv.weight)
-        self.packed = self.f32(50 * DIM)
-        self.pinv_scratch = self.f32(int(self.L.tm_pinv_scratch_floats(1)))
 
     # -- small helpers
     # Buffers: a forward asks for the same sequence of buffers every time it runs the same plan, so they are handed out
@@ -135,6 +148,7 @@ class CudaOps:
     # consumer of a buffer is ordered before its next producer on the same stream (NCCL ops are ordered against it by
     # torch.distributed).
     def begin_forward(self, key):
+        self.refresh_weights()
         if key != self._arena_key:
             self._arena_key, self._arena = key, []
         self._arena_pos = 0
@@ -443,6 +457,10 @@ class TokenShardedTransMIL:
             plan = self.plan(n)
         with torch.cuda.device(self.ops.dev):
             if self.cuda_graph:
+                before = self.ops._weights_key
+                self.ops.refresh_weights()
+                if self.ops._weights_key != before:
+                    self._graphs = {}                     # captured graphs hold the old operand copies
                 return self._run_graph(plan, x)
             self.ops.begin_forward(plan.p["n"])
             return sharded_forward(self.ops, plan, x).clone()      # the buffer list is reused by the next call

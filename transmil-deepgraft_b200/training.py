@@ -435,6 +435,9 @@ def _kernels_for(x):
 def _param_grads(ctx, dlogits, keep_dxn=False):
     """The library backward for what a forward kept on `ctx`: (parameters by name, gradients by name)."""
     model, x = ctx.model, ctx.x
+    if ctx.saved is None:
+        raise RuntimeError("libtransmil_b200: the stages kept by this forward were released by an earlier backward (the library "
+                           "backward runs once per forward; call the model again instead of backward(retain_graph=True))")
     p = {n: t.detach() for n, t in model.named_parameters()}
     dev, K = _kernels_for(x)
     with dev:

@@ -11,6 +11,8 @@ runs in libtransmil_b200.so (hand-written sm_100a CUDA) through the C ABI in
 include/transmil_b200.h.  There is no PyTorch or CPU fallback.
 """
 import ctypes as C
+import math
+import os
 
 import numpy as np
 import torch
@@ -69,15 +71,16 @@ class PPEG(nn.Module):
 def _fc1_1024_else_form():
     """the reference's in_features==1024 branch (TransMIL.py:117-121)
     raises at the first forward; 1024-d inputs use Sequential(Linear(1024,512), GELU())
-    (= code/models/MDMIL.py:66 = TransMIL's else branch).  Drawn from a generator seeded
-    initial_seed()+1 so the init stream of every other parameter is untouched."""
-    state = torch.random.get_rng_state()
-    seed = torch.initial_seed()
-    torch.manual_seed(seed + 1)
-    fc1 = nn.Sequential(nn.Linear(1024, 512), nn.GELU())
-    torch.manual_seed(seed)
-    torch.random.set_rng_state(state)
-    return fc1
+    (= code/models/MDMIL.py:66 = TransMIL's else branch).  Drawn from a LOCAL generator seeded
+    initial_seed()+1 (nn.Linear.reset_parameters restated with generator=), so no global RNG
+    state -- CPU or CUDA -- is touched and the init stream of every other parameter is unchanged."""
+    g = torch.Generator().manual_seed(torch.initial_seed() + 1)
+    lin = torch.nn.utils.skip_init(nn.Linear, 1024, 512)
+    with torch.no_grad():
+        nn.init.kaiming_uniform_(lin.weight, a=math.sqrt(5), generator=g)
+        bound = 1.0 / math.sqrt(1024)
+        nn.init.uniform_(lin.bias, -bound, bound, generator=g)
+    return nn.Sequential(lin, nn.GELU())
 
 
 class TransMIL(nn.Module):
@@ -114,10 +117,37 @@ class TransMIL(nn.Module):
         self.layer2 = TransLayer(norm_layer=norm_layer, dim=out_features)
         self.norm = norm_layer(out_features)
         self._fc = nn.Linear(out_features, self.n_classes)
-        self.flags = 0          # capi.TM_FLAG_* bits OR-ed into every call
+        self.flags = 0          # capi.TM_FLAG_* bits OR-ed into every call (the public knob is the `engine` property)
+        if os.environ.get("TRANSMIL_B200_ENGINE"):
+            self.engine = os.environ["TRANSMIL_B200_ENGINE"]
         self.keep_graph = False  # True: differentiate the eval-mode forward too (GradCAM-style consumers); default eval = fast path
         self._ws = None         # cached device workspace (uint8 tensor)
         self._stage_key = None
+
+    # ---- arithmetic engine -------------------------------------------------------
+    ENGINES = {
+        # name: (flag bits, what it computes in, measured error against the fp32 CPU oracle)
+        "tensor-core": (0, "tcgen05: tf32 operands for fc1 (the fp32 bag is read as is), fp16 operands for everything behind the first "
+                           "LayerNorm (xn, q, k, v, landmarks, softmax probabilities, the 6 pinv iterations, merged, to_qkv / to_out "
+                           "weights), fp32 accumulation, statistics, softmax and residual stream.  Default-init weights: max|dlogit| "
+                           "<= 2e-4, max|dY_prob| <= 5e-5 (50 k ... 200 k patches); weights after training steps: tests/"
+                           "test_zzzz_trained_weights_gpu.py; to_qkv x 8 (\"sharp softmax\" stress set): up to 2.4e-2, the same size as "
+                           "TF32 -- the reference's own GPU setting, code/train.py:94 -- gives there (DESIGN.md, Precision)"),
+        "fp32": (capi.TM_FLAG_SIMT_ONLY, "fp32 CUDA-core kernels everywhere (no tensor cores): the on-device cross-check, 1e-5-class "
+                                         "agreement with the oracle, about 30x slower at 50 k patches"),
+    }
+
+    @property
+    def engine(self):
+        """Which arithmetic the forward uses: "tensor-core" (default) or "fp32" (see TransMIL.ENGINES for what each computes in
+        and its measured error).  Settable; the environment variable TRANSMIL_B200_ENGINE sets the initial value."""
+        return "fp32" if int(self.flags) & capi.TM_FLAG_SIMT_ONLY else "tensor-core"
+
+    @engine.setter
+    def engine(self, name):
+        if name not in self.ENGINES:
+            raise ValueError(f"engine must be one of {sorted(self.ENGINES)}, not {name!r}")
+        self.flags = (int(self.flags) & ~capi.TM_FLAG_SIMT_ONLY) | self.ENGINES[name][0]
 
     # ---- parameters -> C struct ------------------------------------------------
     def _ptr(self, t, shape=None):
@@ -248,6 +278,9 @@ class TransMIL(nn.Module):
         device = self.cls_token.device
         if device.type != "cuda":
             raise capi.TransmilError("TransMIL must be on a CUDA device (model.cuda()); there is no CPU path")
+        if x.requires_grad:
+            raise NotImplementedError("libtransmil_b200: the bag requires grad, but the library's backward differentiates the parameters "
+                                      "only (d/dx through _fc1 is not built; the reference's bags are leaf features without grad)")
         xd = x.detach().to(device=device, dtype=torch.float32, non_blocking=True).contiguous()   # x.float(), TransMIL.py:174
         hooked = self._hooked_norms()
         if hooked:
