@@ -302,6 +302,53 @@ int tm_conv_halo_fix_fwd(const void* v_prev16, const void* v_next16, const float
 int tm_ppeg_rows_fwd(const tm_weights* w, const float* in_rows, int64_t y_in0, int64_t y_in1, int64_t G, int64_t tok0,
                      int64_t tok1, float* out, float* packed, void* stream);
 
+/* ---- token-sharded single bag, whole schedule in one call -----------------------------------------
+ * tm_transmil_fwd_sharded is TransMIL.forward (code/models/TransMIL.py:167-211) of ONE bag for a group of `world` GPUs, one
+ * call per rank: the per-kernel entry points above plus every exchange between the ranks, all issued on the caller's stream
+ * (asynchronous, capturable into a CUDA graph).  The exchanges run over NVLink peer memory: each rank owns a communication
+ * region that the other ranks map (CUDA IPC for one process per GPU, device pointers for one thread per GPU); data moves
+ * with flag-guarded pull kernels, no collective library on the data path.  Protocol for the host:
+ *   tm_shard_comm_create(rank, world, max_n, &comm)         on the rank's device (cudaSetDevice first)
+ *   tm_shard_comm_handle(comm, h)                            64 bytes; allgather them between the processes, any transport
+ *   tm_shard_comm_attach(comm, handles[world][64])           once; barrier between the ranks before the first forward
+ *   per bag:  tm_make_shard_plan(n, world, rank, &plan); tm_transmil_fwd_sharded(w, x_rows, &plan, comm, logits, ws, ...)
+ * Every rank must issue the same sequence of forwards (it is a collective); a rank whose peer does not arrive within 4 s
+ * records an error code readable with tm_shard_comm_status instead of hanging.  Barrier before tm_shard_comm_destroy. */
+typedef struct tm_shard_plan {
+  tm_plan bag;             /* the whole bag (tm_make_plan) */
+  int64_t world, rank;
+  int64_t row0, rows;      /* padded rows [row0, row0+rows), rows % 256 == 0 */
+  int64_t P_local;         /* front-pad rows held here (rank 0: bag.P, else 0) */
+  int64_t S_local;         /* sequence positions held here (cls = position 0, rank 0) */
+  int64_t has_cls;
+  int64_t tok0, ntok;      /* tokens [tok0, tok0+ntok) of the squared sequence (token t >= n is the duplicate pad x[t-n]) */
+  int64_t n_x_ranges;      /* 1 or 2 */
+  int64_t x_range[2][2];   /* rows [a,b) of the bag x this rank projects, concatenated in this order: x_rows [ntok, D] */
+  int64_t y_in0, y_in1;    /* image rows of the G x G token image the PPEG of this rank reads (own rows + 3-row halo) */
+  int64_t halo_lo, halo_hi;/* tokens received from rank-1 / rank+1 for the PPEG */
+  int64_t n_up, n_dn;      /* tokens sent to rank+1 / rank-1 */
+} tm_shard_plan;
+typedef struct tm_shard_comm tm_shard_comm;
+#define TM_SHARD_HANDLE_BYTES 64
+#define TM_SHARD_MAX_WORLD 16
+
+int tm_make_shard_plan(int64_t n, int64_t world, int64_t rank, tm_shard_plan* out);
+int tm_shard_comm_create(int rank, int world, int64_t max_n, tm_shard_comm** out);
+int64_t tm_shard_comm_bytes(const tm_shard_comm* comm);
+int tm_shard_comm_handle(const tm_shard_comm* comm, void* handle64);
+int tm_shard_comm_attach(tm_shard_comm* comm, const void* handles);
+/* one process driving several GPUs: the peers' regions by pointer (tm_shard_comm_base) and their device ordinals */
+void* tm_shard_comm_base(const tm_shard_comm* comm);
+int tm_shard_comm_attach_ptrs(tm_shard_comm* comm, void* const* bases, const int* devices);
+/* synchronises the device; *code = 0 or 1 + the index of the exchange that timed out since the last call */
+int tm_shard_comm_status(tm_shard_comm* comm, int32_t* code);
+int tm_shard_comm_destroy(tm_shard_comm* comm);
+int tm_sharded_workspace_bytes(const tm_weights* w, const tm_shard_plan* plan, size_t* bytes);
+/* x_rows: [plan->ntok, D] fp32 on the device (plan->x_range of the bag, concatenated); logits: [n_classes] on the device,
+ * written on every rank.  flags: 0 or TM_FLAG_NO_OVERLAP. */
+int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows, const tm_shard_plan* plan, tm_shard_comm* comm,
+                            float* logits, void* workspace, size_t workspace_bytes, uint32_t flags, void* stream);
+
 /* K14: final LayerNorm on the cls row + _fc (TransMIL.py:202-204).  h [B,S,512] -> logits [B,n_classes]. */
 int tm_head_fwd(const tm_weights* w, const float* h, int64_t B, int64_t S, float* logits,
                 void* stream);

@@ -1,5 +1,5 @@
 """torchrun worker of tests/test_sharded_gpu.py::test_sharded_forward_multi_gpu (and of tools/gpu_round scripts): the
-token-sharded forward over NCCL on WORLD_SIZE GPUs against the unsharded forward on rank 0 and the CPU oracle."""
+token-sharded forward (peer-memory transport, eager and graph-captured, and the NCCL transport) on WORLD_SIZE GPUs against the unsharded forward on rank 0 and the CPU oracle."""
 import os
 import sys
 
@@ -18,16 +18,28 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    ok = True
+    ok, keep = True, []
     for n, D in [(6000, 1024), (20000, 2048), (50000, 1024)]:
         m = build_model(2, D).cuda()
         x = make_input("rand", 1, n, D, 5)
-        sharded = TokenShardedTransMIL(m)
+        sharded = TokenShardedTransMIL(m)                     # transport="peer": one C call per rank, NVLink peer-memory exchanges
         got = sharded(x).cpu()
         local_rows = sharded.plan(n).take(x, rank)           # the loader-side form: only this rank's rows
         got2 = sharded(local_rows, n=n).cpu()
+        graphed = TokenShardedTransMIL(m, cuda_graph=True)   # eager first call, captured second, replayed third
+        g1, g2, g3 = graphed(x).cpu(), graphed(x).cpu(), graphed(x * 1.0).cpu()
+        g_other = graphed(make_input("rand", 1, n, D, 6)).cpu()
+        via_nccl = TokenShardedTransMIL(m, transport="nccl")(x).cpu()   # Python-issued schedule over torch.distributed
+        status = sharded.comm.status() | graphed.comm.status()
         with torch.no_grad():
             plain = m(x.cuda()).cpu()
+        peer_ok = (status == 0 and torch.equal(g1, got) and torch.equal(g2, got) and torch.equal(g3, got) and not torch.equal(g_other, got)
+                   and (via_nccl - got).abs().max().item() < 1e-4)
+        if not peer_ok:
+            print(f"rank {rank} n={n}: status={status} graph==eager {torch.equal(g2, got)} replay {torch.equal(g3, got)} "
+                  f"|nccl-peer|={(via_nccl - got).abs().max().item():.2e}", flush=True)
+        ok = ok and peer_ok
+        keep.append((sharded, graphed))                      # regions stay mapped until every rank is done (freed at exit)
         gathered = [torch.empty_like(got) for _ in range(world)]
         dist.all_gather_object(gathered, got)
         if rank == 0:
@@ -39,7 +51,7 @@ def main():
             print(f"n={n} D={D} world={world}: |sharded-oracle|={e_ref:.2e} |dprob|={e_prob:.2e} |sharded-unsharded|={e_plain:.2e} ranks_agree={same}", flush=True)
             ok = ok and e_ref < LOGIT_TOL and e_prob < PROB_TOL and e_plain < 2e-4 and same
     flag = torch.tensor([1 if ok else 0], device="cuda")
-    dist.broadcast(flag, 0)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
     if rank == 0 and ok:
         print("SHARDED-OK", flush=True)

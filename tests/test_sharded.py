@@ -51,6 +51,39 @@ def test_shard_plan_integers():
         ShardPlan(5000, 20)   # 256-row shards: the 3-row PPEG halo (up to 4*71 tokens) would span more than one neighbour
 
 
+def test_c_shard_plan_equals_python_shard_plan(built_lib):
+    """tm_make_shard_plan (the plan tm_transmil_fwd_sharded runs on) holds the integers of ShardPlan / RankShard, and refuses
+    the same bags."""
+    import transmil_b200 as T
+    from transmil_b200.sharded import ShardPlan, shard_plan_c
+    cases = [(n, w) for n in (600, 3000, 6000, 20000, 49999, 50000, 100000, 200000, 1000000) for w in (1, 2, 3, 4, 8, 16)]
+    checked = 0
+    for n, world in cases:
+        try:
+            sp = ShardPlan(n, world)
+        except ValueError:
+            with pytest.raises(ValueError):
+                shard_plan_c(n, world, 0)
+            continue
+        for r, s in enumerate(sp.shards):
+            c = shard_plan_c(n, world, r)
+            assert c.bag.as_dict() == sp.p
+            got = {k: int(getattr(c, k)) for k in ("world", "rank", "row0", "rows", "P_local", "S_local", "has_cls", "tok0", "ntok",
+                                                   "y_in0", "y_in1", "halo_lo", "halo_hi")}
+            want = dict(world=world, rank=r, row0=s.row0, rows=s.rows, P_local=s.P_local, S_local=s.S_local, has_cls=int(s.has_cls),
+                        tok0=s.tok0, ntok=s.ntok, y_in0=s.y_in0, y_in1=s.y_in1, halo_lo=s.halo_lo, halo_hi=s.halo_hi)
+            assert got == want, (n, world, r)
+            assert c.x_ranges() == [tuple(t) for t in s.x_ranges]
+            assert int(c.n_up) == (sp.shards[r + 1].halo_lo if r + 1 < world else 0)
+            assert int(c.n_dn) == (sp.shards[r - 1].halo_hi if r > 0 else 0)
+            checked += 1
+    assert checked > 100
+    with pytest.raises(ValueError):
+        shard_plan_c(50000, 17, 0)       # TM_SHARD_MAX_WORLD
+    with pytest.raises(ValueError):
+        shard_plan_c(50000, 4, 4)
+
+
 def _worker(rank, world, port, n, D, n_classes, sd, x, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)

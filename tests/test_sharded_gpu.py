@@ -160,15 +160,16 @@ def one_rank_group():
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("transport", ["peer", "nccl"])
 @pytest.mark.parametrize("n,D", [(3000, 1024), (6000, 2048), (20000, 512)])
-def test_sharded_forward_one_rank_matches_unsharded_and_oracle(built_lib, one_rank_group, n, D):
+def test_sharded_forward_one_rank_matches_unsharded_and_oracle(built_lib, one_rank_group, n, D, transport):
     from oracle import transmil_oracle as O
     from transmil_b200.sharded import TokenShardedTransMIL
     m = build_model(2, D).cuda()
     x = make_input("rand", 1, n, D, 11)
     with torch.no_grad():
         plain = m(x.cuda()).cpu()
-    sharded = TokenShardedTransMIL(m, cuda_graph=True)
+    sharded = TokenShardedTransMIL(m, cuda_graph=True, transport=transport)
     got = sharded(x).cpu()                 # first call: eager
     again = sharded(x).cpu()               # second call: captured into a CUDA graph and replayed
     third = sharded(x * 1.0).cpu()         # replay with a fresh input tensor
@@ -179,16 +180,19 @@ def test_sharded_forward_one_rank_matches_unsharded_and_oracle(built_lib, one_ra
     assert (got - ref).abs().max().item() < LOGIT_TOL
     assert (torch.softmax(got, 1) - torch.softmax(ref, 1)).abs().max().item() < PROB_TOL
     assert (got - plain).abs().max().item() < 2e-4
+    if transport == "peer":
+        assert sharded.comm.status() == 0
 
 
-def test_sharded_path_follows_parameter_updates(built_lib, one_rank_group):
+@pytest.mark.parametrize("transport", ["peer", "nccl"])
+def test_sharded_path_follows_parameter_updates(built_lib, one_rank_group, transport):
     """the operand copies of the GEMM weights are re-derived when a parameter changes after TokenShardedTransMIL was
     built (load_state_dict / optimizer step), with and without a captured graph."""
     from transmil_b200.sharded import TokenShardedTransMIL
     m = build_model(2, 1024).cuda()
     x = make_input("rand", 1, 3000, 1024, 21)
     for graph in (False, True):
-        sharded = TokenShardedTransMIL(m, cuda_graph=graph)
+        sharded = TokenShardedTransMIL(m, cuda_graph=graph, transport=transport)
         first = sharded(x).cpu()
         sharded(x)
         other = build_model(2, 1024, seed=77).state_dict()

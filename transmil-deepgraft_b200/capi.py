@@ -41,6 +41,20 @@ class Weights(C.Structure):
                                       "norm_w", "norm_b", "fc_w", "fc_b")])
 
 
+class ShardPlanC(C.Structure):
+    """tm_shard_plan: what one rank of a token-sharded bag owns (same integers as sharded.RankShard)."""
+    _fields_ = ([("bag", Plan)] + [(k, C.c_int64) for k in ("world", "rank", "row0", "rows", "P_local", "S_local", "has_cls", "tok0",
+                                                           "ntok", "n_x_ranges")]
+                + [("x_range", (C.c_int64 * 2) * 2)]
+                + [(k, C.c_int64) for k in ("y_in0", "y_in1", "halo_lo", "halo_hi", "n_up", "n_dn")])
+
+    def x_ranges(self):
+        return [(int(self.x_range[i][0]), int(self.x_range[i][1])) for i in range(int(self.n_x_ranges))]
+
+
+TM_SHARD_HANDLE_BYTES = 64
+TM_SHARD_MAX_WORLD = 16
+
 # symbol -> (restype, argtypes); every symbol declared in include/transmil_b200.h
 _i64, _u32, _sz = C.c_int64, C.c_uint32, C.c_size_t
 _PW = C.POINTER(Weights)
@@ -100,6 +114,17 @@ SIGNATURES = {
     "tm_conv_halo_fix_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp]),
     "tm_ppeg_rows_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _i64, _i64, _i64, _fp, _fp, _fp]),
     "tm_gemm_nt": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _i64, _u32, _fp]),
+    "tm_make_shard_plan": (C.c_int, [_i64, _i64, _i64, C.POINTER(ShardPlanC)]),
+    "tm_shard_comm_create": (C.c_int, [C.c_int, C.c_int, _i64, C.POINTER(C.c_void_p)]),
+    "tm_shard_comm_bytes": (_i64, [C.c_void_p]),
+    "tm_shard_comm_handle": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tm_shard_comm_attach": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tm_shard_comm_base": (C.c_void_p, [C.c_void_p]),
+    "tm_shard_comm_attach_ptrs": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int)]),
+    "tm_shard_comm_status": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32)]),
+    "tm_shard_comm_destroy": (C.c_int, [C.c_void_p]),
+    "tm_sharded_workspace_bytes": (C.c_int, [_PW, C.POINTER(ShardPlanC), C.POINTER(_sz)]),
+    "tm_transmil_fwd_sharded": (C.c_int, [_PW, _fp, C.POINTER(ShardPlanC), C.c_void_p, _fp, _fp, _sz, _u32, _fp]),
 }
 
 # backward entry points (csrc/backward.cu); transmil-deepgraft_b200/training.py is their only caller

@@ -315,6 +315,11 @@ int attn3v_tc_fwd_budget(const void* qlm16, const void* k16, const void* v16, in
                          int reserved_sms, cudaStream_t st) {
   return attn3v_tc_run(qlm16, k16, v16, B, Sp, W3, nullptr, scratch, st, reserved_sms);
 }
+// tm_attn3v_tc_partial_fwd with the same SM budget (sharded_fwd.cu: the replicated pinv chain runs beside it)
+int attn3v_tc_partial_budget(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t rows, float* partial,
+                             float* scratch, int reserved_sms, cudaStream_t st) {
+  return attn3v_tc_run(qlm16, k16, v16, B, rows, nullptr, partial, scratch, st, reserved_sms);
+}
 }  // namespace tmil
 
 extern "C" int64_t tm_attn3v_partial_floats(int64_t B) { return B * TM_HEADS * TM_LANDMARKS * (TM_DHEAD + 2); }

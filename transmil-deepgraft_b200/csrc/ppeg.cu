@@ -208,6 +208,12 @@ int ppeg_fwd_prepacked(const tm_weights* w, const float* h_in, int64_t B, int64_
   return ppeg_launch(w, h_in + TM_DIM, 0, G, bag, B, G, 0, G * G, h_out + TM_DIM, bag, h_in, bag, h_out, bag, packed, st, true);
 }
 
+// tm_ppeg_rows_fwd with `packed` already filled by prep_operands (sharded_fwd.cu)
+int ppeg_rows_prepacked(const tm_weights* w, const float* in_rows, int64_t y_in0, int64_t y_in1, int64_t G, int64_t tok0, int64_t tok1,
+                        float* out, float* packed, cudaStream_t st) {
+  return ppeg_launch(w, in_rows, y_in0, y_in1, 0, 1, G, tok0, tok1, out, 0, nullptr, 0, nullptr, 0, packed, st, true);
+}
+
 }  // namespace tmil
 
 extern "C" int tm_ppeg_fwd(const tm_weights* w, const float* h_in, int64_t B, int64_t G, float* h_out, float* packed,

@@ -395,23 +395,80 @@ def sharded_forward(ops, plan, x_local):
     return logits
 
 
+class PeerComm:
+    """This rank's communication region for tm_transmil_fwd_sharded plus the mappings of the peers' regions.  The 64-byte
+    CUDA IPC handles are exchanged once through the process group (any transport would do: they are plain bytes)."""
+
+    def __init__(self, max_n, dev):
+        L = self.L = capi.lib()
+        self.rank, self.world, self.max_n = dist.get_rank(), dist.get_world_size(), int(max_n)
+        if self.world > capi.TM_SHARD_MAX_WORLD:
+            raise ValueError(f"token sharding supports up to {capi.TM_SHARD_MAX_WORLD} ranks")
+        self.handle = C.c_void_p()
+        with torch.cuda.device(dev):
+            capi.check(L.tm_shard_comm_create(self.rank, self.world, self.max_n, C.byref(self.handle)))
+            if self.world > 1:
+                mine = (C.c_ubyte * capi.TM_SHARD_HANDLE_BYTES)()
+                capi.check(L.tm_shard_comm_handle(self.handle, mine))
+                blobs = [None] * self.world
+                dist.all_gather_object(blobs, bytes(mine))
+                capi.check(L.tm_shard_comm_attach(self.handle, b"".join(blobs)))
+                dist.barrier()          # nobody starts a forward before every rank has mapped every region
+
+    def status(self):
+        """0, or 1 + the index of the exchange whose producer timed out since the last call (synchronises the device)."""
+        code = C.c_int32()
+        capi.check(self.L.tm_shard_comm_status(self.handle, C.byref(code)))
+        return int(code.value)
+
+    def close(self):
+        """Collective in spirit: call it on every rank after a barrier (a peer may still be reading this rank's region)."""
+        if self.handle:
+            self.L.tm_shard_comm_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+
+def shard_plan_c(n, world, rank):
+    """tm_make_shard_plan as a capi.ShardPlanC (same integers as ShardPlan(n, world).shards[rank])."""
+    sp = capi.ShardPlanC()
+    capi.check(capi.lib().tm_make_shard_plan(int(n), int(world), int(rank), C.byref(sp)))
+    return sp
+
+
 class TokenShardedTransMIL:
     """`TokenShardedTransMIL(model)(x)`: the drop-in module's forward for ONE bag, token-sharded over the default process
     group (one process per GPU).  `x` is the full bag [n,D] / [1,n,D] on every rank (host or device) or, with `n=...`, this
-    rank's rows only (`plan(n).take(x, rank)`) -- the form a sharded loader would hand over."""
+    rank's rows only (`plan(n).take(x, rank)`) -- the form a sharded loader would hand over.
 
-    def __init__(self, model, cuda_graph=False):
+    transport="peer" (default): ONE library call per bag, tm_transmil_fwd_sharded -- the whole per-rank schedule and the
+    exchanges (flag-guarded pulls over NVLink peer memory) are issued by the library on the current stream; with
+    cuda_graph=True the call is captured once per bag size and replayed (any world size).
+    transport="nccl": the schedule is issued from Python (`sharded_forward`) kernel by kernel with torch.distributed
+    collectives in between -- the cross-check of the peer path, and the form the gloo CPU tests drive."""
+
+    def __init__(self, model, cuda_graph=False, transport="peer", max_n=1 << 20):
         if model.training:
             raise NotImplementedError("token-sharded path: inference only (model.eval())")
+        if transport not in ("peer", "nccl"):
+            raise ValueError("transport must be 'peer' or 'nccl'")
         self.model = model
-        self.ops = CudaOps(model)
+        self.transport = transport
         self._plans = {}
+        self._graphs = {}      # n -> dict(graph, x, logits) | "eager" (first call done, capture next) | "failed"
+        if transport == "peer":
+            self.dev = model.cls_token.device
+            if self.dev.type != "cuda":
+                raise capi.TransmilError("token-sharded TransMIL needs the model on a CUDA device; there is no CPU path")
+            self.cuda_graph = bool(cuda_graph)
+            self.comm = PeerComm(max_n, self.dev)
+            self._cplans, self._ws, self._w = {}, None, None
+            return
+        self.ops = CudaOps(model)
         # cuda_graph=True (single-rank groups only): after an eager first call per bag size the whole schedule -- kernels,
         # side-stream fork/join -- is captured into a CUDA graph and replayed, one launch per bag.  With more than one rank
         # the capture would have to include the NCCL point-to-point exchanges; that hung on a 2 x B200 box (r1), so
         # multi-rank groups always issue the schedule eagerly.
         self.cuda_graph = bool(cuda_graph) and dist.get_world_size() == 1
-        self._graphs = {}      # n -> dict(graph, x, logits) | "eager" (first call done, capture next) | "failed"
 
     def plan(self, n):
         key = (int(n), dist.get_world_size())
@@ -444,6 +501,61 @@ class TokenShardedTransMIL:
         state["graph"].replay()
         return state["logits"].clone()
 
+    # ---- transport="peer" -------------------------------------------------------------------------------------------
+    def _peer_call(self, cplan, x_rows, logits):
+        L, m = capi.lib(), self.model
+        w = self._w = m._weights()
+        nbytes = C.c_size_t()
+        capi.check(L.tm_sharded_workspace_bytes(C.byref(w), C.byref(cplan), C.byref(nbytes)))
+        if self._ws is None or self._ws.numel() < nbytes.value:
+            if self._graphs:
+                self._graphs = {}          # captured graphs point into the old workspace
+            self._ws = torch.empty(int(nbytes.value), dtype=torch.uint8, device=self.dev)
+        capi.check(L.tm_transmil_fwd_sharded(C.byref(w), x_rows.data_ptr(), C.byref(cplan), self.comm.handle, logits.data_ptr(),
+                                             self._ws.data_ptr(), self._ws.numel(), 0, torch.cuda.current_stream(self.dev).cuda_stream))
+
+    def _peer_forward(self, plan, x):
+        n, rank = plan.p["n"], dist.get_rank()
+        if n > self.comm.max_n:            # every rank sees the same n, so every rank rebuilds (a collective) together
+            torch.cuda.synchronize(self.dev)
+            dist.barrier()
+            self.comm.close()
+            self.comm = PeerComm(2 * n, self.dev)
+            self._graphs = {}
+        cplan = self._cplans.get(n)
+        if cplan is None:
+            cplan = self._cplans[n] = shard_plan_c(n, plan.world, rank)
+        x = x.to(device=self.dev, dtype=torch.float32, non_blocking=True).contiguous()
+        if tuple(x.shape) != (int(cplan.ntok), self.model.in_features):
+            raise ValueError(f"rank {rank} expects {int(cplan.ntok)} rows of the bag (plan.take), got {tuple(x.shape)}")
+        if not self.cuda_graph:
+            logits = torch.empty(1, self.model.n_classes, device=self.dev)
+            self._peer_call(cplan, x, logits)
+            return logits
+        # the captured call reads the parameters through their pointers at replay time (operand copies are re-derived inside
+        # the graph), so in-place updates need nothing; a REPLACED parameter tensor needs a new capture
+        key = tuple(p.data_ptr() for p in self.model.parameters())
+        state = self._graphs.get(n)
+        if isinstance(state, dict) and state["key"] != key:
+            state = None
+        if state is None:
+            # first call of a bag size: eager (loads the kernels, sizes the workspace) -- then capture.  All ranks take the
+            # same branch because they see the same sequence of bag sizes.
+            logits = torch.empty(1, self.model.n_classes, device=self.dev)
+            self._peer_call(cplan, x, logits)
+            self._graphs[n] = "eager"
+            return logits
+        if state == "eager":
+            sx, sl = x.clone(), torch.empty(1, self.model.n_classes, device=self.dev)
+            torch.cuda.synchronize(self.dev)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._peer_call(cplan, sx, sl)
+            state = self._graphs[n] = dict(graph=g, x=sx, logits=sl, key=key, w=self._w)
+        state["x"].copy_(x, non_blocking=True)
+        state["graph"].replay()
+        return state["logits"].clone()
+
     @torch.no_grad()
     def __call__(self, x, n=None):
         if n is None:
@@ -455,6 +567,9 @@ class TokenShardedTransMIL:
             x = plan.take(x, dist.get_rank())
         else:
             plan = self.plan(n)
+        if self.transport == "peer":
+            with torch.cuda.device(self.dev):
+                return self._peer_forward(plan, x)
         with torch.cuda.device(self.ops.dev):
             if self.cuda_graph:
                 before = self.ops._weights_key
