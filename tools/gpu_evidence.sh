@@ -88,7 +88,7 @@ shard)
   tail -15 gpurun_out/pytest_sharded_n$N.log
   for D in 2048 1024; do
     timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29556 \
-        bench.py --gpus $N --shard tokens --n 200000 --features $D --steps 20 --warmup 3 > gpurun_out/shard_n${N}_$D.json 2> gpurun_out/shard_n${N}_$D.err
+        bench.py --gpus $N --shard tokens --patches 200000 --features $D --steps 20 --warmup 3 > gpurun_out/shard_n${N}_$D.json 2> gpurun_out/shard_n${N}_$D.err
     echo "shard bench D=$D exit $?"; tail -3 gpurun_out/shard_n${N}_$D.err
     show gpurun_out/shard_n${N}_$D.json value ms_per_step token_shard
   done
