@@ -8,6 +8,7 @@
 #   gpurun --timeout 900  -- 'bash tools/gpu_evidence.sh tools'          D6 torch eager, cfg5, files->logits, sweep, budgets
 #   gpurun --gpus N --timeout 1200 -- 'bash tools/gpu_evidence.sh multi N'   bench.py under torchrun + sharded parity tests
 #   gpurun --gpus N --timeout 1200 -- 'bash tools/gpu_evidence.sh shard N'   token-sharded bag: tests + strong-scaling points
+#   gpurun --gpus N --timeout 600  -- 'bash tools/gpu_evidence.sh shardprof N [patches]'   per-stage times of the sharded forward
 MODE=${1:-tests}
 N=${2:-2}
 set -x
@@ -91,6 +92,14 @@ shard)
         bench.py --gpus $N --shard tokens --patches 200000 --features $D --steps 20 --warmup 3 > gpurun_out/shard_n${N}_$D.json 2> gpurun_out/shard_n${N}_$D.err
     echo "shard bench D=$D exit $?"; tail -3 gpurun_out/shard_n${N}_$D.err
     show gpurun_out/shard_n${N}_$D.json value ms_per_step token_shard
+  done
+  ;;
+shardprof)
+  P=${3:-200000}
+  for D in 2048 1024; do
+    timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29557 \
+        tools/shard_profile.py --patches $P --features $D > gpurun_out/shard_profile_n${N}_${P}_$D.txt 2> gpurun_out/shard_profile.err
+    echo "shard profile D=$D exit $?"; tail -3 gpurun_out/shard_profile.err; cat gpurun_out/shard_profile_n${N}_${P}_$D.txt
   done
   ;;
 *) echo "unknown mode $MODE"; exit 2 ;;

@@ -13,7 +13,9 @@ void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 
 enum Stage : int { ST_FC1_GEMM0 = 0, ST_FC1_LN, ST_FC1_GEMM1, ST_FC1_TAIL, ST_LN_PAD, ST_QKV, ST_LANDMARKS, ST_PINV, ST_ATTN3V,
-                   ST_ZW, ST_NYSTROM_OUT, ST_TO_OUT, ST_PPEG, ST_HEAD, ST_END, ST_COUNT };
+                   ST_ZW, ST_NYSTROM_OUT, ST_TO_OUT, ST_PPEG, ST_HEAD,
+                   // token-sharded forward only: operand preparation and the exchanges (publish + wait + pull)
+                   ST_PREP, ST_X_LANDMARKS, ST_X_ATTN3V, ST_X_CONV_HALO, ST_X_PPEG_HALO, ST_X_LOGITS, ST_END, ST_COUNT };
 void prof_mark(int stage, cudaStream_t st);
 bool prof_enabled();
 // Library-owned high-priority side stream of the current device plus a fork/join event pair (created on first use): lets

@@ -23,7 +23,8 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 // ---- per-stage CUDA-event profiler (bench.py's roofline numbers) -----------
 static const char* kStageNames[ST_COUNT] = {"fc1_gemm0", "fc1_ln", "fc1_gemm1", "fc1_tail", "ln_pad", "qkv", "landmarks",
-                                            "pinv", "attn3v", "zw", "nystrom_out", "to_out", "ppeg", "head", "end"};
+                                            "pinv", "attn3v", "zw", "nystrom_out", "to_out", "ppeg", "head", "prep", "x_landmarks",
+                                            "x_attn3v", "x_conv_halo", "x_ppeg_halo", "x_logits", "end"};
 static bool g_prof_on = false;
 static std::vector<std::pair<int, cudaEvent_t>> g_marks;
 static std::vector<cudaEvent_t> g_pool;

@@ -419,17 +419,23 @@ static int sh_layer(const ShCtx& x, const tm_layer_weights& lw, const tm_shard_p
   const int rank = c->rank, world = c->world;
   void* xn = ws + L.xn; void* q16 = ws + L.q; void* k16 = ws + L.k; void* v16 = ws + L.v; void* merged = ws + L.merged;
   float* q_lm = ws + L.q_lm; float* k_lm = ws + L.k_lm; void* qlm16 = ws + L.qlm16; void* klm16 = ws + L.klm16; void* mt16 = ws + L.mt16;
+  prof_mark(ST_LN_PAD, st);
   TM_PROPAGATE(tm_ln_pad_fwd(h_in, lw.norm_w, lw.norm_b, 1, s.S_local, s.P_local, (float*)xn, flags, st));
+  prof_mark(ST_QKV, st);
   TM_PROPAGATE(tm_qkv16_fwd(xn, lw.qkv_w, 1, s.rows, q16, k16, v16, flags, st));
   // landmark partial sums -> own region -> everyone
+  prof_mark(ST_LANDMARKS, st);
   TM_PROPAGATE(tm_landmark_sums16_fwd(q16, k16, 1, s.rows, s.row0, s.bag.l, (float*)(x.own + c->L.lm[li]), st));
+  prof_mark(ST_X_LANDMARKS, st);
   TM_PROPAGATE(sh_signal(x, FL_LM0 + li, x.all_mask));
   // res_conv halo rows -> own region -> neighbours (consumed late in the layer)
   if (x.nb_mask) {
+    prof_mark(ST_X_CONV_HALO, st);
     v_edges_kernel<<<8, 256, 0, st>>>((const __half*)v16, s.rows, (__half*)(x.own + c->L.ve[li]));
     TM_LAUNCH_CHECK();
     TM_PROPAGATE(sh_signal(x, FL_VE0 + li, x.nb_mask));
   }
+  prof_mark(ST_X_LANDMARKS, st);
   {
     GroupRanges gr;
     memset(&gr, 0, sizeof(gr));
@@ -443,7 +449,8 @@ static int sh_layer(const ShCtx& x, const tm_layer_weights& lw, const tm_shard_p
     TM_LAUNCH_CHECK();
   }
   // replicated sim2 + pseudo-inverse on the side stream, beside this rank's share of attn3.v and its exchange
-  const bool overlap = !(flags & TM_FLAG_NO_OVERLAP);
+  const bool overlap = !(flags & TM_FLAG_NO_OVERLAP) && !prof_enabled();
+  prof_mark(ST_PINV, st);
   SideStream ss;
   if (overlap) {
     TM_PROPAGATE(side_stream(&ss));
@@ -456,7 +463,9 @@ static int sh_layer(const ShCtx& x, const tm_layer_weights& lw, const tm_shard_p
   } else {
     TM_PROPAGATE(tm_pinv_fwd(q_lm, k_lm, 1, ws + L.attn2, ws + L.Z, ws + L.pinv_s, flags, st));
   }
+  prof_mark(ST_ATTN3V, st);
   TM_PROPAGATE(attn3v_tc_partial_budget(qlm16, k16, v16, 1, s.rows, (float*)(x.own + c->L.a3[li]), ws + L.a3_s, overlap ? 4 * TM_HEADS : 0, st));
+  prof_mark(ST_X_ATTN3V, st);
   TM_PROPAGATE(sh_signal(x, FL_A30 + li, x.all_mask));
   {
     PullJob job;
@@ -465,16 +474,20 @@ static int sh_layer(const ShCtx& x, const tm_layer_weights& lw, const tm_shard_p
     for (int r = 0; r < world; ++r) { job.src_off[r] = c->L.a3[li]; job.dst_off16[r] = r * n16; job.n16[r] = n16; }
     TM_PROPAGATE(sh_pull(x, FL_A30 + li, x.all_mask, ws + L.a3_gather, job));
   }
+  prof_mark(ST_ATTN3V, st);
   TM_PROPAGATE(tm_attn3v_merge_fwd(ws + L.a3_gather, world, 1, ws + L.W3, st));
   if (overlap) {
     TM_CUDA(cudaStreamWaitEvent(st, ss.join, 0));
     pdl_plain_next();
   }
+  prof_mark(ST_ZW, st);
   TM_PROPAGATE(tm_zw16_fwd(ws + L.Z, ws + L.W3, 1, ws + L.M, mt16, st));
+  prof_mark(ST_NYSTROM_OUT, st);
   TM_PROPAGATE(tm_nystrom_out_tc_fwd(q16, klm16, mt16, v16, lw.conv_w, 1, s.rows, merged, flags, st));
   if (x.nb_mask) {
     PullJob job;
     memset(&job, 0, sizeof(job));
+    prof_mark(ST_X_CONV_HALO, st);
     const i64 n16 = (i64)TM_HEADS * 16 * TM_DHEAD * 2 / 16;    // one edge: [8,16,64] fp16
     if (rank > 0) { job.src_off[rank - 1] = c->L.ve[li] + (size_t)n16 * 16; job.dst_off16[rank - 1] = 0; job.n16[rank - 1] = n16; }
     if (rank + 1 < world) {
@@ -486,6 +499,7 @@ static int sh_layer(const ShCtx& x, const tm_layer_weights& lw, const tm_shard_p
     TM_PROPAGATE(tm_conv_halo_fix_fwd(rank > 0 ? (void*)(ws + L.v_prev) : nullptr, rank + 1 < world ? (void*)(ws + L.v_next) : nullptr,
                                       lw.conv_w, 1, s.rows, merged, st));
   }
+  prof_mark(ST_TO_OUT, st);
   TM_PROPAGATE(tm_to_out_residual_fwd((const float*)merged, lw.out_w, lw.out_b, h_in, 1, s.S_local, s.P_local, h_out, flags, st));
   return TM_OK;
 }
@@ -537,6 +551,7 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
   x.all_mask = (1u << world) - 1;
   x.nb_mask = (rank > 0 ? 1u << (rank - 1) : 0u) | (rank + 1 < world ? 1u << (rank + 1) : 0u);
 
+  prof_mark(ST_PREP, st);
   epoch_bump_kernel<<<1, 1, 0, st>>>(x.epoch);
   TM_LAUNCH_CHECK();
   // operand copies of the parameters (tf32-rounded fc1, fp16 to_qkv / to_out, packed PPEG filter) in one launch
@@ -577,6 +592,7 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
   // PPEG halo (TransMIL.py:60-75 on the G x G token image): my first n_dn tokens are the previous rank's upper halo, my last
   // n_up tokens the next rank's lower halo
   if (x.nb_mask) {
+    prof_mark(ST_X_PPEG_HALO, st);
     const float* toks = h1 + off * TM_DIM;
     const i64 n_dn16 = s.n_dn * (TM_DIM / 4), n_up16 = s.n_up * (TM_DIM / 4);
     if (n_dn16 || n_up16) {
@@ -595,6 +611,7 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
     }
     TM_PROPAGATE(sh_pull(x, FL_PPEG, x.nb_mask, ext, job));
   }
+  prof_mark(ST_PPEG, st);
   TM_PROPAGATE(ppeg_rows_prepacked(&wl, ext + off * TM_DIM, s.y_in0, s.y_in1, s.bag.G, s.tok0, s.tok0 + s.ntok, h2 + off * TM_DIM, ws + L.packed, st));
   if (s.has_cls) {
     TM_CUDA(cudaMemcpyAsync(h2, h1, TM_DIM * sizeof(float), cudaMemcpyDeviceToDevice, st));
@@ -602,6 +619,7 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
   }
   TM_PROPAGATE(sh_layer(x, wl.layer2, s, 1, h2, h3, ws, L, flags));
   // final norm + head on the cls row (TransMIL.py:202-204): rank 0, into its region; everyone pulls the logits
+  prof_mark(ST_HEAD, st);
   if (s.has_cls) {
     TM_PROPAGATE(tm_head_fwd(&wl, h3, 1, s.S_local, (float*)(x.own + comm->L.logits), st));
     TM_PROPAGATE(sh_signal(x, FL_LOGITS, x.all_mask));
@@ -609,9 +627,11 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
   {
     PullJob job;
     memset(&job, 0, sizeof(job));
+    prof_mark(ST_X_LOGITS, st);
     job.src_off[0] = comm->L.logits; job.dst_off16[0] = 0; job.n16[0] = ceil_div((i64)w->n_classes * 4, 16);
     TM_PROPAGATE(sh_pull(x, FL_LOGITS, 1u, ws + L.logits, job));
   }
   TM_CUDA(cudaMemcpyAsync(logits, ws + L.logits, (size_t)w->n_classes * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  prof_mark(ST_END, st);
   return TM_OK;
 }
