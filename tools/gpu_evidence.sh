@@ -8,6 +8,7 @@
 #   gpurun --timeout 900  -- 'bash tools/gpu_evidence.sh tools'          D6 torch eager, cfg5, files->logits, sweep, budgets
 #   gpurun --gpus N --timeout 1200 -- 'bash tools/gpu_evidence.sh multi N'   bench.py under torchrun + sharded parity tests
 #   gpurun --gpus N --timeout 1200 -- 'bash tools/gpu_evidence.sh shard N'   token-sharded bag: tests + strong-scaling points
+#   gpurun --timeout 400 -- 'bash tools/gpu_evidence.sh pinv'             pinv cluster kernel: parity test + time per generation
 #   gpurun --gpus N --timeout 600  -- 'bash tools/gpu_evidence.sh shardprof N [patches]'   per-stage times of the sharded forward
 MODE=${1:-tests}
 N=${2:-2}
@@ -93,6 +94,11 @@ shard)
     echo "shard bench D=$D exit $?"; tail -3 gpurun_out/shard_n${N}_$D.err
     show gpurun_out/shard_n${N}_$D.json value ms_per_step token_shard
   done
+  ;;
+pinv)
+  timeout 120 python -m pytest tests/test_pinv_gpu.py -m gpu -x -q 2>&1 | tail -15
+  TM_PINV_KERNEL=push timeout 120 python tools/pinv_check.py 2>&1 | tail -5
+  timeout 120 python tools/pinv_check.py 2>&1 | tail -5
   ;;
 shardprof)
   P=${3:-200000}

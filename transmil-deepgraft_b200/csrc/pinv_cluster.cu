@@ -309,6 +309,7 @@ __global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restric
 }
 
 int pinv_push_launch(__half* A16, __half* Za, __half* Zb, int nbh, float* Z, cudaStream_t st);   // pinv_push.cu
+int pinv_pipe_launch(__half* A16, __half* Za, __half* Zb, int nbh, float* Z, cudaStream_t st);   // pinv_pipe.cu
 
 // scratch16: 6 fp16 matrices per (bag, head): A16, Za, Zb, XZ, T1, T2
 int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpart, int nparts, const float* scale, int nbh,
@@ -328,8 +329,9 @@ int pinv_cluster_run(const float* attn2, const float* rowsum, const float* colpa
   static int use_push = -1;
   if (use_push < 0) {
     const char* e = getenv("TM_PINV_KERNEL");
-    use_push = (e != nullptr && strcmp(e, "tma") == 0) ? 0 : 1;
+    use_push = (e != nullptr && strcmp(e, "tma") == 0) ? 0 : ((e != nullptr && (strcmp(e, "push") == 0 || strcmp(e, "remote") == 0)) ? 1 : 2);
   }
+  if (use_push == 2) return pinv_pipe_launch(A16, Za, Zb, nbh, Z, st);
   if (use_push) return pinv_push_launch(A16, Za, Zb, nbh, Z, st);
   PinvMaps maps;
   __half* ptrs[6] = {A16, Za, Zb, XZ, T1, T2};
