@@ -44,7 +44,7 @@ __device__ __forceinline__ uint32_t pq_mapa(uint32_t cta_addr, uint32_t rank) {
 }
 // one arrival + `bytes` expected on a PEER's barrier, then the copy that completes them
 __device__ __forceinline__ void pq_push(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
-  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(bar_cluster), "r"(bytes) : "memory");
+  asm volatile("mbarrier.arrive.expect_tx.relaxed.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(bar_cluster), "r"(bytes) : "memory");
   asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_cluster),
                "r"(src_cta), "r"(bytes), "r"(bar_cluster)
                : "memory");
@@ -79,8 +79,8 @@ pinv_pipe_kernel(const __grid_constant__ PinvPipeMaps maps, const __half* __rest
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
 
 #ifdef TM_PINV_TIMELINE
-  __shared__ long long tl[PQ_STEPS][2][6];   // per half: mma start, mma committed | epi ready, packed, pushed, done
-#define TLQ(s, gg, i) tl[s][gg][i] = clock64()
+  __shared__ long long tl[12][2][6];   // per half: mma start, mma committed | epi ready, packed, pushed, done
+#define TLQ(s, gg, i) if ((s) < 12) tl[s][gg][i] = clock64()
 #else
 #define TLQ(s, gg, i)
 #endif
