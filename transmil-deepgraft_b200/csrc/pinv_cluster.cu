@@ -282,12 +282,28 @@ __global__ void __launch_bounds__(256) pinv_prep16_kernel(const float* __restric
   pdl_sync();
   const int tid = threadIdx.y * 32 + threadIdx.x;
   float mr = 0.f, mc = 0.f;
-  for (int i = tid; scale == nullptr && i < nbh * TM_LANDMARKS; i += 256) {
-    mr = fmaxf(mr, __ldg(rowsum + i));
-    const int bh = i / TM_LANDMARKS, j = i - bh * TM_LANDMARKS;
-    float c = 0.f;
-    for (int p = 0; p < nparts; ++p) c += __ldg(colpart + ((long long)bh * nparts + p) * TM_LANDMARKS + j);
-    mc = fmaxf(mc, c);
+  if (scale == nullptr) {
+    // global init scalar: every CTA needs it, so the scan is kept short -- four columns per thread, the 16 row-tile partials
+    // of a head as 16 independent 16-byte loads (fixed summation order p = 0 .. 15: same bits in every CTA and every run)
+    const int j4 = (tid & 63) * 4;
+    for (int bh = tid >> 6; bh < nbh; bh += 4) {
+      const float4 rs = __ldg(reinterpret_cast<const float4*>(rowsum + bh * TM_LANDMARKS + j4));
+      mr = fmaxf(mr, fmaxf(fmaxf(rs.x, rs.y), fmaxf(rs.z, rs.w)));
+      float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (nparts == 16) {
+        float4 v[16];
+#pragma unroll
+        for (int p = 0; p < 16; ++p) v[p] = __ldg(reinterpret_cast<const float4*>(colpart + ((long long)bh * 16 + p) * TM_LANDMARKS + j4));
+#pragma unroll
+        for (int p = 0; p < 16; ++p) { c.x += v[p].x; c.y += v[p].y; c.z += v[p].z; c.w += v[p].w; }
+      } else {
+        for (int p = 0; p < nparts; ++p) {
+          const float4 v = __ldg(reinterpret_cast<const float4*>(colpart + ((long long)bh * nparts + p) * TM_LANDMARKS + j4));
+          c.x += v.x; c.y += v.y; c.z += v.z; c.w += v.w;
+        }
+      }
+      mc = fmaxf(mc, fmaxf(fmaxf(c.x, c.y), fmaxf(c.z, c.w)));
+    }
   }
   mr = warp_max(mr); mc = warp_max(mc);
   if (threadIdx.x == 0) { red[0][threadIdx.y] = mr; red[1][threadIdx.y] = mc; }
