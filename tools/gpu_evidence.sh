@@ -97,7 +97,6 @@ shard)
   ;;
 pinv)
   timeout 120 python -m pytest tests/test_pinv_gpu.py -m gpu -x -q 2>&1 | tail -15
-  TM_PINV_KERNEL=push timeout 120 python tools/pinv_check.py 2>&1 | tail -5
   timeout 120 python tools/pinv_check.py 2>&1 | tail -5
   ;;
 shardprof)

@@ -1,5 +1,5 @@
 """MEASUREMENT TOOL: time of tm_pinv_fwd (attn2 + prep + cluster kernel) at B = 1 / 8 / 64 and its error against float64, for the
-kernel generation selected by TM_PINV_KERNEL (default: pinv_pipe.cu; "push": pinv_push.cu).  Run under `timeout`."""
+cluster kernel of csrc/pinv_pipe.cu.  Run under `timeout`."""
 import os
 import sys
 
@@ -12,7 +12,6 @@ from test_pinv_gpu import _pinv64  # noqa: E402
 
 L = T.capi.lib()
 st = torch.cuda.current_stream().cuda_stream
-print("TM_PINV_KERNEL =", os.environ.get("TM_PINV_KERNEL", "(default: pipe)"))
 for B in (1, 8, 64):
     g = torch.Generator().manual_seed(B)
     q = (torch.randn(B, 8, 256, 64, generator=g) * 0.3).cuda()

@@ -1,5 +1,5 @@
 // K7, third generation: the 24 dependent 256^3 products of the Moore-Penrose iteration inside a 4-CTA cluster, exchanged through
-// distributed shared memory like pinv_push.cu, but PIPELINED BY COLUMN HALF.
+// distributed shared memory (like the second generation, r1) and PIPELINED BY COLUMN HALF.
 //
 //   XZ = A Z;  T1 = 7 XZ - XZ XZ;  T2 = 15 XZ - XZ T1;  Z' = 3.25 Z - 0.25 Z T2      (moore_penrose_iter_pinv, 0.0.11)
 //
