@@ -402,6 +402,30 @@ def run_extras(a, rank, world, dev, barrier, model, x_dev, oracle_logits):
             return bench_torch_eager.measure(model, x_dev, steps=5, warmup=2, oracle_logits=oracle_logits)
     part("torch_eager", eager, collective=False)
 
+    # E4: the same bag with the second layer's out-projection restricted to the cls row's tiles (model.skip_unread_rows).  A
+    # separate number: it does FEWER flops than the headline (the reference computes those rows), same logits bit for bit.
+    def e4():
+        with torch.no_grad():
+            full = model(x_dev)
+            model.skip_unread_rows = True
+            try:
+                for _ in range(3):
+                    got = model(x_dev)
+                torch.cuda.synchronize(dev)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(20):
+                    got = model(x_dev)
+                e1.record()
+                torch.cuda.synchronize(dev)
+            finally:
+                model.skip_unread_rows = False
+        ms = e0.elapsed_time(e1) / 20
+        return {"ms_per_step": ms, "value": x_dev.shape[0] / (ms / 1e3), "unit": UNIT, "logits_bit_identical_to_full_path": bool(torch.equal(full, got)),
+                "note": "TM_FLAG_CLS_ONLY_L2: layer-2 nystrom_out / to_out run for the cls row's 128-row tiles only (TransMIL.py:197-204 reads "
+                        "h[:, 0] only); q, k, v, landmarks, pinv, attn3.v complete.  Fewer flops than the headline step: not comparable with it"}
+    part("e4_cls_only", e4, collective=False)
+
     # config 2: training step (reference-default batch and one 20 000-patch bag), gradient allreduce over NCCL at N > 1
     def train():
         import bench_train

@@ -68,6 +68,12 @@ typedef enum tm_fc1_kind {
                                        fp16 copy of its weight (same 10-bit mantissa as the tf32 operands of the fp32 path).
                                        Tensor-core engine only. */
 
+#define TM_FLAG_CLS_ONLY_L2 128u    /* tm_transmil_fwd: of the second TransLayer's output only the cls row is read (TransMIL.py:197-204:
+                                       h = self.norm(h)[:, 0]), so its out-projection (nystrom_out, to_out + residual) is run for the
+                                       128-row tiles that hold the cls row only; q, k, v, landmarks, pinv and attn3.v are complete.
+                                       The cls row, hence the logits, has the same bits as without the flag.  Off by default: the
+                                       skipped rows are work the reference does.  Ignored with TM_FLAG_KEEP_STAGES / SIMT_ONLY. */
+
 /* Index contract of one bag (TransMIL.py:177-179,184-186,190-193 and the
  * nystrom-attention 0.0.11 front pad / landmark grouping).  Pure host code. */
 typedef struct tm_plan {

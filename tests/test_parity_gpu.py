@@ -247,3 +247,21 @@ def test_full_size_properties(T, n, D):
     assert 1e-6 < res < 0.2
     h0 = m.stage("h0")
     assert torch.equal(h0[:, 1 + n:], h0[:, 1:1 + p["dup"]])
+
+
+@pytest.mark.parametrize("n,D,B", [(700, 512, 1), (3000, 1024, 1), (50000, 1024, 1), (1000, 2048, 4), (65025, 1024, 1)])
+def test_skip_unread_rows_keeps_the_logit_bits(T, n, D, B):
+    """SURVEY 8e/E4 (TM_FLAG_CLS_ONLY_L2): the second layer's out-projection for the cls row's tiles only.  Every tile is computed as
+    in the full call, so the logits must not change by a bit (65025 = 255^2: S % 256 == 2, P = 254, the cls row sits in the
+    second 128-row tile)."""
+    m = _gpu_model(2, D, 0)
+    x = make_input("rand", B, n, D, 5).cuda()
+    with torch.no_grad():
+        full = m(x)
+        m.skip_unread_rows = True
+        skip = m(x)
+        m.skip_unread_rows = False
+        again = m(x)
+    assert torch.isfinite(skip).all()
+    assert torch.equal(full, skip), (full - skip).abs().max().item()
+    assert torch.equal(full, again)

@@ -8,6 +8,8 @@ extern "C" int64_t tm_pinv_scratch_floats(int64_t B);
 
 namespace tmil {
 
+int nystrom_out_tc_tiles(const void* q16, const void* klm16, const void* mt16, const void* v16, const float* conv_w, int64_t B, int64_t Sp,
+                         int64_t row_tiles, void* merged, uint32_t flags, cudaStream_t stream);
 int attn3v_tc_fwd_budget(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3, float* scratch,
                          int reserved_sms, cudaStream_t st);
 int prep_operands(const float* const* srcs, void* const* dsts, const long long* counts, const int* kinds, int njobs,
@@ -130,6 +132,7 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
   float* attn2 = ws + L.small[li][SM_ATTN2]; float* Z = ws + L.small[li][SM_Z];
   float* W3 = ws + L.small[li][SM_W3]; float* M = ws + L.small[li][SM_M];
   float* merged = ws + L.merged;
+  int64_t cls_tiles = 0;
   prof_mark(ST_LN_PAD, st);
   pdl_gate(32);
   TM_PROPAGATE(tm_ln_pad_fwd(h_in, lw.norm_w, lw.norm_b, B, p.S, p.P, xn, flags, st));
@@ -196,7 +199,10 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
     TM_PROPAGATE(tm_zw16_fwd(Z, W3, B, M, mt16, st));
     prof_mark(ST_NYSTROM_OUT, st);
     pdl_gate(16);
-    TM_PROPAGATE(tm_nystrom_out_tc_fwd(q16, klm16, mt16, v16, lw.conv_w, B, p.Sp, merged, flags, st));
+    // second layer, only the cls row is read afterwards (TM_FLAG_CLS_ONLY_L2): the tiles up to and including the one that holds
+    // padded row P (the cls token); one bag at a time would be B launches of to_out, so larger batches keep the full GEMM
+    cls_tiles = (li == 1 && (flags & TM_FLAG_CLS_ONLY_L2) && !(flags & TM_FLAG_KEEP_STAGES)) ? p.P / 128 + 1 : 0;
+    TM_PROPAGATE(nystrom_out_tc_tiles(q16, klm16, mt16, v16, lw.conv_w, B, p.Sp, cls_tiles, merged, flags, st));
   } else {
   prof_mark(ST_QKV, st);
   TM_PROPAGATE(tm_qkv_fwd(xn, lw.qkv_w, B, p.Sp, q, k, v, flags, st));
@@ -213,6 +219,11 @@ static int layer_fwd(const tm_layer_weights& lw, const tm_plan& p, int64_t B, co
   }
   prof_mark(ST_TO_OUT, st);
   pdl_gate(128);
+  if (cls_tiles > 0 && B == 1 && cls_tiles * 128 < p.Sp) {
+    // rows [0, cls_tiles * 128) of the padded sequence: the same 128-row GEMM tiles as the full call, just fewer of them
+    TM_PROPAGATE(tm_to_out_residual_fwd(merged, lw.out_w, lw.out_b, h_in, 1, cls_tiles * 128 - p.P, p.P, h_out, flags, st));
+    return TM_OK;
+  }
   TM_PROPAGATE(tm_to_out_residual_fwd(merged, lw.out_w, lw.out_b, h_in, B, p.S, p.P, h_out, flags, st));
   return TM_OK;
 }

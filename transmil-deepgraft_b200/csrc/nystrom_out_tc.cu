@@ -384,8 +384,20 @@ extern "C" int tm_zw16_fwd(const float* Z, const float* W3, int64_t B, float* M,
   return TM_OK;
 }
 
+namespace tmil {
+int nystrom_out_tc_tiles(const void* q16, const void* klm16, const void* mt16, const void* v16, const float* conv_w, int64_t B, int64_t Sp,
+                         int64_t row_tiles, void* merged, uint32_t flags, cudaStream_t stream);
+}
+
 extern "C" int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const void* mt16, const void* v16, const float* conv_w,
                                      int64_t B, int64_t Sp, void* merged, uint32_t flags, void* stream) {
+  return tmil::nystrom_out_tc_tiles(q16, klm16, mt16, v16, conv_w, B, Sp, 0, merged, flags, (cudaStream_t)stream);
+}
+
+// row_tiles > 0: only the first row_tiles tiles of 128 padded rows of every bag are produced (the rest of `merged` is left
+// untouched); every tile is computed exactly as in the full call (same operands, same order), so its rows have the same bits.
+int tmil::nystrom_out_tc_tiles(const void* q16, const void* klm16, const void* mt16, const void* v16, const float* conv_w, int64_t B,
+                               int64_t Sp, int64_t row_tiles, void* merged, uint32_t flags, cudaStream_t stream) {
   using namespace tmil;
   TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE, "tm_nystrom_out_tc_fwd: Sp must be a multiple of 256 (Sp=%lld)", (long long)Sp);
   TM_CHECK_ARG(q16 && klm16 && mt16 && v16 && conv_w && merged, TM_ERR_BAD_ARGUMENT, "tm_nystrom_out_tc_fwd: NULL pointer");
@@ -402,7 +414,8 @@ extern "C" int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const v
     TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
     TM_CUDA(cudaFuncSetAttribute(nystrom_out_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM));
   }
-  const int tiles_per_bh = (int)(Sp / NT_TOK);
+  int tiles_per_bh = (int)(Sp / NT_TOK);
+  if (row_tiles > 0 && row_tiles < tiles_per_bh) tiles_per_bh = (int)row_tiles;
   const int chunks = attn_chunks(nbh, tiles_per_bh);
   const int tpc = (int)ceil_div(tiles_per_bh, chunks);
   const int used = (int)ceil_div(tiles_per_bh, tpc);

@@ -121,6 +121,9 @@ class TransMIL(nn.Module):
         if os.environ.get("TRANSMIL_B200_ENGINE"):
             self.engine = os.environ["TRANSMIL_B200_ENGINE"]
         self.keep_graph = False  # True: differentiate the eval-mode forward too (GradCAM-style consumers); default eval = fast path
+        # True: the second TransLayer's out-projection is run for the cls row's tiles only (TransMIL.py:197-204 reads nothing else
+        # of it); logits keep their bits.  Off by default because those rows are work the reference does.
+        self.skip_unread_rows = False
         self._ws = None         # cached device workspace (uint8 tensor)
         self._stage_key = None
 
@@ -223,6 +226,8 @@ class TransMIL(nn.Module):
         L = capi.lib()
         B, n, D = (int(s) for s in x.shape)
         flags = int(self.flags) | (capi.TM_FLAG_KEEP_STAGES if return_attn else 0)
+        if getattr(self, "skip_unread_rows", False) and not return_attn:
+            flags |= capi.TM_FLAG_CLS_ONLY_L2
         # fp16 feature bags (half-precision feature files) are consumed as they are: x.float() of
         # TransMIL.py:174 is an exact upcast, so fc1 reads the halves directly (half the H2D and HBM bytes)
         half_in = x.dtype == torch.float16 and not (flags & capi.TM_FLAG_SIMT_ONLY)
