@@ -97,16 +97,9 @@ __device__ __forceinline__ uint4 ld_peer16(const uint4* p) {   // never served f
 
 __global__ void epoch_bump_kernel(uint32_t* epoch) { *epoch += 1; }
 
-// Publish: thread t stores this rank's epoch into flag [kind][my_rank] of rank t's region (t in `mask`).  Everything this
+// Publishing a contribution = storing this rank's epoch into flag [kind][my_rank] of every consumer's region.  Everything the
 // rank's stream wrote before the launch is ordered before the flag (kernel boundary, then fence + release at system scope).
-__global__ void signal_kernel(PeerPtrs regions, size_t flags_off, uint32_t mask, int kind, int my_rank, const uint32_t* epoch) {
-  const int t = threadIdx.x;
-  if (!((mask >> t) & 1)) return;
-  __threadfence_system();
-  uint32_t* f = reinterpret_cast<uint32_t*>(regions.p[t] + flags_off) + (kind * SH_MAX_WORLD + my_rank) * SH_FLAG_STRIDE;
-  st_release_sys(f, *epoch);
-}
-
+// There is no separate publish kernel: the store is the first thing the next kernel of the schedule does.
 constexpr unsigned long long SH_TIMEOUT_NS = 4000000000ull;   // 4 s: a dead peer becomes an error code, not a hung GPU
 __device__ __forceinline__ void wait_flag(const uint32_t* flags, int kind, int src, uint32_t want, uint32_t* err) {
   const uint32_t* f = flags + (kind * SH_MAX_WORLD + src) * SH_FLAG_STRIDE;
@@ -119,9 +112,18 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flags, int kind, int s
 
 // Pull: for every source s in `mask` (grid.y = world), wait for its flag, then copy n16 16-byte words from its region at
 // src_off[s] to dst + dst_off16[s].
+// sig_mask != 0: block (0, 0) first publishes this rank's own contribution of the same exchange (see above), so
+// publish + wait + copy is one launch.  Every block of the grid is resident at once (<= 32 x 16 blocks), so the publishing
+// block always runs even while the others spin.
 struct PullJob { size_t src_off[SH_MAX_WORLD]; i64 dst_off16[SH_MAX_WORLD]; i64 n16[SH_MAX_WORLD]; };
 __global__ void __launch_bounds__(256) pull_kernel(PeerPtrs regions, const uint32_t* flags, uint32_t mask, int kind, const uint32_t* epoch,
-                                                   uint4* __restrict__ dst, PullJob job, uint32_t* err) {
+                                                   uint4* __restrict__ dst, PullJob job, uint32_t* err, size_t flags_off, uint32_t sig_mask,
+                                                   int my_rank) {
+  if (sig_mask != 0 && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < SH_MAX_WORLD && ((sig_mask >> threadIdx.x) & 1)) {
+    __threadfence_system();
+    uint32_t* f = reinterpret_cast<uint32_t*>(regions.p[threadIdx.x] + flags_off) + (kind * SH_MAX_WORLD + my_rank) * SH_FLAG_STRIDE;
+    st_release_sys(f, *epoch);
+  }
   const int s = blockIdx.y;
   if (!((mask >> s) & 1)) return;
   if (threadIdx.x == 0) wait_flag(flags, kind, s, *epoch, err);
@@ -159,13 +161,29 @@ __global__ void __launch_bounds__(256) landmark_gather_finish_kernel(PeerPtrs re
   *reinterpret_cast<float2*>((is_k ? k_lm : q_lm) + o) = make_float2(a, b);
   *reinterpret_cast<uint32_t*>((is_k ? klm16 : qlm16) + o) = pack_f16x2(a, b);
 }
-// first / last 16 rows of v [8, rows, 64] fp16 -> edges [2][8][16][64]
-__global__ void __launch_bounds__(256) v_edges_kernel(const __half* __restrict__ v, i64 rows, __half* __restrict__ edges) {
-  const int i = blockIdx.x * 256 + threadIdx.x;          // uint4 index: 2 * 8 * 16 * 8
-  if (i >= 2 * TM_HEADS * 16 * 8) return;
-  const int c = i & 7, t = (i >> 3) & 15, h = (i >> 7) & 7, e = i >> 10;
-  const i64 row = e == 0 ? t : rows - 16 + t;
-  reinterpret_cast<uint4*>(edges)[i] = reinterpret_cast<const uint4*>(v + ((i64)h * rows + row) * TM_DHEAD)[c];
+// One block, launched behind landmark_sums: publishes the landmark partial sums (flag kind_lm, to lm_mask) at once, then packs
+// the first / last 16 rows of v [8, rows, 64] fp16 into edges [2][8][16][64] of the own region and publishes those (kind_ve,
+// to the neighbours in ve_mask).
+__global__ void __launch_bounds__(1024) publish_layer_kernel(PeerPtrs regions, size_t flags_off, int my_rank, const uint32_t* epoch,
+                                                             uint32_t lm_mask, int kind_lm, uint32_t ve_mask, int kind_ve,
+                                                             const __half* __restrict__ v, i64 rows, __half* __restrict__ edges) {
+  const int t = threadIdx.x;
+  const uint32_t ep = *epoch;
+  if (t < SH_MAX_WORLD && ((lm_mask >> t) & 1)) {
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(regions.p[t] + flags_off) + (kind_lm * SH_MAX_WORLD + my_rank) * SH_FLAG_STRIDE, ep);
+  }
+  if (ve_mask == 0) return;
+  for (int i = t; i < 2 * TM_HEADS * 16 * 8; i += 1024) {      // uint4 index
+    const int c = i & 7, tt = (i >> 3) & 15, h = (i >> 7) & 7, e = i >> 10;
+    const i64 row = e == 0 ? tt : rows - 16 + tt;
+    reinterpret_cast<uint4*>(edges)[i] = reinterpret_cast<const uint4*>(v + ((i64)h * rows + row) * TM_DHEAD)[c];
+  }
+  __syncthreads();
+  if (t < SH_MAX_WORLD && ((ve_mask >> t) & 1)) {
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(regions.p[t] + flags_off) + (kind_ve * SH_MAX_WORLD + my_rank) * SH_FLAG_STRIDE, ep);
+  }
 }
 // up to two plain device copies in one launch (grid.y selects the job)
 __global__ void __launch_bounds__(256) copy2_kernel(const uint4* __restrict__ s0, uint4* __restrict__ d0, i64 n0,
@@ -392,21 +410,16 @@ struct ShCtx {
   uint32_t all_mask, nb_mask;
   cudaStream_t st;
 };
-static int sh_signal(const ShCtx& x, int kind, uint32_t mask) {
-  if (!mask) return TM_OK;
-  signal_kernel<<<1, 32, 0, x.st>>>(x.regions, x.c->L.flags, mask, kind, x.c->rank, x.epoch);
-  TM_LAUNCH_CHECK();
-  return TM_OK;
-}
-static int sh_pull(const ShCtx& x, int kind, uint32_t mask, void* dst, const PullJob& job) {
-  if (!mask) return TM_OK;
+static int sh_pull(const ShCtx& x, int kind, uint32_t mask, void* dst, const PullJob& job, uint32_t sig_mask = 0) {
+  if (!mask && !sig_mask) return TM_OK;
   i64 most = 0;
   for (int s = 0; s < x.c->world; ++s)
     if (((mask >> s) & 1) && job.n16[s] > most) most = job.n16[s];
   int blocks = (int)ceil_div(most, 256 * 8);
   if (blocks < 1) blocks = 1;
   if (blocks > 32) blocks = 32;
-  pull_kernel<<<dim3((unsigned)blocks, (unsigned)x.c->world), 256, 0, x.st>>>(x.regions, x.flags, mask, kind, x.epoch, (uint4*)dst, job, x.err);
+  pull_kernel<<<dim3((unsigned)blocks, (unsigned)x.c->world), 256, 0, x.st>>>(x.regions, x.flags, mask, kind, x.epoch, (uint4*)dst, job, x.err,
+                                                                              x.c->L.flags, sig_mask, x.c->rank);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
@@ -426,16 +439,11 @@ static int sh_layer(const ShCtx& x, const tm_layer_weights& lw, const tm_shard_p
   // landmark partial sums -> own region -> everyone
   prof_mark(ST_LANDMARKS, st);
   TM_PROPAGATE(tm_landmark_sums16_fwd(q16, k16, 1, s.rows, s.row0, s.bag.l, (float*)(x.own + c->L.lm[li]), st));
+  // publish them; the same launch packs the res_conv halo rows of v for the neighbours (consumed late in the layer)
   prof_mark(ST_X_LANDMARKS, st);
-  TM_PROPAGATE(sh_signal(x, FL_LM0 + li, x.all_mask));
-  // res_conv halo rows -> own region -> neighbours (consumed late in the layer)
-  if (x.nb_mask) {
-    prof_mark(ST_X_CONV_HALO, st);
-    v_edges_kernel<<<8, 256, 0, st>>>((const __half*)v16, s.rows, (__half*)(x.own + c->L.ve[li]));
-    TM_LAUNCH_CHECK();
-    TM_PROPAGATE(sh_signal(x, FL_VE0 + li, x.nb_mask));
-  }
-  prof_mark(ST_X_LANDMARKS, st);
+  publish_layer_kernel<<<1, 1024, 0, st>>>(x.regions, c->L.flags, rank, x.epoch, x.all_mask, FL_LM0 + li, x.nb_mask, FL_VE0 + li,
+                                           (const __half*)v16, s.rows, (__half*)(x.own + c->L.ve[li]));
+  TM_LAUNCH_CHECK();
   {
     GroupRanges gr;
     memset(&gr, 0, sizeof(gr));
@@ -466,13 +474,12 @@ static int sh_layer(const ShCtx& x, const tm_layer_weights& lw, const tm_shard_p
   prof_mark(ST_ATTN3V, st);
   TM_PROPAGATE(attn3v_tc_partial_budget(qlm16, k16, v16, 1, s.rows, (float*)(x.own + c->L.a3[li]), ws + L.a3_s, overlap ? 4 * TM_HEADS : 0, st));
   prof_mark(ST_X_ATTN3V, st);
-  TM_PROPAGATE(sh_signal(x, FL_A30 + li, x.all_mask));
   {
     PullJob job;
     memset(&job, 0, sizeof(job));
     const i64 n16 = (i64)(a3_partial_bytes() / 16);
     for (int r = 0; r < world; ++r) { job.src_off[r] = c->L.a3[li]; job.dst_off16[r] = r * n16; job.n16[r] = n16; }
-    TM_PROPAGATE(sh_pull(x, FL_A30 + li, x.all_mask, ws + L.a3_gather, job));
+    TM_PROPAGATE(sh_pull(x, FL_A30 + li, x.all_mask, ws + L.a3_gather, job, x.all_mask));   // publish own partial + gather all
   }
   prof_mark(ST_ATTN3V, st);
   TM_PROPAGATE(tm_attn3v_merge_fwd(ws + L.a3_gather, world, 1, ws + L.W3, st));
@@ -600,7 +607,6 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
                                                (const uint4*)(toks + (s.ntok - s.n_up) * TM_DIM), (uint4*)(x.own + comm->L.ppeg_hi), n_up16);
       TM_LAUNCH_CHECK();
     }
-    TM_PROPAGATE(sh_signal(x, FL_PPEG, x.nb_mask));
     PullJob job;
     memset(&job, 0, sizeof(job));
     if (rank > 0) { job.src_off[rank - 1] = comm->L.ppeg_hi; job.dst_off16[rank - 1] = 0; job.n16[rank - 1] = s.halo_lo * (TM_DIM / 4); }
@@ -609,7 +615,7 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
       job.dst_off16[rank + 1] = (s.halo_lo + s.S_local) * (TM_DIM / 4);
       job.n16[rank + 1] = s.halo_hi * (TM_DIM / 4);
     }
-    TM_PROPAGATE(sh_pull(x, FL_PPEG, x.nb_mask, ext, job));
+    TM_PROPAGATE(sh_pull(x, FL_PPEG, x.nb_mask, ext, job, x.nb_mask));
   }
   prof_mark(ST_PPEG, st);
   TM_PROPAGATE(ppeg_rows_prepacked(&wl, ext + off * TM_DIM, s.y_in0, s.y_in1, s.bag.G, s.tok0, s.tok0 + s.ntok, h2 + off * TM_DIM, ws + L.packed, st));
@@ -620,16 +626,13 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
   TM_PROPAGATE(sh_layer(x, wl.layer2, s, 1, h2, h3, ws, L, flags));
   // final norm + head on the cls row (TransMIL.py:202-204): rank 0, into its region; everyone pulls the logits
   prof_mark(ST_HEAD, st);
-  if (s.has_cls) {
-    TM_PROPAGATE(tm_head_fwd(&wl, h3, 1, s.S_local, (float*)(x.own + comm->L.logits), st));
-    TM_PROPAGATE(sh_signal(x, FL_LOGITS, x.all_mask));
-  }
+  if (s.has_cls) TM_PROPAGATE(tm_head_fwd(&wl, h3, 1, s.S_local, (float*)(x.own + comm->L.logits), st));
   {
     PullJob job;
     memset(&job, 0, sizeof(job));
     prof_mark(ST_X_LOGITS, st);
     job.src_off[0] = comm->L.logits; job.dst_off16[0] = 0; job.n16[0] = ceil_div((i64)w->n_classes * 4, 16);
-    TM_PROPAGATE(sh_pull(x, FL_LOGITS, 1u, ws + L.logits, job));
+    TM_PROPAGATE(sh_pull(x, FL_LOGITS, 1u, ws + L.logits, job, s.has_cls ? x.all_mask : 0u));
   }
   TM_CUDA(cudaMemcpyAsync(logits, ws + L.logits, (size_t)w->n_classes * sizeof(float), cudaMemcpyDeviceToDevice, st));
   prof_mark(ST_END, st);
