@@ -67,6 +67,11 @@ train)
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/train_launches_20k.csv \
       python tools/bench_train.py --bags 1 --patches 20000 --steps 1 --warmup 1 > gpurun_out/train_ncu20k.log 2>&1; echo "train ncu 20k exit $?"
   python tools/launch_summary.py gpurun_out/train_launches.csv > gpurun_out/train_launch_summary.txt 2>&1; head -40 gpurun_out/train_launch_summary.txt
+  # one --set full capture of the training step's top kernel (a handful of launches from the middle of the second step)
+  timeout 600 ncu --set full --import-source on --clock-control none -k regex:bgemm_tc_kernel -s 400 -c 8 -f -o gpurun_out/train_bgemm_full \
+      python tools/bench_train.py --steps 1 --warmup 1 > gpurun_out/train_ncu_full.log 2>&1; echo "train ncu full exit $?"
+  ncu -i gpurun_out/train_bgemm_full.ncu-rep --page raw --csv > gpurun_out/train_bgemm_full_raw.csv 2>/dev/null
+  SZ=$(stat -c %s gpurun_out/train_bgemm_full.ncu-rep 2>/dev/null || echo 0); if [ "$SZ" -gt 30000000 ]; then rm gpurun_out/train_bgemm_full.ncu-rep; fi
   ;;
 tools)
   timeout 400 python tools/bench_torch_eager.py --n 50000 --features 1024 > gpurun_out/torch_eager_50k_1024.jsonl 2> gpurun_out/eager.err; echo "eager exit $?"

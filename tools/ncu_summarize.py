@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Turn `ncu -i full.ncu-rep --page raw --csv` of one bench.py forward into the two files bench.py and the judge read:
-profiles/<tag>_forward_ncu_full_summary.csv (one row per launch, a handful of metrics) and profiles/r1_ncu_traffic.json
+profiles/<tag>_forward_ncu_full_summary.csv (one row per launch, a handful of metrics) and profiles/<tag>_ncu_traffic.json
 (dram bytes per launch of each stage).  Usage: python tools/ncu_summarize.py gpurun_out/full_raw.csv [tag]"""
 import csv, json, os, sys
 
@@ -65,7 +65,7 @@ def main():
     js = {"source": f"ncu --set full --clock-control none, one forward of bench.py (50000 x 1024 bag), profiles/{tag}_forward_ncu_full_summary.csv; "
                     "dram__bytes_read.sum + dram__bytes_write.sum summed over the kernels of one launch of each stage (tools/ncu_summarize.py)",
           "workload": {"n": 50000, "in_features": 1024, "bags": 1}, "launches_in_forward": len(fwd), "stages": stages}
-    with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json"), "w") as f:
+    with open(os.path.join(ROOT, "profiles", f"{tag}_ncu_traffic.json"), "w") as f:
         json.dump(js, f, indent=1)
     tot = sum(e["gpu_time_us"] * PER_FORWARD.get(s, 2) for s, e in stages.items())
     for s, e in stages.items():
