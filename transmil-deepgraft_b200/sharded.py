@@ -406,14 +406,31 @@ class PeerComm:
             raise ValueError(f"token sharding supports up to {capi.TM_SHARD_MAX_WORLD} ranks")
         self.handle = C.c_void_p()
         with torch.cuda.device(dev):
-            capi.check(L.tm_shard_comm_create(self.rank, self.world, self.max_n, C.byref(self.handle)))
+            # every step is followed by an exchange of "did it work here", so a failure on one rank (no peer access, IPC refused
+            # in a container) raises on EVERY rank instead of leaving the others waiting in a collective
+            err, mine = None, (C.c_ubyte * capi.TM_SHARD_HANDLE_BYTES)()
+            try:
+                capi.check(L.tm_shard_comm_create(self.rank, self.world, self.max_n, C.byref(self.handle)))
+                if self.world > 1:
+                    capi.check(L.tm_shard_comm_handle(self.handle, mine))
+            except Exception as e:      # noqa: BLE001
+                err = f"rank {self.rank}: {e}"
             if self.world > 1:
-                mine = (C.c_ubyte * capi.TM_SHARD_HANDLE_BYTES)()
-                capi.check(L.tm_shard_comm_handle(self.handle, mine))
                 blobs = [None] * self.world
-                dist.all_gather_object(blobs, bytes(mine))
-                capi.check(L.tm_shard_comm_attach(self.handle, b"".join(blobs)))
-                dist.barrier()          # nobody starts a forward before every rank has mapped every region
+                dist.all_gather_object(blobs, (err, bytes(mine)))
+                errs = [b[0] for b in blobs if b[0]]
+                if not errs:
+                    try:
+                        capi.check(L.tm_shard_comm_attach(self.handle, b"".join(b[1] for b in blobs)))
+                    except Exception as e:      # noqa: BLE001
+                        err = f"rank {self.rank}: {e}"
+                    errs2 = [None] * self.world
+                    dist.all_gather_object(errs2, err)     # also the barrier: nobody starts a forward before every region is mapped
+                    errs = [e for e in errs2 if e]
+                err = "; ".join(errs) if errs else None
+            if err:
+                self.close()
+                raise capi.TransmilError(f"token-sharded TransMIL: peer-memory transport unavailable ({err}); use transport='nccl'")
 
     def status(self):
         """0, or 1 + the index of the exchange whose producer timed out since the last call (synchronises the device)."""
