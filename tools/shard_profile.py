@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--patches", type=int, default=200000)
     ap.add_argument("--features", type=int, default=2048)
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--nccl", action="store_true", help="also time the Python-issued NCCL schedule")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -49,12 +50,19 @@ def main():
         return float(t[0])
 
     with torch.no_grad():
+        def note(msg):
+            print(f"[rank {rank}] {msg}", file=sys.stderr, flush=True)
         eager = TokenShardedTransMIL(model)
         x = eager.plan(n).take(x_full, rank).to(dev)
+        note("peer comm up, timing eager")
         out["peer_eager_ms"] = timed(eager, x)
+        note(f"eager {out['peer_eager_ms']:.3f} ms, status {eager.comm.status()}")
         graphed = TokenShardedTransMIL(model, cuda_graph=True)
         out["peer_graph_ms"] = timed(graphed, x)
-        out["nccl_ms"] = timed(TokenShardedTransMIL(model, transport="nccl"), x)
+        note(f"graph {out['peer_graph_ms']:.3f} ms, status {graphed.comm.status()}")
+        if a.nccl:
+            out["nccl_ms"] = timed(TokenShardedTransMIL(model, transport="nccl"), x)
+        note("variants done, stage profile")
         # stage profile (events serialise the side stream: the sum is the no-overlap time)
         L.tm_profile_enable(1)
         T.capi.profile_read()
