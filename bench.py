@@ -308,7 +308,7 @@ def token_shard_measure(n, features, classes, steps, warmup, rank, world, dev, b
             dist.all_reduce(nr)
             res["comm_nranks_seen"] = int(nr.item())
             try:
-                graphed = TokenShardedTransMIL(model, cuda_graph=True)
+                graphed = TokenShardedTransMIL(model, cuda_graph=True, static_input=True)   # replays read x_dev in place
                 eager = TokenShardedTransMIL(model)
             except T.capi.TransmilError as e:          # raised on every rank together (PeerComm): report the NCCL form alone
                 graphed = None

@@ -11,17 +11,31 @@
 
 namespace tmil {
 
-// One warp per (tensor, bh, group): sum of the local rows that fall into global group g = (row0 + r) / l.
-// sums [2][nbh][256][64] fp32; groups with no local row get zeros (so the cross-rank sum is the plain allreduce).
+// One block of 8 warps per (local landmark group, tensor, bh): sum of the local rows that fall into global group
+// g = (row0 + r) / l.  A rank holds rows / l + 1 groups of l rows each (l = 782 for a 200 k bag), so the rows of a group are
+// spread over the 8 warps (4 rows per warp and step: 8 lanes x 16 bytes per row) and reduced through shared memory in a fixed
+// order.  The trailing `zero_blocks` blocks clear the groups without a local row (sums [2][nbh][256][64] fp32 is complete, so
+// the cross-rank sum may also be a plain allreduce).
 __global__ void __launch_bounds__(256) landmark_sums16_kernel(const __half* __restrict__ q, const __half* __restrict__ k, int nbh,
-                                                              long long rows, long long row0, int l, float* __restrict__ sums) {
-  const long long gid = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
-  const long long per_tensor = (long long)nbh * TM_LANDMARKS;
-  if (gid >= 2 * per_tensor) return;
-  const int lane = threadIdx.x & 31, lane8 = lane & 7, phase = lane >> 3;
-  const bool is_k = gid >= per_tensor;
-  const long long rem = is_k ? gid - per_tensor : gid;
-  const long long bh = rem / TM_LANDMARKS, g = rem % TM_LANDMARKS;
+                                                              long long rows, long long row0, int l, int g_lo, int n_groups,
+                                                              float* __restrict__ sums) {
+  __shared__ float part[8][TM_DHEAD];
+  const int active = n_groups * 2 * nbh;
+  if ((int)blockIdx.x >= active) {
+    // zero fill: groups outside [g_lo, g_lo + n_groups), 16 floats per thread step
+    const long long total = 2ll * nbh * TM_LANDMARKS * (TM_DHEAD / 4);
+    const int zb = gridDim.x - active;
+    for (long long i = (long long)(blockIdx.x - active) * 256 + threadIdx.x; i < total; i += (long long)zb * 256) {
+      const int g = (int)((i / (TM_DHEAD / 4)) % TM_LANDMARKS);
+      if (g < g_lo || g >= g_lo + n_groups) reinterpret_cast<float4*>(sums)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    return;
+  }
+  const int gl = blockIdx.x / (2 * nbh), tb = blockIdx.x % (2 * nbh);
+  const bool is_k = tb >= nbh;
+  const int bh = is_k ? tb - nbh : tb;
+  const long long g = g_lo + gl;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lane8 = lane & 7, phase = lane >> 3;
   long long lo = g * l - row0, hi = (g + 1) * l - row0;
   if (lo < 0) lo = 0;
   if (hi > rows) hi = rows;
@@ -29,9 +43,9 @@ __global__ void __launch_bounds__(256) landmark_sums16_kernel(const __half* __re
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
   if (lo < hi) {
-    const uint4* src = reinterpret_cast<const uint4*>((is_k ? k : q) + (bh * rows + lo) * TM_DHEAD) + lane8;
+    const uint4* src = reinterpret_cast<const uint4*>((is_k ? k : q) + ((long long)bh * rows + lo) * TM_DHEAD) + lane8;
     const long long cnt = hi - lo;
-    for (long long j = phase; j < cnt; j += 4) {
+    for (long long j = warp * 4 + phase; j < cnt; j += 32) {
       const uint4 u = __ldg(src + j * 8);
       const __half2* h2 = reinterpret_cast<const __half2*>(&u);
 #pragma unroll
@@ -46,10 +60,17 @@ __global__ void __launch_bounds__(256) landmark_sums16_kernel(const __half* __re
     acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
     acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
   }
-  if (phase != 0) return;
-  float4* dst = reinterpret_cast<float4*>(sums + gid * TM_DHEAD) + lane8 * 2;
-  dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-  dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  if (phase == 0) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) part[warp][lane8 * 8 + e] = acc[e];
+  }
+  __syncthreads();
+  if (threadIdx.x < TM_DHEAD) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += part[w][threadIdx.x];
+    sums[(((long long)(is_k ? nbh : 0) + bh) * TM_LANDMARKS + g) * TM_DHEAD + threadIdx.x] = s;
+  }
 }
 
 // means = sums / l, plus the fp16 operand copies (same outputs as landmarks16_kernel).
@@ -99,9 +120,14 @@ extern "C" int tm_landmark_sums16_fwd(const void* q16, const void* k16, int64_t 
                                       float* sums, void* stream) {
   TM_CHECK_ARG(B > 0 && rows > 0 && row0 >= 0 && l > 0, TM_ERR_BAD_SHAPE, "tm_landmark_sums16_fwd: bad shape");
   TM_CHECK_ARG(aligned16(q16) && aligned16(k16) && aligned16(sums), TM_ERR_BAD_ALIGNMENT, "tm_landmark_sums16_fwd: pointers must be 16-byte aligned");
-  const long long groups = 2ll * B * TM_HEADS * TM_LANDMARKS;
-  landmark_sums16_kernel<<<(unsigned)ceil_div(groups, 8), 256, 0, (cudaStream_t)stream>>>((const __half*)q16, (const __half*)k16,
-                                                                                         (int)(B * TM_HEADS), rows, row0, (int)l, sums);
+  TM_CHECK_ARG(B * TM_HEADS <= 16384, TM_ERR_BAD_SHAPE, "tm_landmark_sums16_fwd: too many bags");
+  const int64_t g_lo = row0 / l;
+  int64_t g_hi = (row0 + rows - 1) / l;
+  if (g_hi > TM_LANDMARKS - 1) g_hi = TM_LANDMARKS - 1;
+  const int n_groups = g_lo <= g_hi ? (int)(g_hi - g_lo + 1) : 0;
+  const int nbh = (int)(B * TM_HEADS);
+  landmark_sums16_kernel<<<(unsigned)(n_groups * 2 * nbh + 64), 256, 0, (cudaStream_t)stream>>>((const __half*)q16, (const __half*)k16, nbh,
+                                                                                                 rows, row0, (int)l, (int)g_lo, n_groups, sums);
   TM_LAUNCH_CHECK();
   return TM_OK;
 }

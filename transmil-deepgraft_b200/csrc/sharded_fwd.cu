@@ -131,7 +131,14 @@ __global__ void __launch_bounds__(256) pull_kernel(PeerPtrs regions, const uint3
   const uint4* from = reinterpret_cast<const uint4*>(regions.p[s] + job.src_off[s]);
   uint4* to = dst + job.dst_off16[s];
   const i64 n16 = job.n16[s];
-  for (i64 i = (i64)blockIdx.x * 256 + threadIdx.x; i < n16; i += (i64)gridDim.x * 256) to[i] = ld_peer16(from + i);
+  // four loads in flight per thread: a 3.6 MB PPEG halo over NVLink is latency x concurrency bound, not link bound
+  const i64 stride = (i64)gridDim.x * 256;
+  i64 i = (i64)blockIdx.x * 256 + threadIdx.x;
+  for (; i + 3 * stride < n16; i += 4 * stride) {
+    const uint4 a = ld_peer16(from + i), b = ld_peer16(from + i + stride), c = ld_peer16(from + i + 2 * stride), d = ld_peer16(from + i + 3 * stride);
+    to[i] = a; to[i + stride] = b; to[i + 2 * stride] = c; to[i + 3 * stride] = d;
+  }
+  for (; i < n16; i += stride) to[i] = ld_peer16(from + i);
 }
 
 // Landmark means straight from the peers' regions: group g of (tensor, head) receives the partial sums of the ranks whose
@@ -417,7 +424,8 @@ static int sh_pull(const ShCtx& x, int kind, uint32_t mask, void* dst, const Pul
     if (((mask >> s) & 1) && job.n16[s] > most) most = job.n16[s];
   int blocks = (int)ceil_div(most, 256 * 8);
   if (blocks < 1) blocks = 1;
-  if (blocks > 32) blocks = 32;
+  const int cap = 592 / x.c->world > 16 ? 592 / x.c->world : 16;     // the whole grid stays resident (4 CTAs of 256 threads per SM)
+  if (blocks > cap) blocks = cap;
   pull_kernel<<<dim3((unsigned)blocks, (unsigned)x.c->world), 256, 0, x.st>>>(x.regions, x.flags, mask, kind, x.epoch, (uint4*)dst, job, x.err,
                                                                               x.c->L.flags, sig_mask, x.c->rank);
   TM_LAUNCH_CHECK();
@@ -603,7 +611,7 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
     const float* toks = h1 + off * TM_DIM;
     const i64 n_dn16 = s.n_dn * (TM_DIM / 4), n_up16 = s.n_up * (TM_DIM / 4);
     if (n_dn16 || n_up16) {
-      copy2_kernel<<<dim3(64, 2), 256, 0, st>>>((const uint4*)toks, (uint4*)(x.own + comm->L.ppeg_lo), n_dn16,
+      copy2_kernel<<<dim3(148, 2), 256, 0, st>>>((const uint4*)toks, (uint4*)(x.own + comm->L.ppeg_lo), n_dn16,
                                                (const uint4*)(toks + (s.ntok - s.n_up) * TM_DIM), (uint4*)(x.own + comm->L.ppeg_hi), n_up16);
       TM_LAUNCH_CHECK();
     }

@@ -459,11 +459,13 @@ class TokenShardedTransMIL:
 
     transport="peer" (default): ONE library call per bag, tm_transmil_fwd_sharded -- the whole per-rank schedule and the
     exchanges (flag-guarded pulls over NVLink peer memory) are issued by the library on the current stream; with
-    cuda_graph=True the call is captured once per bag size and replayed (any world size).
+    cuda_graph=True the call is captured once per bag size and replayed (any world size); a host bag is copied straight into
+    the graph's input buffer (one H2D), a device bag is copied into it too unless static_input=True and it is the very
+    tensor the graph was captured on (a caller that refills one device buffer per bag: no copy at all).
     transport="nccl": the schedule is issued from Python (`sharded_forward`) kernel by kernel with torch.distributed
     collectives in between -- the cross-check of the peer path, and the form the gloo CPU tests drive."""
 
-    def __init__(self, model, cuda_graph=False, transport="peer", max_n=1 << 20):
+    def __init__(self, model, cuda_graph=False, transport="peer", max_n=1 << 20, static_input=False):
         if model.training:
             raise NotImplementedError("token-sharded path: inference only (model.eval())")
         if transport not in ("peer", "nccl"):
@@ -477,6 +479,7 @@ class TokenShardedTransMIL:
             if self.dev.type != "cuda":
                 raise capi.TransmilError("token-sharded TransMIL needs the model on a CUDA device; there is no CPU path")
             self.cuda_graph = bool(cuda_graph)
+            self.static_input = bool(static_input)
             self.comm = PeerComm(max_n, self.dev)
             self._cplans, self._ws, self._w = {}, None, None
             return
@@ -542,9 +545,21 @@ class TokenShardedTransMIL:
         cplan = self._cplans.get(n)
         if cplan is None:
             cplan = self._cplans[n] = shard_plan_c(n, plan.world, rank)
-        x = x.to(device=self.dev, dtype=torch.float32, non_blocking=True).contiguous()
         if tuple(x.shape) != (int(cplan.ntok), self.model.in_features):
             raise ValueError(f"rank {rank} expects {int(cplan.ntok)} rows of the bag (plan.take), got {tuple(x.shape)}")
+        state = self._graphs.get(n) if self.cuda_graph else None
+        if isinstance(state, dict):
+            # replay: the graph reads a fixed device buffer.  A host bag is copied straight into it (one H2D, nothing else); a
+            # device bag that IS that buffer (the graph was captured on the caller's tensor) costs nothing
+            key = tuple(p.data_ptr() for p in self.model.parameters())
+            if state["key"] == key:
+                if not (x.is_cuda and x.data_ptr() == state["x"].data_ptr()):
+                    state["x"].copy_(x, non_blocking=True)
+                state["graph"].replay()
+                return state["logits"].clone()
+            state = self._graphs[n] = None       # a parameter tensor was replaced: the graph holds the old pointers
+        given = x
+        x = x.to(device=self.dev, dtype=torch.float32, non_blocking=True).contiguous()
         if not self.cuda_graph:
             logits = torch.empty(1, self.model.n_classes, device=self.dev)
             self._peer_call(cplan, x, logits)
@@ -552,9 +567,6 @@ class TokenShardedTransMIL:
         # the captured call reads the parameters through their pointers at replay time (operand copies are re-derived inside
         # the graph), so in-place updates need nothing; a REPLACED parameter tensor needs a new capture
         key = tuple(p.data_ptr() for p in self.model.parameters())
-        state = self._graphs.get(n)
-        if isinstance(state, dict) and state["key"] != key:
-            state = None
         if state is None:
             # first call of a bag size: eager (loads the kernels, sizes the workspace) -- then capture.  All ranks take the
             # same branch because they see the same sequence of bag sizes.
@@ -562,14 +574,17 @@ class TokenShardedTransMIL:
             self._peer_call(cplan, x, logits)
             self._graphs[n] = "eager"
             return logits
-        if state == "eager":
-            sx, sl = x.clone(), torch.empty(1, self.model.n_classes, device=self.dev)
-            torch.cuda.synchronize(self.dev)
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._peer_call(cplan, sx, sl)
-            state = self._graphs[n] = dict(graph=g, x=sx, logits=sl, key=key, w=self._w)
-        state["x"].copy_(x, non_blocking=True)
+        # second call of a bag size: capture, on a private copy of the input -- or, with static_input=True, ON the caller's device
+        # tensor (kept alive here): a caller that refills one buffer per bag then replays with no copy at all, and any OTHER
+        # input passed later is copied into that tensor
+        mine = not (given.is_cuda and given.data_ptr() == x.data_ptr())
+        sx = x if (mine or self.static_input) else x.clone()
+        sl = torch.empty(1, self.model.n_classes, device=self.dev)
+        torch.cuda.synchronize(self.dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._peer_call(cplan, sx, sl)
+        state = self._graphs[n] = dict(graph=g, x=sx, logits=sl, key=key, w=self._w)
         state["graph"].replay()
         return state["logits"].clone()
 
