@@ -213,8 +213,13 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         uint32_t pk[16];
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
-          const float p0 = ex2_approx(fmaf(__uint_as_float(cur[2 * e]), NT_LOG2E, -ml));
-          const float p1 = ex2_approx(fmaf(__uint_as_float(cur[2 * e + 1]), NT_LOG2E, -ml));
+          float p0, p1;
+          if (e % 3 == 2) {    // 5 of 16 pairs on the FMA pipe, 11 on the MUFU pipe
+            ex2_poly_pair(fmaf(__uint_as_float(cur[2 * e]), NT_LOG2E, -ml), fmaf(__uint_as_float(cur[2 * e + 1]), NT_LOG2E, -ml), p0, p1);
+          } else {
+            p0 = ex2_approx(fmaf(__uint_as_float(cur[2 * e]), NT_LOG2E, -ml));
+            p1 = ex2_approx(fmaf(__uint_as_float(cur[2 * e + 1]), NT_LOG2E, -ml));
+          }
           s4[e & 3] += p0 + p1;
           pk[e] = pack_f16x2(p0, p1);
         }

@@ -221,6 +221,41 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
+// 2^y for a PAIR of non-positive exponents on the FMA pipe (no MUFU): y is clamped to >= -125, split by the magic-number add
+// into n = round(y) and f = y - n in [-0.5, 0.5], 2^f is a degree-3 minimax polynomial (relative error 7.6e-5, 6x below the
+// fp16 half-ulp of the probabilities it feeds) evaluated with packed fma.rn.f32x2 (FFMA2), and 2^n goes into the exponent
+// field by an integer add.  The attention kernels send about a third of their exponentials here: the MUFU pipe (16 ex2 per
+// clock and SM) is what bounds their softmax phase.
+__device__ __forceinline__ unsigned long long tm_pack2(float lo, float hi) {
+  unsigned long long d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(__float_as_uint(lo)), "r"(__float_as_uint(hi)));
+  return d;
+}
+__device__ __forceinline__ unsigned long long tm_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned long long tm_add2(unsigned long long a, unsigned long long b) {
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ void ex2_poly_pair(float y0, float y1, float& p0, float& p1) {
+  constexpr float MAGIC = 12582912.0f;   // 1.5 * 2^23: the low mantissa bits of y + MAGIC hold round(y)
+  const unsigned long long y = tm_pack2(fmaxf(y0, -125.0f), fmaxf(y1, -125.0f));
+  const unsigned long long t = tm_add2(y, tm_pack2(MAGIC, MAGIC));
+  const unsigned long long n = tm_add2(t, tm_pack2(-MAGIC, -MAGIC));
+  const unsigned long long f = tm_fma2(n, tm_pack2(-1.0f, -1.0f), y);
+  unsigned long long p = tm_fma2(tm_pack2(0.055217594f, 0.055217594f), f, tm_pack2(0.24261497f, 0.24261497f));
+  p = tm_fma2(p, f, tm_pack2(0.69325256f, 0.69325256f));
+  p = tm_fma2(p, f, tm_pack2(0.99992758f, 0.99992758f));
+  uint32_t t0, t1, q0, q1;
+  asm("mov.b64 {%0, %1}, %2;" : "=r"(t0), "=r"(t1) : "l"(t));
+  asm("mov.b64 {%0, %1}, %2;" : "=r"(q0), "=r"(q1) : "l"(p));
+  p0 = __uint_as_float(q0 + (t0 << 23));
+  p1 = __uint_as_float(q1 + (t1 << 23));
+}
 // mbarrier try_wait with a suspend-time hint free spin (many waiters per barrier in the attention kernels)
 __device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
