@@ -15,6 +15,9 @@
 
 #include "common.cuh"
 #include "tc_common.cuh"
+#ifndef TM_POLY_A3
+#define TM_POLY_A3 (false)   // which exponential pairs (e = 0..15 of a 32-column chunk) use ex2_poly_pair: none here -- measured on B200, any share made this kernel slower (64.5 us -> 66.9 with 5 of 16, 67.3 with 4 of 16); nystrom_out gains (68.0 -> 59.6)
+#endif
 
 namespace tmil {
 
@@ -198,7 +201,7 @@ attn3v_tc_kernel(const __grid_constant__ CUtensorMap tmQlm, const __grid_constan
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           float p0, p1;
-          if (e % 3 == 2) {    // 5 of 16 pairs on the FMA pipe, 11 on the MUFU pipe
+          if (TM_POLY_A3) {    // some of the 16 pairs on the FMA pipe, the rest on the MUFU pipe
             ex2_poly_pair(fmaf(__uint_as_float(r[2 * e]), A3_LOG2E, -ml), fmaf(__uint_as_float(r[2 * e + 1]), A3_LOG2E, -ml), p0, p1);
           } else {
             p0 = ex2_approx(fmaf(__uint_as_float(r[2 * e]), A3_LOG2E, -ml));

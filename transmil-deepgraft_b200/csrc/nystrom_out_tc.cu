@@ -14,6 +14,9 @@
 
 #include "common.cuh"
 #include "tc_common.cuh"
+#ifndef TM_POLY_NO
+#define TM_POLY_NO (e % 3 == 2)   // which exponential pairs (e = 0..15 of a 32-column chunk) use ex2_poly_pair
+#endif
 
 namespace tmil {
 
@@ -214,7 +217,7 @@ nystrom_out_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           float p0, p1;
-          if (e % 3 == 2) {    // 5 of 16 pairs on the FMA pipe, 11 on the MUFU pipe
+          if (TM_POLY_NO) {    // some of the 16 pairs on the FMA pipe, the rest on the MUFU pipe
             ex2_poly_pair(fmaf(__uint_as_float(cur[2 * e]), NT_LOG2E, -ml), fmaf(__uint_as_float(cur[2 * e + 1]), NT_LOG2E, -ml), p0, p1);
           } else {
             p0 = ex2_approx(fmaf(__uint_as_float(cur[2 * e]), NT_LOG2E, -ml));
