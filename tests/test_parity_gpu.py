@@ -65,31 +65,42 @@ def test_every_stage_against_oracle(T, D, nc, n, B, gen, engine):
     sd = {k: v.cpu() for k, v in m.state_dict().items()}
     ref, st = O.forward(sd, x, return_stages=True)
     tight = engine == "simt"
-    a = 2e-5 if tight else 2e-3
+    # Per-stage budgets RELATIVE to the stage's largest entry, about 3x the worst value tools/stage_budget.py measured on a B200
+    # over these bags plus a 6 000- and a 20 000-patch one (profiles/r2/stage_budget.txt).  Tensor-core engine: every stage
+    # 2.8e-4 ... 8.2e-4 except the pseudo-inverse (fp16-operand chain, 5.6e-3); fp32 engine: <= 1.8e-6, pseudo-inverse 1.2e-5.
+    rel = 6e-6 if tight else 2.5e-3
+    rel_z = 4e-5 if tight else 1.5e-2
+
+    def close_rel(got, want, r, what):
+        got, want = got.detach().double().cpu(), want.detach().double().cpu()
+        err, mx = (got - want).abs().max().item(), want.abs().max().item()
+        assert err <= r * mx, f"{what}: {err:.3e} > {r:.1e} x max|ref| {mx:.3e} ({engine} engine)"
+
     p = O.plan(n)
     # index contract, bit-exact: cls row, duplicate-pad rows, front zero-pad rows
     h0 = m.stage("h0")
     assert torch.equal(h0[:, 0].cpu(), sd["cls_token"][0].expand(B, -1))
     if p["dup"] > 0:
         assert torch.equal(h0[:, 1 + n:1 + n + p["dup"]], h0[:, 1:1 + p["dup"]])
-    _close(h0, st["h0"], a * 5)
+    close_rel(h0, st["h0"], rel, "h0")
     for name, key in (("q_lm1", "q_lm"), ("k_lm1", "k_lm"), ("attn21", "attn2"), ("W31", "W3")):
-        _close(m.stage(name), st["layer1"][key], a)
-    _close(m.stage("Z1"), st["layer1"]["Z"], a * 50, rtol=1e-3 if not tight else 1e-4)
-    _close(m.stage("h1"), st["h1"], a * 5)
-    _close(m.stage("h2"), st["h2"], a * 10)
+        close_rel(m.stage(name), st["layer1"][key], rel, name)
+    close_rel(m.stage("Z1"), st["layer1"]["Z"], rel_z, "Z1")
+    close_rel(m.stage("h1"), st["h1"], rel, "h1")
+    close_rel(m.stage("h2"), st["h2"], rel, "h2")
     l2 = st["layer2"]
     if l2["P"] > 0:
         for name in ("xn", "q", "k", "v"):
             t = m.stage(name)
             pad = t[:, :l2["P"]] if name == "xn" else t[:, :, :l2["P"]]
             assert float(pad.abs().max()) == 0.0, f"front-pad rows of {name} must be exactly zero"
-    _close(m.stage("xn")[:, l2["P"]:], st["layer2"]["xn"], a * 5)
+    close_rel(m.stage("xn")[:, l2["P"]:], st["layer2"]["xn"], rel, "xn")
     for name in ("q", "k", "v"):
-        _close(m.stage(name), l2[name], a * 5)
-    _close(m.stage("merged"), l2["merged"], a * 5)
-    _close(m.stage("h3")[:, 0], st["h3"][:, 0], a * 10)
-    _close(logits, ref, LOGIT_TOL if not tight else 5e-5)
+        close_rel(m.stage(name), l2[name], rel, name)
+    close_rel(m.stage("merged"), l2["merged"], rel, "merged")
+    close_rel(m.stage("Z"), l2["Z"], rel_z, "Z")
+    close_rel(m.stage("h3")[:, 0], st["h3"][:, 0], rel, "h3 cls row")
+    _close(logits, ref, LOGIT_TOL if not tight else 5e-6)
 
 
 def test_host_buffer_abi_and_data_kwarg(T):
