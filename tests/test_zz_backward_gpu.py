@@ -1,8 +1,7 @@
 """GPU suite of the backward, sorted last on purpose: the nvcc build of csrc/backward.cu and the autograd
 path of the drop-in module against the float64 backward oracle on the same seeded bags.
 
-Status note: this file was written in a session that had no GPU minutes left; the kernel source had only been executed
-through the host harness (tests/test_backward_emu.py) when it was committed.  /root/reference is never read here.
+Both engines of the backward run every test (fixture `engine`).  /root/reference is never read here.
 """
 import ctypes as C
 
@@ -16,9 +15,10 @@ from oracle import transmil_oracle as O
 pytestmark = pytest.mark.gpu
 # max-abs error of a gradient tensor relative to its largest entry, vs the float64 backward oracle, per engine of the backward
 # contractions (tm_bgemm_engine): the fp32 CUDA-core kernels, and the tcgen05 engine (tf32 operands -- 10-bit mantissas -- with
-# fp32 accumulation, on top of the fp16/tf32 tensor-core forward).  Budgets measured with tools/grad_budget.py
-# (profiles/r2_grad_budget.txt).
-GRAD_RTOL = {"simt": 5e-4, "tc": 5e-3}
+# fp32 accumulation, on top of the fp16/tf32 tensor-core forward whose kept stages xn, q, k, v, merged are fp16).  Measured on
+# B200 with tools/grad_budget.py over the bags below (profiles/r2/grad_budget.txt): fp32 engine worst parameter 4.0e-6
+# (median 1e-6), tensor-core engine worst 4.3e-3 (LayerNorm / bias gradients; median 2e-3).  Budgets = measured x 2.3 ... 5.
+GRAD_RTOL = {"simt": 2e-5, "tc": 1e-2}
 ENGINES = {"simt": 1, "tc": 0}
 
 

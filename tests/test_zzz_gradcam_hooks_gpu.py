@@ -45,10 +45,10 @@ def test_hook_on_layer2_norm_sees_activation_and_gradient(built_lib):
     (out * dlogits.double()).sum().backward()
     assert seen["act"].shape == (B, O.plan(n)["S"], 512) and seen["act"].is_cuda
     _close(seen["act"], xn, 1e-3, "hooked activation")   # the tensor-core forward keeps LayerNorm's output as fp16 (11-bit mantissa)
-    _close(seen["grad"], xn.grad, 5e-3, "gradient of the hooked activation")
+    _close(seen["grad"], xn.grad, 1e-2, "gradient of the hooked activation")
     ref, _ = OB.backward(sd, x, dlogits.double())
     for k, p in m.named_parameters():
-        _close(p.grad, ref[k].reshape(p.shape), 5e-3, k)
+        _close(p.grad, ref[k].reshape(p.shape), 1e-2, k)   # tensor-core engine: measured worst 4.3e-3 (profiles/r2/grad_budget.txt)
     handle.remove()
     with torch.no_grad():
         assert not m(x.cuda()).requires_grad            # back on the inference path

@@ -9,7 +9,7 @@ from oracle import transmil_backward as OB
 from oracle import transmil_oracle as O
 
 pytestmark = pytest.mark.gpu
-GRAD_RTOL = 5e-3
+GRAD_RTOL = 1e-2   # tensor-core engine: measured worst 4.3e-3 (profiles/r2/grad_budget.txt)
 
 
 def test_768_stem_parameter_gradients(built_lib):
