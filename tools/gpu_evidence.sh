@@ -7,7 +7,7 @@
 #   gpurun --timeout 900  -- 'bash tools/gpu_evidence.sh train'          training step: numbers + ncu launch lists
 #   gpurun --timeout 900  -- 'bash tools/gpu_evidence.sh tools'          D6 torch eager, cfg5, files->logits, sweep, budgets
 #   gpurun --gpus N --timeout 1200 -- 'bash tools/gpu_evidence.sh multi N'   bench.py under torchrun + sharded parity tests
-#   gpurun --gpus N --timeout 1200 -- 'bash tools/gpu_evidence.sh shard N'   token-sharded bag: tests + strong-scaling points
+#   gpurun --gpus N --timeout 1200 -- 'bash tools/gpu_evidence.sh shard N'   token-sharded bag: tests + strong-scaling points (shardbench N: the points only)
 #   gpurun --timeout 400 -- 'bash tools/gpu_evidence.sh pinv'             pinv cluster kernel: parity test + time per generation
 #   gpurun --gpus N --timeout 600  -- 'bash tools/gpu_evidence.sh shardprof N [patches]'   per-stage times of the sharded forward
 MODE=${1:-tests}
@@ -89,10 +89,12 @@ multi)
   timeout 600 python -m pytest tests/test_sharded_gpu.py -m gpu -q > gpurun_out/pytest_sharded_n$N.log 2>&1; echo "sharded tests exit $?"
   tail -8 gpurun_out/pytest_sharded_n$N.log
   ;;
-shard)
-  nvidia-smi topo -m 2>/dev/null | head -12
-  timeout 900 python -m pytest tests/test_sharded_gpu.py -m gpu -x -q > gpurun_out/pytest_sharded_n$N.log 2>&1; echo "sharded tests exit $?"
-  tail -15 gpurun_out/pytest_sharded_n$N.log
+shard|shardbench)
+  if [ $MODE = shard ]; then
+    nvidia-smi topo -m 2>/dev/null | head -12
+    timeout 900 python -m pytest tests/test_sharded_gpu.py -m gpu -x -q > gpurun_out/pytest_sharded_n$N.log 2>&1; echo "sharded tests exit $?"
+    tail -15 gpurun_out/pytest_sharded_n$N.log
+  fi
   for D in 2048 1024; do
     timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29556 \
         bench.py --gpus $N --shard tokens --patches 200000 --features $D --steps 20 --warmup 3 > gpurun_out/shard_n${N}_$D.json 2> gpurun_out/shard_n${N}_$D.err
