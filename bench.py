@@ -278,6 +278,7 @@ def token_shard_measure(n, features, classes, steps, warmup, rank, world, dev, b
             torch.cuda.synchronize(dev)
             single_ms = e0.elapsed_time(e1) / steps
             del xd
+        barrier()      # the other ranks stay idle (no host pinning, no collectives spinning) while rank 0 times the single-GPU bag
         if world > 1:
             def timed(sharded, xin, sync_host=False):
                 for _ in range(max(warmup, 3)):
