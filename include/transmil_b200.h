@@ -276,8 +276,9 @@ int tm_ppeg_fwd(const tm_weights* w, const float* h_in, int64_t B, int64_t G, fl
 /* ---- token-sharded single bag (the reference has no counterpart: it runs one bag on one GPU) ----------
  * Every rank holds a contiguous range [row0, row0+rows) of the PADDED token axis of ONE layer, rows % 256 == 0, and runs
  * the per-kernel entry points above on it with B = 1, Sp = rows (rank 0 passes P, the others P = 0).  These entry points
- * produce / consume what crosses rank boundaries; the collectives themselves (NCCL through torch.distributed) are issued
- * by the host side (transmil-deepgraft_b200/sharded.py). */
+ * produce / consume what crosses rank boundaries.  Two hosts use them: tm_transmil_fwd_sharded below (the whole per-rank
+ * schedule with exchanges over NVLink peer memory, one call per rank) and the Python-issued schedule of
+ * transmil-deepgraft_b200/sharded.py with transport="nccl" (collectives through torch.distributed; the cross-check). */
 /* K1 without the duplicate pad / cls row: x_rows [rows,D] -> h_rows [rows,512] (TransMIL.py:175 on a run of rows).
  * scratch: rows*F0 floats for the two-Linear stems. */
 int tm_fc1_rows_fwd(const tm_weights* w, const float* x_rows, int64_t rows, float* h_rows, float* scratch,

@@ -13,11 +13,18 @@ the token axis with a handful of small exchanges per layer, so a 200k-token slid
   * fc1 is row-parallel; the duplicate-pad tail (TransMIL.py:177-180) is recomputed from the first `dup` input rows by the
     rank(s) that own it, so it needs no communication;  * the cls row lives on rank 0: logits there, broadcast at the end.
 
-`ShardPlan` is pure integer arithmetic (testable anywhere).  `sharded_forward` is the host logic: buffers with halo
-room, the collectives (torch.distributed: NCCL over NVLink on the GPUs), and the order of kernel calls.  All arithmetic is
-done by an `ops` object; the product one is `CudaOps` (ctypes -> libtransmil_b200.so, no fallback).  The `ops` seam
-exists so that the world_size-2 gloo test on CPU can drive the very same host logic with a torch restatement that lives
-under tests/ (never imported from here).
+`ShardPlan` is pure integer arithmetic (testable anywhere; `tm_make_shard_plan` holds the same integers in C).
+
+Two ways to run the schedule (`TokenShardedTransMIL(transport=...)`):
+  * "peer" (default): ONE C call per rank and bag, `tm_transmil_fwd_sharded` (csrc/sharded_fwd.cu): the library issues every
+    kernel and every exchange itself -- flag-guarded pulls over NVLink peer memory between communication regions that the
+    ranks map through CUDA IPC (`PeerComm`); nothing is launched from Python, so the call is captured into a CUDA graph at any
+    world size.  torch.distributed is used once, to pass the 64-byte IPC handles around.
+  * "nccl": `sharded_forward` below issues the schedule from Python kernel by kernel with torch.distributed collectives in
+    between (NCCL over NVLink on the GPUs).  All arithmetic is done by an `ops` object; the product one is `CudaOps`
+    (ctypes -> libtransmil_b200.so, no fallback).  The `ops` seam exists so that the world_size-2 gloo test on CPU can drive
+    the very same host logic with a torch restatement that lives under tests/ (never imported from here).  On the device
+    it is the cross-check of the peer path.
 """
 import ctypes as C
 import math
