@@ -86,3 +86,25 @@ def test_workspace_size_host_only(capi):
     p = capi.make_plan(50000)
     assert nbytes.value > 8 * p.Sp * 512 * 4          # h x3, xn, merged, q, k, v
     assert nbytes.value < 4 << 30
+
+
+def test_sharded_entry_points_refuse_loudly_without_a_gpu(built_lib):
+    """The token-sharded C ABI on a box without a CUDA device: plans are host arithmetic and work; everything that needs the
+    device returns a status and a message instead of crashing or pretending (there is no CPU path)."""
+    import ctypes as C
+    import torch
+    import transmil_b200 as T
+    L = T.capi.lib()
+    sp = T.capi.ShardPlanC()
+    assert L.tm_make_shard_plan(200000, 8, 3, C.byref(sp)) == 0
+    assert int(sp.world) == 8 and int(sp.rank) == 3 and int(sp.rows) % 256 == 0 and int(sp.ntok) > 0
+    assert L.tm_make_shard_plan(200000, 8, 8, C.byref(sp)) != 0 and b"rank" in L.tm_last_error()
+    assert L.tm_make_shard_plan(300, 4, 0, C.byref(sp)) != 0            # 2 blocks of 256 rows cannot feed 4 ranks
+    assert L.tm_make_shard_plan(0, 1, 0, C.byref(sp)) != 0
+    assert L.tm_shard_comm_destroy(None) == 0                            # NULL is a no-op, like free()
+    if not torch.cuda.is_available():
+        h = C.c_void_p()
+        assert L.tm_shard_comm_create(0, 1, 1000, C.byref(h)) != 0 and not h.value
+        assert L.tm_last_error()
+    code = C.c_int32(7)
+    assert L.tm_shard_comm_status(None, C.byref(code)) != 0
