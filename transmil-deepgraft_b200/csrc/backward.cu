@@ -1,4 +1,7 @@
-// Backward of the TransMIL bag-level path: first correct fp32 CUDA-core kernels.
+// Backward of the TransMIL bag-level path: the entry points, and the fp32 CUDA-core kernels behind them.
+// When the tensor-core engine is on (the default on a B200) the contractions go to bgemm_tc.cu (tcgen05, tf32 operands) and
+// the HBM-bound parts to backward_fast.cu; the plain kernels of this file are then the on-device cross-check
+// (tm_bgemm_engine(1)) and, through tests/cuda_emu, the host-executable form of the same arithmetic.
 //
 // The reference has no backward code: gradients come from torch.autograd through code/models/TransMIL.py:167-211 and
 // nystrom-attention 0.0.11.  The contractions and their order are those written out in oracle/transmil_backward.py; the
