@@ -259,6 +259,18 @@ int tm_nystrom_out_tc_fwd(const void* q16, const void* klm16, const void* mt16, 
 int64_t tm_attn3v_tc_scratch_floats(int64_t B, int64_t Sp);
 int tm_attn3v_tc_fwd(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp,
                      float* W3, float* scratch, uint32_t flags, void* stream);
+/* tm_attn3v_tc_fwd without the scratch argument, for callers that may not allocate device memory (CUDA-graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The chunk partials live in a file-scope static device array of the library (10 002 432 bytes = 148
+ * (bag, head, chunk) slots x 256 landmarks x 66 floats, held by every GPU that loads the library until the process exits);
+ * the call issues no cudaMalloc / cudaFree / allocating library routine.  Same inputs, output and (measured) bits as
+ * tm_attn3v_tc_fwd.  Limit: tm_attn3v_tc_scratch_floats(B, Sp) <= 2 500 608, i.e. B <= 18 on a 148-SM device, any Sp;
+ * beyond it the call returns TM_ERR_BAD_SHAPE and tm_last_error() says so.  Every call on a device shares the one array
+ * (it keeps the previous call's partials; nothing in it has to start at zero, each call overwrites what it reads), so two
+ * calls that overlap on the GPU - different streams, or this entry point beside itself in two host threads - RACE:
+ * order them on one stream or with events. */
+int tm_attn3v_tc_fwd_static(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp,
+                            float* W3, uint32_t flags, void* stream);
 
 /* K12: to_out Linear(512,512)+bias on rows [P,Sp) of merged (the `[:, -S:]` slice),
  * plus the TransLayer residual (TransMIL.py:53).  h_out may alias h_in.  With TM_FLAG_F16_ACT merged and out_w point

@@ -101,6 +101,7 @@ SIGNATURES = {
     "tm_nystrom_out_tc_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
     "tm_attn3v_tc_scratch_floats": (_i64, [_i64, _i64]),
     "tm_attn3v_tc_fwd": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _fp, _u32, _fp]),
+    "tm_attn3v_tc_fwd_static": (C.c_int, [_fp, _fp, _fp, _i64, _i64, _fp, _u32, _fp]),
     "tm_to_out_residual_fwd": (C.c_int, [_fp, _fp, _fp, _fp, _i64, _i64, _i64, _fp, _u32, _fp]),
     "tm_ppeg_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp, _fp]),
     "tm_head_fwd": (C.c_int, [_PW, _fp, _i64, _i64, _fp, _fp]),

@@ -352,3 +352,37 @@ extern "C" int tm_attn3v_merge_fwd(const float* gathered, int64_t R, int64_t B, 
   TM_LAUNCH_CHECK();
   return TM_OK;
 }
+
+// ---- tm_attn3v_tc_fwd_static: the same launch pair with the chunk partials in library-owned static device memory ------
+// For callers that may not allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc): no cudaMalloc,
+// cudaFree or allocating library routine on this path.  The array below exists once per GPU that loads the library and is
+// held until the process exits (10 002 432 bytes).  In HOST code its name is only a stand-in, not a device address: the
+// address each device gave it is looked up once per device, with that device current, by cudaGetSymbolAddress.
+#define TM_ATTN3V_STATIC_SLOTS 148   /* (bag, head, chunk) partial slots: one per SM of a B200 */
+#define TM_ATTN3V_STATIC_FLOATS (TM_ATTN3V_STATIC_SLOTS * TM_LANDMARKS * (TM_DHEAD + 2))
+static __device__ __align__(256) float g_attn3v_static_scratch[TM_ATTN3V_STATIC_FLOATS];
+
+extern "C" int tm_attn3v_tc_fwd_static(const void* qlm16, const void* k16, const void* v16, int64_t B, int64_t Sp, float* W3,
+                                       uint32_t flags, void* stream) {
+  (void)flags;
+  TM_CHECK_ARG(W3 != nullptr, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_fwd_static: NULL pointer");
+  TM_CHECK_ARG(B > 0 && Sp > 0 && Sp % TM_LANDMARKS == 0, TM_ERR_BAD_SHAPE,
+               "tm_attn3v_tc_fwd_static: Sp must be a multiple of 256 (Sp=%lld)", (long long)Sp);
+  const int64_t need = tm_attn3v_tc_scratch_floats(B, Sp);
+  TM_CHECK_ARG(need <= (int64_t)TM_ATTN3V_STATIC_FLOATS, TM_ERR_BAD_SHAPE,
+               "tm_attn3v_tc_fwd_static: B=%lld, Sp=%lld needs %lld scratch floats, the static array holds %lld "
+               "(148 partial slots: B <= 18 on a 148-SM device); use tm_attn3v_tc_fwd with caller-owned scratch",
+               (long long)B, (long long)Sp, (long long)need, (long long)TM_ATTN3V_STATIC_FLOATS);
+  static float* dev_ptr[64] = {nullptr};   // per device: the array's address on that device
+  int dev = 0;
+  TM_CUDA(cudaGetDevice(&dev));
+  TM_CHECK_ARG(dev >= 0 && dev < 64, TM_ERR_BAD_ARGUMENT, "tm_attn3v_tc_fwd_static: device ordinal %d out of range", dev);
+  if (dev_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    TM_CUDA(cudaGetSymbolAddress((void**)&p, g_attn3v_static_scratch));
+    TM_CHECK_ARG(p != nullptr, TM_ERR_CUDA, "tm_attn3v_tc_fwd_static: cudaGetSymbolAddress returned NULL");
+    dev_ptr[dev] = p;
+  }
+  // every slot the combine kernel reads is written in full by the partial kernel of the same call: nothing has to start at zero
+  return attn3v_tc_run(qlm16, k16, v16, B, Sp, W3, nullptr, dev_ptr[dev], stream);
+}
