@@ -444,6 +444,9 @@ int tm_gelu_bwd(const float* z, const float* dy, float* dz, int64_t n, void* str
  * 0.7), applied in place after tm_to_out_residual_fwd: y = h_in + to_out  ->  h_in + mask * to_out / (1-p).  The keep mask is
  * a counter-based function of (seed, element index), regenerated by tm_pad_front_bwd. */
 int tm_dropout_resid_fwd(float* y, const float* h_in, int64_t n, uint64_t seed, float p, void* stream);
+/* Dropout(0.6) inside the 768-d stem in training mode (TransMIL.py:123-126): y = mask(seed) * x / (1-p) with the same
+ * counter-based mask; the backward applies the same call to the gradient.  x may alias y. */
+int tm_dropout_fwd(const float* x, float* y, int64_t n, uint64_t seed, float p, void* stream);
 /* dy [B,S,C] -> out [B,S+P,C]: P zero rows in front (backward of the `[:, -S:]` slice), times the dropout mask when p > 0. */
 int tm_pad_front_bwd(const float* dy, int64_t B, int64_t S, int64_t P, int64_t C, uint64_t seed, float p, float* out, void* stream);
 /* 'b n (h d) -> b h n d' on a [B,Sp,512] gradient. */
@@ -470,6 +473,9 @@ int tm_ppeg_bwd(const tm_weights* w, const float* h_in, const float* dy, int64_t
 int tm_head_bwd(const tm_weights* w, const float* h3, const float* dlogits, int64_t B, int64_t S, float* dcls, float* g_norm_w,
                 float* g_norm_b, float* g_fc_w, float* g_fc_b, void* stream);
 /* Backward of the duplicate pad and the cls concat (TransMIL.py:177-186): dh0 [B,1+n+dup,512] -> dhf [B,n,512]. */
+/* Duplicate pad + cls concat (TransMIL.py:177-186; CTMIL.py:144-152) of tokens a stem produced outside tm_fc1_fwd:
+ * hf [B,n,512], cls [512] -> h0 [B,1+n+dup,512]. */
+int tm_dup_cls_fwd(const float* hf, const float* cls, int64_t B, int64_t n, int64_t dup, float* h0, void* stream);
 int tm_dup_cls_bwd(const float* dh0, int64_t B, int64_t n, int64_t dup, float* dhf, void* stream);
 
 /* ---- optimizer step ----------------------------------------------------------------------------------

@@ -165,8 +165,9 @@ def ppeg_backward(sd, h, G, dy):
     return dh, grads
 
 
-def fc1_backward(sd, x, dh):
-    """Backward of oracle.fc1 (eval).  Returns dx and the stem's parameter gradients."""
+def fc1_backward(sd, x, dh, masks=None):
+    """Backward of oracle.fc1 (eval; with `masks` = (m0, m4) the training mode of the 768-d stem, see oracle.fc1).  Returns dx
+    and the stem's parameter gradients."""
     keys = sorted(k for k in sd if k.startswith("_fc1."))
     idx = sorted({int(k.split(".")[1]) for k in keys})
     lin = lambda a, i: F.linear(a, sd[f"_fc1.{i}.weight"], sd[f"_fc1.{i}.bias"])
@@ -193,12 +194,13 @@ def fc1_backward(sd, x, dh):
         d = ln_bwd(a0, 2, d)
         return lin_bwd(x, 0, gelu_backward(z0, d)), g
     if idx == [0, 3, 4, 7]:                          # Linear GELU (Dropout) LN Linear GELU (Dropout) LN
-        z0 = lin(x, 0); a0 = F.gelu(z0)
+        m0, m4 = masks if masks is not None else (1.0, 1.0)
+        z0 = lin(x, 0); a0 = F.gelu(z0) * m0
         a1 = F.layer_norm(a0, (a0.shape[-1],), sd["_fc1.3.weight"], sd["_fc1.3.bias"], 1e-5)
-        z4 = lin(a1, 4); a4 = F.gelu(z4)
-        d = ln_bwd(a4, 7, dh)
+        z4 = lin(a1, 4); a4 = F.gelu(z4) * m4
+        d = ln_bwd(a4, 7, dh) * m4
         d = lin_bwd(a1, 4, gelu_backward(z4, d))
-        d = ln_bwd(a0, 3, d)
+        d = ln_bwd(a0, 3, d) * m0
         return lin_bwd(x, 0, gelu_backward(z0, d)), g
     raise RuntimeError(f"unsupported _fc1 layout {idx}")
 

@@ -53,8 +53,10 @@ def plan(n):
     return dict(n=n, G=G, N=N, dup=dup, S=S, l=l, Sp=Sp, P=P, padding=padding)
 
 
-def fc1(sd, x):
-    """TransMIL._fc1 in eval mode (TransMIL.py:100-133).  Dropout = identity."""
+def fc1(sd, x, masks=None):
+    """TransMIL._fc1 (TransMIL.py:100-133).  Eval mode: Dropout = identity.  `masks` = (m0, m4), the training-mode keep masks
+    of the two Dropout(0.6) of the 768-d stem (TransMIL.py:123-126), already scaled by 1/(1-p), multiplied onto the GELU
+    outputs where the reference's Sequential drops them (pinned to the reference module in train mode by tests/test_oracle.py)."""
     keys = sorted(k for k in sd if k.startswith("_fc1."))
     idx = sorted({int(k.split(".")[1]) for k in keys})
     D = x.shape[-1]
@@ -67,8 +69,12 @@ def fc1(sd, x):
     if idx == [0, 3, 4, 7] and D == 768:
         # Linear GELU Dropout LN(768) Linear GELU Dropout LN(512)  (TransMIL.py:123-126)
         h = F.gelu(F.linear(x, sd["_fc1.0.weight"], sd["_fc1.0.bias"]))
+        if masks is not None:
+            h = h * masks[0]
         h = F.layer_norm(h, (h.shape[-1],), sd["_fc1.3.weight"], sd["_fc1.3.bias"], 1e-5)
         h = F.gelu(F.linear(h, sd["_fc1.4.weight"], sd["_fc1.4.bias"]))
+        if masks is not None:
+            h = h * masks[1]
         h = F.layer_norm(h, (h.shape[-1],), sd["_fc1.7.weight"], sd["_fc1.7.bias"], 1e-5)
         return h
     if idx == [0]:

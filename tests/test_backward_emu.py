@@ -293,3 +293,58 @@ def test_dropout_mask_is_the_same_in_forward_and_backward(K):
     K.check(K.L.tm_pad_front_bwd(dy.data_ptr(), B, S, P, Cc, seed, p, out.data_ptr(), None))
     assert out[:, :P].abs().max().item() == 0.0
     _close(out[:, P:], dy * mask / (1 - p), 1e-6, "dropout backward")
+
+
+def test_stem_dropout_and_dup_cls_forward_kernels(K):
+    """tm_dropout_fwd draws the SAME counter-based mask as the to_out Dropout for a (seed, index), in place or not;
+    tm_dup_cls_fwd == oracle.square_pad_cls (TransMIL.py:177-186)."""
+    g = torch.Generator().manual_seed(21)
+    n_el, p, seed = 3 * 70 * 512, 0.6, 424242
+    x = torch.randn(n_el, generator=g)
+    y = torch.empty_like(x)
+    K.check(K.L.tm_dropout_fwd(x.data_ptr(), y.data_ptr(), n_el, seed, p, None))
+    zeros, t = torch.zeros(n_el), x.clone()
+    K.check(K.L.tm_dropout_resid_fwd(t.data_ptr(), zeros.data_ptr(), n_el, seed, p, None))
+    assert torch.equal(y, t)
+    mask = (y != 0).float()
+    assert abs(mask.mean().item() - (1 - p)) < 0.01
+    _close(y, x * mask / (1 - p), 1e-6, "dropout forward")
+    K.check(K.L.tm_dropout_fwd(x.data_ptr(), x.data_ptr(), n_el, seed, p, None))
+    assert torch.equal(x, y)
+    for B, n in [(2, 10), (1, 16), (3, 1)]:
+        hf = torch.randn(B, n, 512, generator=g)
+        cls = torch.randn(1, 1, 512, generator=g)
+        ref, pl = O.square_pad_cls({"cls_token": cls}, hf)
+        h0 = torch.full((B, pl["S"], 512), float("nan"))
+        K.check(K.L.tm_dup_cls_fwd(hf.data_ptr(), cls.data_ptr(), B, n, pl["dup"], h0.data_ptr(), None))
+        assert torch.equal(h0, ref)
+
+
+def test_768_stem_in_training_mode_forward_and_backward(K, T):
+    """train() of the 768-d stem (TransMIL.py:123-126, Dropout(0.6) twice inside _fc1): the library's forward and parameter
+    gradients against the oracle with the SAME masks (regenerated from the seeds through tm_dropout_fwd on ones)."""
+    from transmil_b200 import training
+    B, n, D = 2, 45, 768
+    m = build_model(2, D)
+    sd = {k: v.detach().contiguous() for k, v in m.state_dict().items()}
+    x = make_input("randn", B, n, D, 80).contiguous()
+    seeds = (1234567, 7654321)
+    pl = O.plan(n)
+    h0 = training.stem768_train_forward(K, sd, x, pl["dup"], seeds)
+    masks = []
+    for seed, width in zip(seeds, (768, 512)):
+        ones = torch.ones(B, n, width)
+        K.check(K.L.tm_dropout_fwd(ones.data_ptr(), ones.data_ptr(), ones.numel(), seed, training.STEM768_DROPOUT, None))
+        assert abs((ones > 0).float().mean().item() - 0.4) < 0.02
+        masks.append(ones)
+    sd64 = {k: v.double() for k, v in sd.items()}
+    m64 = tuple(t.double() for t in masks)
+    ref_h0, _ = O.square_pad_cls(sd64, O.fc1(sd64, x.double(), masks=m64))
+    _close(h0, ref_h0, 1e-4, "h0 of the training-mode 768 stem")
+    assert not torch.allclose(h0.double(), O.square_pad_cls(sd64, O.fc1(sd64, x.double()))[0], atol=1e-2)
+    dh = torch.randn(B, n, 512, generator=torch.Generator().manual_seed(16))
+    _, ref = OB.fc1_backward(sd64, x.double(), dh.double(), masks=m64)
+    g = training.fc1_backward(K, sd, m._fc1_kind, x, dh.clone(), seeds, training.STEM768_DROPOUT)
+    assert set(g) == set(ref)
+    for k in sorted(ref):
+        _close(g[k].reshape(ref[k].shape), ref[k], 1e-3, k)

@@ -103,3 +103,25 @@ def test_front_pad_rows_count_in_attn3_softmax():
     w_without = torch.softmax(sim3[..., P:], -1) @ l1["v"][:, :, P:]
     assert torch.allclose(w_with, l1["W3"], atol=1e-6)
     assert not torch.allclose(w_without, l1["W3"], atol=1e-4)
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="/root/reference only exists in the build container")
+def test_768_stem_train_mode_masks_sit_where_the_reference_drops():
+    """Training mode of the 768-d stem (TransMIL.py:123-126): the reference's `_fc1` in train() with a seeded CPU RNG ==
+    oracle.fc1 with the two keep masks drawn from the same RNG stream in the same order (F.dropout of ones = mask / (1-p))."""
+    import torch.nn.functional as F
+    torch.set_float32_matmul_precision("highest")
+    model = ref_loader.build_reference(2, 768)
+    x = torch.randn(2, 40, 768, generator=torch.Generator().manual_seed(8))
+    model._fc1.train()
+    torch.manual_seed(99)
+    with torch.no_grad():
+        ref = model._fc1(x)
+    model._fc1.eval()
+    torch.manual_seed(99)
+    m0 = F.dropout(torch.ones(2, 40, 768), 0.6, True)
+    m4 = F.dropout(torch.ones(2, 40, 512), 0.6, True)
+    assert 0.3 < (m0 > 0).float().mean().item() < 0.5 and m0.max().item() == pytest.approx(2.5)
+    mine = O.fc1(model.state_dict(), x, masks=(m0, m4))
+    assert torch.allclose(ref, mine, atol=1e-6, rtol=0)
+    assert not torch.allclose(ref, O.fc1(model.state_dict(), x), atol=1e-2)

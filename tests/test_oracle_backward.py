@@ -55,3 +55,21 @@ def test_full_backward_matches_autograd(D, nc, n, B, sharp):
         scale = max(g.abs().max().item(), 1e-30)
         assert (got[k].reshape(g.shape) - g).abs().max().item() <= 1e-8 * scale, k
     assert (got_dx - ref_dx).abs().max().item() <= 1e-8 * ref_dx.abs().max().item()
+
+
+def test_768_stem_backward_with_dropout_masks_matches_autograd():
+    """fc1_backward(masks=...) = autograd of oracle.fc1(masks=...): the training mode of the 768-d stem (TransMIL.py:123-126)."""
+    m = build_model(2, 768)
+    sd = _sd64(m)
+    x = make_input("randn", 2, 30, 768, 12).double()
+    g = torch.Generator().manual_seed(6)
+    m0 = (torch.rand(2, 30, 768, generator=g) >= 0.6).double() / 0.4
+    m4 = (torch.rand(2, 30, 512, generator=g) >= 0.6).double() / 0.4
+    dh = torch.randn(2, 30, 512, generator=g).double()
+    prm = {k: v.clone().requires_grad_(True) for k, v in sd.items() if k.startswith("_fc1.")}
+    xr = x.clone().requires_grad_(True)
+    (O.fc1(prm, xr, masks=(m0, m4)) * dh).sum().backward()
+    dx, got = Bk.fc1_backward(sd, x, dh, masks=(m0, m4))
+    for k, v in prm.items():
+        assert (got[k].reshape(v.shape) - v.grad).abs().max().item() <= 1e-9 * max(v.grad.abs().max().item(), 1e-30), k
+    assert (dx - xr.grad).abs().max().item() <= 1e-9 * xr.grad.abs().max().item()

@@ -146,6 +146,7 @@ BWD_SIGNATURES = {
     "tm_gelu_fwd": (C.c_int, [_fp, _fp, _i64, _fp]),
     "tm_gelu_bwd": (C.c_int, [_fp, _fp, _fp, _i64, _fp]),
     "tm_dropout_resid_fwd": (C.c_int, [_fp, _fp, _i64, _u64, _f32, _fp]),
+    "tm_dropout_fwd": (C.c_int, [_fp, _fp, _i64, _u64, _f32, _fp]),
     "tm_pad_front_bwd": (C.c_int, [_fp, _i64, _i64, _i64, _i64, _u64, _f32, _fp, _fp]),
     "tm_split_heads": (C.c_int, [_fp, _i64, _i64, _fp, _fp]),
     "tm_qkv_grad_merge": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _i64, _i64, _i64, _fp, _fp]),
@@ -156,6 +157,7 @@ BWD_SIGNATURES = {
     "tm_ppeg_bwd_scratch_floats": (_i64, [_i64, _i64]),
     "tm_ppeg_bwd": (C.c_int, [_PW, _fp, _fp, _i64, _i64] + [_fp] * 9),
     "tm_head_bwd": (C.c_int, [_PW, _fp, _fp, _i64, _i64, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "tm_dup_cls_fwd": (C.c_int, [_fp, _fp, _i64, _i64, _i64, _fp, _fp]),
     "tm_dup_cls_bwd": (C.c_int, [_fp, _i64, _i64, _i64, _fp, _fp]),
 }
 

@@ -318,6 +318,12 @@ __global__ void __launch_bounds__(BT) dropout_resid_kernel(float* y, const float
   const i64 i = (i64)blockIdx.x * BT + threadIdx.x;
   if (i < n) y[i] = h_in[i] + keep_scale(seed, (uint64_t)i, p) * (y[i] - h_in[i]);
 }
+// y <- keep * x: the Dropout layers INSIDE the 768-d stem (TransMIL.py:123-126) in training mode, forward (activations) and
+// backward (their gradients) alike; x may alias y
+__global__ void __launch_bounds__(BT) dropout_kernel(const float* x, float* y, i64 n, uint64_t seed, float p) {
+  const i64 i = (i64)blockIdx.x * BT + threadIdx.x;
+  if (i < n) y[i] = keep_scale(seed, (uint64_t)i, p) * x[i];
+}
 // out[b, r, c] = r < P ? 0 : dy[b, r-P, c] (* keep mask when p > 0): gradient entering to_out on the front-padded axis
 __global__ void __launch_bounds__(BT) pad_front_kernel(const float* dy, i64 B, i64 S, i64 P, int C, uint64_t seed, float p, float* out) {
   const i64 i = (i64)blockIdx.x * BT + threadIdx.x;
@@ -570,6 +576,17 @@ __global__ void __launch_bounds__(BT) dup_cls_bwd_kernel(const float* dh0, i64 B
   dhf[i] = o;
 }
 
+// h0[b,0] = cls, h0[b,1+i] = hf[b,i] (i < n), h0[b,1+n+j] = hf[b,j] (j < dup)   (TransMIL.py:177-186: duplicate pad + cls concat
+// for stems that produce their tokens outside tm_fc1_fwd: the training-mode 768-d stem, the conv stem of CTMIL.py:137-152)
+__global__ void __launch_bounds__(BT) dup_cls_fwd_kernel(const float* hf, const float* cls, i64 B, i64 n, i64 dup, float* h0) {
+  const i64 i = (i64)blockIdx.x * BT + threadIdx.x;
+  const i64 S = n + dup + 1;
+  if (i >= B * S * TM_DIM) return;
+  const int c = (int)(i % TM_DIM);
+  const i64 r = (i / TM_DIM) % S, b = i / (TM_DIM * S);
+  h0[i] = r == 0 ? cls[c] : hf[(b * n + (r - 1 < n ? r - 1 : r - 1 - n)) * TM_DIM + c];
+}
+
 // ---- optimizer step over the whole parameter set: torch.optim.RAdam as selected by the reference's factory
 // (code/MyOptimizer/optim_factory.py:78-80) + the Lookahead wrapper (code/MyOptimizer/lookahead.py:28-41), one launch each --------
 struct OptBatch { tm_opt_tensor t[TM_OPT_MAX_TENSORS]; };
@@ -774,6 +791,14 @@ int tm_dropout_resid_fwd(float* y, const float* h_in, int64_t n, uint64_t seed, 
   BW_LAUNCH(dropout_resid_kernel, grid1d(n), dim3(BT), (cudaStream_t)stream, y, h_in, (i64)n, seed, p);
   return TM_OK;
 }
+/* Training-mode Dropout(p) inside the 768-d stem (TransMIL.py:123-126: Linear GELU Dropout(0.6) LN Linear GELU Dropout(0.6) LN):
+ * y = mask(seed) * x / (1-p), the same counter-based mask as the to_out Dropout; the backward applies the same call to the
+ * gradient.  x may alias y. */
+int tm_dropout_fwd(const float* x, float* y, int64_t n, uint64_t seed, float p, void* stream) {
+  TM_CHECK_ARG(x && y && n > 0 && p >= 0.f && p < 1.f, TM_ERR_BAD_ARGUMENT, "tm_dropout_fwd: bad argument");
+  BW_LAUNCH(dropout_kernel, grid1d(n), dim3(BT), (cudaStream_t)stream, x, y, (i64)n, seed, p);
+  return TM_OK;
+}
 /* dy [B,S,C] -> out [B,S+P,C] with P zero rows in front (the `[:, -S:]` slice backward), times the dropout mask if p > 0. */
 int tm_pad_front_bwd(const float* dy, int64_t B, int64_t S, int64_t P, int64_t C, uint64_t seed, float p, float* out, void* stream) {
   TM_CHECK_ARG(dy && out && B > 0 && S > 0 && P >= 0 && C > 0 && p >= 0.f && p < 1.f, TM_ERR_BAD_ARGUMENT, "tm_pad_front_bwd: bad argument");
@@ -935,6 +960,14 @@ int tm_head_bwd(const tm_weights* w, const float* h3, const float* dlogits, int6
   TM_CHECK_ARG(B > 0 && S > 0 && w->n_classes > 0 && w->n_classes <= TM_DIM, TM_ERR_BAD_SHAPE, "tm_head_bwd: bad shape");
   BW_LAUNCH(head_bwd_kernel, dim3(1), dim3(TM_DIM), (cudaStream_t)stream, h3, dlogits, w->norm_w, w->norm_b, w->fc_w, (i64)B, (i64)S,
             (int)w->n_classes, dcls, g_norm_w, g_norm_b, g_fc_w, g_fc_b);
+  return TM_OK;
+}
+
+/* Duplicate pad + cls concat (TransMIL.py:177-186) of tokens a stem produced outside tm_fc1_fwd: hf [B,n,512], cls [512]
+ * -> h0 [B,1+n+dup,512]. */
+int tm_dup_cls_fwd(const float* hf, const float* cls, int64_t B, int64_t n, int64_t dup, float* h0, void* stream) {
+  TM_CHECK_ARG(hf && cls && h0 && B > 0 && n > 0 && dup >= 0 && dup <= n, TM_ERR_BAD_ARGUMENT, "tm_dup_cls_fwd: bad argument");
+  BW_LAUNCH(dup_cls_fwd_kernel, grid1d(B * (1 + n + dup) * TM_DIM), dim3(BT), (cudaStream_t)stream, hf, cls, (i64)B, (i64)n, (i64)dup, h0);
   return TM_OK;
 }
 

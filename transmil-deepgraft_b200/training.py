@@ -22,6 +22,7 @@ BWD_SIGNATURES = capi.BWD_SIGNATURES   # C ABI of csrc/backward.cu (declared in 
 
 H, DH, DIM, LM = 8, 64, 512, 256
 TO_OUT_DROPOUT = 0.7    # TransLayer passes dropout=0.7 to NystromAttention (TransMIL.py:33)
+STEM768_DROPOUT = 0.6   # the two Dropout layers inside the 768-d _fc1 (TransMIL.py:123-126), active in train() only
 
 
 def bind(lib):
@@ -154,7 +155,45 @@ def _linear_wgrad(K, dz, a, g, key, R, Din, Dout):
     g[key + ".bias"] = K.colsum(dz, R, Dout, Dout)
 
 
-def fc1_backward(K, p, kind, x, dhf):
+def _drop(K, t, seed, p):
+    if p > 0.0:
+        K.check(K.L.tm_dropout_fwd(t.data_ptr(), t.data_ptr(), t.numel(), seed, p, K.st))
+    return t
+
+
+def stem768(K, p, xf, R, D, seeds=(0, 0), drop=0.0):
+    """The 768-d stem up to its last LayerNorm (TransMIL.py:123-126): Linear GELU Dropout LN(768) Linear(768,512) GELU Dropout.
+    Returns (z0, a0, a1, z4, a4) with a0 / a4 AFTER their Dropout (`drop` = 0.6 in train(), 0 in eval; the keep masks are
+    counter-based functions of (seed, element index), so the backward regenerates them).  Used by the training-mode forward
+    and, recomputing, by fc1_backward."""
+    F0 = p["_fc1.0.weight"].shape[0]
+    z0 = _linear_fwd(K, xf, p["_fc1.0.weight"], p["_fc1.0.bias"], R, D, F0)
+    a0 = torch.empty_like(z0)
+    K.check(K.L.tm_gelu_fwd(z0.data_ptr(), a0.data_ptr(), R * F0, K.st))
+    _drop(K, a0, seeds[0], drop)
+    a1 = torch.empty_like(z0)
+    K.check(K.L.tm_ln_rows_fwd(a0.data_ptr(), p["_fc1.3.weight"].data_ptr(), p["_fc1.3.bias"].data_ptr(), R, F0, a1.data_ptr(), K.st))
+    z4 = _linear_fwd(K, a1, p["_fc1.4.weight"], p["_fc1.4.bias"], R, F0, DIM)
+    a4 = torch.empty_like(z4)
+    K.check(K.L.tm_gelu_fwd(z4.data_ptr(), a4.data_ptr(), R * DIM, K.st))
+    _drop(K, a4, seeds[1], drop)
+    return z0, a0, a1, z4, a4
+
+
+def stem768_train_forward(K, p, x, dup, seeds):
+    """h0 [B,1+n+dup,512] of a train()-mode forward with the 768-d stem: tm_fc1_fwd is the eval stem (no Dropout inside), so the
+    training forward strings the stem together from the same kernels the backward recomputes it with."""
+    B, n, D = x.shape
+    R = B * n
+    a4 = stem768(K, p, x.reshape(R, D), R, D, seeds, STEM768_DROPOUT)[4]
+    hf = torch.empty_like(a4)
+    K.check(K.L.tm_ln_rows_fwd(a4.data_ptr(), p["_fc1.7.weight"].data_ptr(), p["_fc1.7.bias"].data_ptr(), R, DIM, hf.data_ptr(), K.st))
+    h0 = K.new(x, B, 1 + n + dup, DIM)
+    K.check(K.L.tm_dup_cls_fwd(hf.data_ptr(), p["cls_token"].data_ptr(), B, n, dup, h0.data_ptr(), K.st))
+    return h0
+
+
+def fc1_backward(K, p, kind, x, dhf, stem_seeds=(0, 0), stem_drop=0.0):
     """Backward of TransMIL._fc1 (TransMIL.py:100-133) for the parameters (the bag x is a leaf without gradient).  The stem's
     pre-activations are recomputed.  oracle/transmil_backward.py fc1_backward."""
     B, n, D = x.shape
@@ -183,29 +222,24 @@ def fc1_backward(K, p, kind, x, dhf):
         _linear_wgrad(K, z0, xf, g, "_fc1.0", R, D, F0)
         return g
     if kind == capi.TM_FC1_768:
-        # Linear GELU [Dropout] LN(768) Linear(768,512) GELU [Dropout] LN(512) (TransMIL.py:123-126); the eval-mode graph
-        # (keep_graph): the two Dropout(0.6) are identities; train mode of this stem is refused by the forward
+        # Linear GELU [Dropout] LN(768) Linear(768,512) GELU [Dropout] LN(512) (TransMIL.py:123-126); stem_drop = 0.6 in train()
+        # (the masks of the forward are regenerated from stem_seeds), 0 for the eval-mode graph (keep_graph)
         F0 = p["_fc1.0.weight"].shape[0]
-        z0 = _linear_fwd(K, xf, p["_fc1.0.weight"], p["_fc1.0.bias"], R, D, F0)
-        a0 = torch.empty_like(z0)
-        K.check(K.L.tm_gelu_fwd(z0.data_ptr(), a0.data_ptr(), R * F0, K.st))
-        a1 = torch.empty_like(z0)
-        K.check(K.L.tm_ln_rows_fwd(a0.data_ptr(), p["_fc1.3.weight"].data_ptr(), p["_fc1.3.bias"].data_ptr(), R, F0, a1.data_ptr(), K.st))
-        z4 = _linear_fwd(K, a1, p["_fc1.4.weight"], p["_fc1.4.bias"], R, F0, DIM)
-        a4 = torch.empty_like(z4)
-        K.check(K.L.tm_gelu_fwd(z4.data_ptr(), a4.data_ptr(), R * DIM, K.st))
+        z0, a0, a1, z4, a4 = stem768(K, p, xf, R, D, stem_seeds, stem_drop)
         da4, g["_fc1.7.weight"], g["_fc1.7.bias"] = K.ln_bwd(a4, p["_fc1.7.weight"], dhf, R, DIM, R, R, 0, None)
+        _drop(K, da4, stem_seeds[1], stem_drop)
         K.check(K.L.tm_gelu_bwd(z4.data_ptr(), da4.data_ptr(), z4.data_ptr(), R * DIM, K.st))           # z4 <- dz4
         _linear_wgrad(K, z4, a1, g, "_fc1.4", R, F0, DIM)
         da1 = K.gemm(z4, (DIM, 1), p["_fc1.4.weight"], (F0, 1), a1, R, F0, DIM, F0)                      # a1 <- da1
         da0, g["_fc1.3.weight"], g["_fc1.3.bias"] = K.ln_bwd(a0, p["_fc1.3.weight"], da1, R, F0, R, R, 0, None)
+        _drop(K, da0, stem_seeds[0], stem_drop)
         K.check(K.L.tm_gelu_bwd(z0.data_ptr(), da0.data_ptr(), z0.data_ptr(), R * F0, K.st))            # z0 <- dz0
         _linear_wgrad(K, z0, xf, g, "_fc1.0", R, D, F0)
         return g
     raise ValueError(f"unknown _fc1 kind {kind}")
 
 
-def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0), drop=0.0, keep_dxn=False):
+def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0, 0, 0), drop=0.0, keep_dxn=False):
     """Gradients of sum(logits * dlogits) for every parameter (reference state_dict keys).  p: name -> parameter tensor,
     w: capi.Weights of the same tensors, saved: stages kept by the forward.  Stage order = reverse of TransMIL.forward
     (TransMIL.py:167-211); mirrors oracle/transmil_backward.py backward()."""
@@ -243,7 +277,9 @@ def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0), drop=0.0, keep_dxn=
     g["cls_token"] = K.colsum(dh0, B, DIM, S * DIM).reshape(1, 1, DIM)
     dhf = new(B, n, DIM)
     K.check(K.L.tm_dup_cls_bwd(dh0.data_ptr(), B, n, dup, dhf.data_ptr(), K.st))
-    g.update(fc1_backward(K, p, kind, x, dhf))
+    # seeds = (layer1 to_out, layer2 to_out, stem Dropout 0, stem Dropout 1); the stem's Dropout exists in the 768-d form only
+    stem_drop = STEM768_DROPOUT if (drop > 0.0 and kind == capi.TM_FC1_768) else 0.0
+    g.update(fc1_backward(K, p, kind, x, dhf, tuple(seeds[2:4]) if len(seeds) >= 4 else (0, 0), stem_drop))
     return g
 
 
@@ -302,10 +338,13 @@ def forward_keep_tc(model, x, training, seeds):
         wt.fc1_w1 = tf32_copy(f[3].weight)
     elif model._fc1_kind == capi.TM_FC1_768:
         wt.fc1_w1 = tf32_copy(f[4].weight)
-    h0 = f32(B, S, DIM)
-    scratch = f32(max(1, B * n * F0))
-    ck(L.tm_fc1_fwd(C.byref(wt), x.data_ptr(), B, n, h0.data_ptr(), scratch.data_ptr(), flags, st))
-    del scratch
+    if training and model._fc1_kind == capi.TM_FC1_768:   # Dropout(0.6) inside the stem (TransMIL.py:123-126)
+        h0 = stem768_train_forward(Kernels(stream=st), {k: t.detach() for k, t in model.named_parameters()}, x, plan["dup"], seeds[2:4])
+    else:
+        h0 = f32(B, S, DIM)
+        scratch = f32(max(1, B * n * F0))
+        ck(L.tm_fc1_fwd(C.byref(wt), x.data_ptr(), B, n, h0.data_ptr(), scratch.data_ptr(), flags, st))
+        del scratch
     saved = {"plan": plan, "h0": h0}
 
     def layer(name, lw, mod, h_in, seed):
@@ -361,10 +400,13 @@ def forward_keep_simt(model, x, training, seeds):
     new = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
     flags = capi.TM_FLAG_SIMT_ONLY
     F0 = {capi.TM_FC1_SINGLE: 0, capi.TM_FC1_2048: 1024, capi.TM_FC1_768: 768}[model._fc1_kind]
-    h0 = new(B, S, DIM)
-    scratch = new(max(1, B * n * F0))
-    ck(L.tm_fc1_fwd(C.byref(w), x.data_ptr(), B, n, h0.data_ptr(), scratch.data_ptr(), flags, st))
-    del scratch
+    if training and model._fc1_kind == capi.TM_FC1_768:   # Dropout(0.6) inside the stem (TransMIL.py:123-126)
+        h0 = stem768_train_forward(Kernels(stream=st), {k: t.detach() for k, t in model.named_parameters()}, x, plan["dup"], seeds[2:4])
+    else:
+        h0 = new(B, S, DIM)
+        scratch = new(max(1, B * n * F0))
+        ck(L.tm_fc1_fwd(C.byref(w), x.data_ptr(), B, n, h0.data_ptr(), scratch.data_ptr(), flags, st))
+        del scratch
     saved = {"plan": plan, "h0": h0}
 
     def layer(name, lw, h_in, seed):
@@ -412,9 +454,7 @@ class TransMILFunction(torch.autograd.Function):
     def forward(ctx, model, x, *params):
         bind(capi.lib())
         training = model.training
-        if training and model._fc1_kind == capi.TM_FC1_768:
-            raise NotImplementedError("libtransmil_b200: training the 768-d stem (Dropout(0.6) inside _fc1) is not built")
-        seeds = tuple(int(s) for s in torch.randint(0, 2 ** 62, (2,))) if training else (0, 0)
+        seeds = tuple(int(s) for s in torch.randint(0, 2 ** 62, (4,))) if training else (0, 0, 0, 0)   # to_out x 2, 768-d stem x 2
         with torch.cuda.device(x.device):
             logits, saved, w = forward_keep(model, x, training, seeds)
         ctx.model, ctx.x, ctx.saved, ctx.seeds, ctx.training = model, x, saved, seeds, training
@@ -465,9 +505,7 @@ class _HookedFunction(torch.autograd.Function):
     def forward(ctx, model, x, holder, hooked, *params):
         bind(capi.lib())
         training = model.training
-        if training and model._fc1_kind == capi.TM_FC1_768:
-            raise NotImplementedError("libtransmil_b200: training the 768-d stem (Dropout(0.6) inside _fc1) is not built")
-        seeds = tuple(int(s) for s in torch.randint(0, 2 ** 62, (2,))) if training else (0, 0)
+        seeds = tuple(int(s) for s in torch.randint(0, 2 ** 62, (4,))) if training else (0, 0, 0, 0)   # to_out x 2, 768-d stem x 2
         with _kernels_for(x)[0]:
             logits, saved, _w = forward_keep(model, x, training, seeds)
         ctx.model, ctx.x, ctx.saved, ctx.seeds, ctx.training = model, x, saved, seeds, training
