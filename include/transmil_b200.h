@@ -45,7 +45,10 @@ typedef enum tm_status {
 typedef enum tm_fc1_kind {
   TM_FC1_SINGLE = 0,  /* Linear(D,512) GELU                      TransMIL.py:130-133, MDMIL.py:66 */
   TM_FC1_2048 = 1,    /* Linear(2048,1024) GELU LN(1024) Linear(1024,512) GELU   TransMIL.py:109-110 */
-  TM_FC1_768 = 2      /* Linear(768,768) GELU LN(768) Linear(768,512) GELU LN(512)  TransMIL.py:123-126 (eval) */
+  TM_FC1_768 = 2,     /* Linear(768,768) GELU LN(768) Linear(768,512) GELU LN(512)  TransMIL.py:123-126 (eval) */
+  TM_FC1_TOKENS = 3   /* no stem inside the library: x is [B,n,512] fp32 tokens produced by the caller (the conv stem of
+                         CTMIL.py:137-142 / the commented forward of TransformerMIL.py:155-161); in_features = 512, the fc1_*
+                         pointers are ignored; duplicate pad + cls (CTMIL.py:144-152) as for the other stems */
 } tm_fc1_kind;
 
 /* Flags for tm_transmil_fwd / tm_workspace_bytes. */

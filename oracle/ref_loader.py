@@ -81,3 +81,18 @@ def make_fc1_1024(seed):
 def reference_forward(model, x, return_attn=False):
     with _NoCuda(), torch.no_grad():
         return model(x, return_attn=return_attn)
+
+
+def load_reference_sibling(name):
+    """Executes the unmodified /root/reference/code/models/<name>.py (CTMIL, TransformerMIL) where it lies.  Those files import
+    `from ._transformer import ...`, so they are loaded as members of a synthetic package whose __path__ is the reference's
+    models directory (its own __init__.py, which pulls in Lightning, is not executed)."""
+    import types
+    if _HERE not in sys.path:
+        sys.path.insert(0, _HERE)
+    pkg = "_reference_models"
+    if pkg not in sys.modules:
+        m = types.ModuleType(pkg)
+        m.__path__ = [os.path.dirname(REF_FILE)]
+        sys.modules[pkg] = m
+    return importlib.import_module(f"{pkg}.{name}")

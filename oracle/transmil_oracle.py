@@ -163,11 +163,47 @@ def ppeg(sd, h, G):
 
 
 @torch.no_grad()
-def forward(sd, x, return_attn=False, return_stages=False, dtype=torch.float32):
+def ctmil_tokens(sd, x, training=False):
+    """Conv stem of CTMIL.forward (code/models/CTMIL.py:137-142; same lines in the commented forward of TransformerMIL.py:157-162):
+    tiles [1,N,C,H,H] -> conv1, conv2 (each Conv3x3 no bias -> BatchNorm2d -> GELU -> MaxPool(3,2,1), CTMIL.py:90-101) ->
+    `.view(N, h*h, 512)`: a REINTERPRETATION of the [N,512,h,h] memory, not a transpose.  sd: CTMIL state_dict.  Eval mode
+    (BatchNorm on its running statistics) unless `training` (batch statistics; the running buffers are not updated here)."""
+    h = x.squeeze(0) if x.dim() == 5 else x
+    for name in ("conv1", "conv2"):
+        h = F.conv2d(h, sd[f"{name}.0.weight"], None, stride=1, padding=1)
+        h = F.batch_norm(h, sd[f"{name}.1.running_mean"], sd[f"{name}.1.running_var"], sd[f"{name}.1.weight"], sd[f"{name}.1.bias"],
+                         training, 0.1, 1e-5)
+        h = F.max_pool2d(F.gelu(h), kernel_size=3, stride=2, padding=1)
+    h = h.contiguous()
+    return h.view(h.shape[0], h.shape[2] * h.shape[2], h.shape[1])
+
+
+def ctmil_state(sd):
+    """CTMIL / TransformerMIL state_dict -> the TransMIL key names forward() reads (PPEG block pos_layer_0, classifier _fc2;
+    CTMIL.py:82,122), without the stem and the sub-modules the Nystrom forward never touches."""
+    out = {}
+    for k, v in sd.items():
+        if k.startswith("pos_layer_0."):
+            out["pos_layer." + k[len("pos_layer_0."):]] = v
+        elif k.startswith("_fc2."):
+            out["_fc." + k[len("_fc2."):]] = v
+        elif k.startswith(("cls_token", "layer1.", "layer2.", "norm.")):
+            out[k] = v
+    return out
+
+
+def ctmil_forward(sd, x, dtype=torch.float32):
+    """CTMIL.forward (CTMIL.py:135-165), eval mode: logits [N, n_classes], one row per tile."""
+    sd = {k: (v.detach().to(dtype) if v.is_floating_point() else v) for k, v in sd.items()}
+    return forward(ctmil_state(sd), ctmil_tokens(sd, x.to(dtype)), dtype=dtype, tokens=True)
+
+
+def forward(sd, x, return_attn=False, return_stages=False, dtype=torch.float32, tokens=False):
     """TransMIL.forward (TransMIL.py:167-211), eval mode.
 
     sd: reference-layout state_dict (any float dtype; cast to `dtype`).
     x:  [B,n,D] / [n,D] / [1,B,n,D] as accepted at TransMIL.py:170-173.
+    tokens: x already holds the [B,n,512] tokens of a stem outside this function (CTMIL.py:142): `_fc1` is skipped.
     """
     sd = {k: v.detach().to(dtype) for k, v in sd.items()}
     if x.dim() > 3:
@@ -176,7 +212,8 @@ def forward(sd, x, return_attn=False, return_stages=False, dtype=torch.float32):
         x = x.unsqueeze(0)
     h = x.to(dtype)
     st = {} if return_stages else None
-    h = fc1(sd, h)
+    if not tokens:
+        h = fc1(sd, h)
     if st is not None:
         st["fc1"] = h
     h, p = square_pad_cls(sd, h)

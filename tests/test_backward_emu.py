@@ -348,3 +348,54 @@ def test_768_stem_in_training_mode_forward_and_backward(K, T):
     assert set(g) == set(ref)
     for k in sorted(ref):
         _close(g[k].reshape(ref[k].shape), ref[k], 1e-3, k)
+
+
+def test_ctmil_autograd_path_returns_token_gradient_and_renamed_parameter_gradients(K, T, monkeypatch):
+    """CTMIL: tokens of a torch stem enter the library's autograd Function with requires_grad; the backward hands
+    d(loss)/d(tokens) back (the conv stem is differentiated by torch) and names the PPEG / classifier gradients pos_layer_0.* /
+    _fc2.* (CTMIL.py:82,122).  Kernels through the host harness, kept stages from the forward oracle; reference = autograd of
+    the float64 oracle."""
+    import contextlib
+    from transmil_b200 import training
+    nc, N, n = 3, 2, 25
+    torch.manual_seed(2021)
+    m = T.CTMIL(n_classes=nc, in_features=64).eval()
+    m.keep_graph = True
+    sd = {k: v.detach().contiguous() for k, v in O.ctmil_state(m.state_dict()).items()}
+    tok = torch.randn(N, n, 512, generator=torch.Generator().manual_seed(81)).requires_grad_(True)
+    dlogits = torch.randn(N, nc, generator=torch.Generator().manual_seed(17))
+    monkeypatch.setattr(training, "_kernels_for", lambda t: (contextlib.nullcontext(), K))
+    monkeypatch.setattr(training, "forward_keep", lambda model, t, tr, seeds: (*_saved_from_oracle_tokens(sd, t), None))
+    monkeypatch.setattr(training, "bind", lambda lib: lib)
+    monkeypatch.setattr(T.capi, "lib", lambda: K.L)
+    m._weights = lambda: _weights(T, {**sd, "_fc1.0.weight": sd["cls_token"], "_fc1.0.bias": sd["cls_token"]}, T.capi.TM_FC1_TOKENS, 512, nc)
+    logits = training.TransMILFunction.apply(m, tok, *m._path_parameters())
+    (logits * dlogits).sum().backward()
+    prm = {k: v.double().clone().requires_grad_(True) for k, v in sd.items()}
+    t64 = tok.detach().double().requires_grad_(True)
+    h, pl = O.square_pad_cls(prm, t64)
+    h = O.trans_layer(prm, "layer2", O.ppeg(prm, O.trans_layer(prm, "layer1", h), pl["G"]))
+    ref_logits = F.linear(F.layer_norm(h, (512,), prm["norm.weight"], prm["norm.bias"], 1e-5)[:, 0], prm["_fc.weight"], prm["_fc.bias"])
+    _close(logits, ref_logits.detach(), 1e-5, "logits")
+    (ref_logits * dlogits.double()).sum().backward()
+    _close(tok.grad, t64.grad, 2e-3, "d(loss)/d(tokens)")
+    names = {n_ for n_, _ in m._path_named_parameters()}
+    for k, p in m.named_parameters():
+        if k not in names:
+            assert p.grad is None, k          # conv stem / unused _fc1: not the library's to differentiate
+            continue
+        ref = prm[k.replace("pos_layer_0.", "pos_layer.").replace("_fc2.", "_fc.")].grad
+        _close(p.grad, ref.reshape(p.shape), 2e-3, k)
+
+
+def _saved_from_oracle_tokens(sd, tok):
+    logits, st = O.forward(sd, tok, return_stages=True, tokens=True)
+    p = O.plan(tok.shape[1])
+    saved = {"plan": p, "h0": st["h0"], "h1": st["h1"], "h2": st["h2"], "h3": st["h3"]}
+    for name in ("layer1", "layer2"):
+        s = st[name]
+        sv = {k: s[k].contiguous() for k in ("q", "k", "v", "q_lm", "k_lm", "attn2", "Z", "W3", "merged")}
+        sv["xn"] = F.pad(s["xn"], (0, 0, p["P"], 0)).contiguous()
+        sv["M"] = (s["Z"] @ s["W3"]).contiguous()
+        saved[name] = sv
+    return logits, {k: (v.contiguous() if torch.is_tensor(v) else v) for k, v in saved.items()}

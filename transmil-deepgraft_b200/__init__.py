@@ -15,6 +15,6 @@ Layout (only what the path needs):
 from . import bagdp, capi, h5bag, training
 from .bagdp import BagParallelInference
 from .ingest import StreamedInference
-from .transmil import MDMIL, LazyAttention, NystromAttention, PPEG, TransLayer, TransMIL, y_prob_y_hat
+from .transmil import CTMIL, MDMIL, TransformerMIL, LazyAttention, NystromAttention, PPEG, TransLayer, TransMIL, y_prob_y_hat
 
-__all__ = ["capi", "h5bag", "bagdp", "training", "BagParallelInference", "TransMIL", "MDMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]
+__all__ = ["capi", "h5bag", "bagdp", "training", "BagParallelInference", "TransMIL", "MDMIL", "CTMIL", "TransformerMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention", "y_prob_y_hat", "StreamedInference"]

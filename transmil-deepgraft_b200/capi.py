@@ -17,7 +17,7 @@ TM_FLAG_F16_ACT = 16
 TM_FLAG_NO_OVERLAP = 32
 TM_FLAG_X_F16 = 64
 TM_FLAG_CLS_ONLY_L2 = 128
-TM_FC1_SINGLE, TM_FC1_2048, TM_FC1_768 = 0, 1, 2
+TM_FC1_SINGLE, TM_FC1_2048, TM_FC1_768, TM_FC1_TOKENS = 0, 1, 2, 3
 
 _fp = C.c_void_p  # device/host float pointers travel as raw addresses
 

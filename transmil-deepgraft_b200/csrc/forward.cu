@@ -49,6 +49,7 @@ static int fc1_width(const tm_weights* w) {
     case TM_FC1_SINGLE: return 0;
     case TM_FC1_2048: return 1024;
     case TM_FC1_768: return 768;
+    case TM_FC1_TOKENS: return 0;
     default: return -1;
   }
 }
@@ -103,7 +104,7 @@ static int make_layout(int64_t B, const tm_plan& p, const tm_weights* w, uint32_
   L->mt16 = bump(cur, lm / 2);
   L->packed = bump(cur, 50 * TM_DIM);
   L->lm_part = bump(cur, (fused_lm_enabled() && p.l >= 128) ? (size_t)B * (p.Sp / 128) * 8 * (2 * TM_DIM) : 0);
-  L->wr_fc1_0 = bump(cur, (size_t)(f0 ? f0 : TM_DIM) * w->in_features);
+  L->wr_fc1_0 = bump(cur, w->fc1_kind == TM_FC1_TOKENS ? 0 : (size_t)(f0 ? f0 : TM_DIM) * w->in_features);
   L->wr_fc1_1 = bump(cur, (size_t)TM_DIM * f0);
   for (int l = 0; l < 2; ++l) {
     L->wr_qkv[l] = bump(cur, (size_t)3 * TM_DIM * TM_DIM);
@@ -117,7 +118,11 @@ static int check_weights(const tm_weights* w) {
   TM_CHECK_ARG(w != nullptr, TM_ERR_BAD_ARGUMENT, "weights struct is NULL");
   TM_CHECK_ARG(w->in_features > 0 && w->in_features % 4 == 0, TM_ERR_BAD_SHAPE, "in_features must be a positive multiple of 4 (got %d)", w->in_features);
   TM_CHECK_ARG(w->n_classes > 0, TM_ERR_BAD_SHAPE, "n_classes must be positive");
-  TM_CHECK_ARG(w->fc1_w0 && w->fc1_b0 && w->cls_token && w->norm_w && w->norm_b && w->fc_w && w->fc_b, TM_ERR_BAD_ARGUMENT, "missing parameter pointer");
+  TM_CHECK_ARG(w->cls_token && w->norm_w && w->norm_b && w->fc_w && w->fc_b, TM_ERR_BAD_ARGUMENT, "missing parameter pointer");
+  if (w->fc1_kind == TM_FC1_TOKENS)
+    TM_CHECK_ARG(w->in_features == TM_DIM, TM_ERR_BAD_SHAPE, "TM_FC1_TOKENS: the bag holds 512-d tokens (in_features=%d)", w->in_features);
+  else
+    TM_CHECK_ARG(w->fc1_w0 && w->fc1_b0, TM_ERR_BAD_ARGUMENT, "missing parameter pointer (_fc1.0)");
   if (w->fc1_kind == TM_FC1_2048)
     TM_CHECK_ARG(w->in_features == 2048 && w->fc1_ln_w && w->fc1_ln_b && w->fc1_w1 && w->fc1_b1, TM_ERR_BAD_ARGUMENT, "TM_FC1_2048 needs in_features=2048 and the LN/second Linear parameters");
   if (w->fc1_kind == TM_FC1_768)
@@ -242,6 +247,14 @@ static int fc1_run(const tm_weights* w, const float* x, int64_t B, int64_t n, fl
   TM_CHECK_ARG(B > 0 && x && h0, TM_ERR_BAD_ARGUMENT, "tm_fc1_fwd: bad arguments");
   TM_CHECK_ARG(B * n < (1ll << 31) && B * p.Sp < (1ll << 31), TM_ERR_BAD_SHAPE, "tm_fc1_fwd: B*n exceeds 2^31 rows");
   const int D = w->in_features;
+  if (w->fc1_kind == TM_FC1_TOKENS) {
+    // the stem ran outside the library (conv stem of CTMIL.py:137-142): x already holds [B,n,512] tokens
+    TM_CHECK_ARG(!(flags & TM_FLAG_X_F16), TM_ERR_BAD_ARGUMENT, "TM_FC1_TOKENS: fp32 tokens only");
+    prof_mark(ST_FC1_TAIL, st);
+    if (pad_cls) return tm_dup_cls_fwd(x, w->cls_token, B, n, p.dup, h0, st);
+    TM_CUDA(cudaMemcpyAsync(h0, x, (size_t)B * n * TM_DIM * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    return TM_OK;
+  }
   GemmParams g;
   memset(&g, 0, sizeof(g));
   g.batch = 1; g.epi = EPI_BIAS_GELU;
@@ -379,9 +392,11 @@ extern "C" int tm_transmil_fwd(const tm_weights* w, const float* x, int64_t B, i
     // merged are produced as fp16 by their kernels) and the packed PPEG filter
     const float* srcs[6]; void* dsts[6]; long long cnt[6]; int kinds[6];
     int nj = 0;
-    srcs[nj] = w->fc1_w0; dsts[nj] = ws + L.wr_fc1_0; cnt[nj] = (long long)(f0 ? f0 : TM_DIM) * w->in_features;
-    kinds[nj++] = (flags & TM_FLAG_X_F16) ? 1 : 0;   // fp16 copy when the bag itself is fp16
-    wl.fc1_w0 = ws + L.wr_fc1_0;
+    if (w->fc1_kind != TM_FC1_TOKENS) {
+      srcs[nj] = w->fc1_w0; dsts[nj] = ws + L.wr_fc1_0; cnt[nj] = (long long)(f0 ? f0 : TM_DIM) * w->in_features;
+      kinds[nj++] = (flags & TM_FLAG_X_F16) ? 1 : 0;   // fp16 copy when the bag itself is fp16
+      wl.fc1_w0 = ws + L.wr_fc1_0;
+    }
     if (f0) {
       srcs[nj] = w->fc1_w1; dsts[nj] = ws + L.wr_fc1_1; cnt[nj] = (long long)TM_DIM * f0; kinds[nj++] = 0;
       wl.fc1_w1 = ws + L.wr_fc1_1;

@@ -538,6 +538,7 @@ extern "C" int tm_transmil_fwd_sharded(const tm_weights* w, const float* x_rows,
   TM_CHECK_ARG(tc_available(), TM_ERR_UNSUPPORTED_ARCH, "tm_transmil_fwd_sharded needs an sm_100 device");
   TM_CHECK_ARG(!(flags & (TM_FLAG_SIMT_ONLY | TM_FLAG_X_F16 | TM_FLAG_KEEP_STAGES | TM_FLAG_PINV_GEMM_CHAIN)), TM_ERR_BAD_ARGUMENT,
                "tm_transmil_fwd_sharded: tensor-core engine, fp32 bag only (flags: 0 or TM_FLAG_NO_OVERLAP)");
+  TM_CHECK_ARG(w->fc1_kind != TM_FC1_TOKENS, TM_ERR_BAD_ARGUMENT, "tm_transmil_fwd_sharded: TM_FC1_TOKENS (per-tile bags of CTMIL) is not sharded");
   const tm_shard_plan& s = *plan;
   TM_CHECK_ARG(s.world == comm->world && s.rank == comm->rank, TM_ERR_BAD_ARGUMENT, "tm_transmil_fwd_sharded: plan is for rank %lld of %lld, comm for %d of %d",
                (long long)s.rank, (long long)s.world, comm->rank, comm->world);

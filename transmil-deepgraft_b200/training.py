@@ -278,6 +278,9 @@ def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0, 0, 0), drop=0.0, kee
     dhf = new(B, n, DIM)
     K.check(K.L.tm_dup_cls_bwd(dh0.data_ptr(), B, n, dup, dhf.data_ptr(), K.st))
     # seeds = (layer1 to_out, layer2 to_out, stem Dropout 0, stem Dropout 1); the stem's Dropout exists in the 768-d form only
+    if kind == capi.TM_FC1_TOKENS:   # the stem ran outside the library (CTMIL's conv stem): hand d(loss)/d(tokens) back to autograd
+        g["_dx"] = dhf
+        return g
     stem_drop = STEM768_DROPOUT if (drop > 0.0 and kind == capi.TM_FC1_768) else 0.0
     g.update(fc1_backward(K, p, kind, x, dhf, tuple(seeds[2:4]) if len(seeds) >= 4 else (0, 0), stem_drop))
     return g
@@ -330,14 +333,15 @@ def forward_keep_tc(model, x, training, seeds):
         ck(L.tm_cvt_f32(t.data_ptr(), o.data_ptr(), t.numel(), st))
         return o
 
-    f = model._fc1
     wt = capi.Weights.from_buffer_copy(w)
-    wt.fc1_w0 = tf32_copy(f[0].weight)
-    F0 = {capi.TM_FC1_SINGLE: 0, capi.TM_FC1_2048: 1024, capi.TM_FC1_768: 768}[model._fc1_kind]
-    if model._fc1_kind == capi.TM_FC1_2048:
-        wt.fc1_w1 = tf32_copy(f[3].weight)
-    elif model._fc1_kind == capi.TM_FC1_768:
-        wt.fc1_w1 = tf32_copy(f[4].weight)
+    F0 = {capi.TM_FC1_SINGLE: 0, capi.TM_FC1_2048: 1024, capi.TM_FC1_768: 768, capi.TM_FC1_TOKENS: 0}[model._fc1_kind]
+    if model._fc1_kind != capi.TM_FC1_TOKENS:
+        f = model._fc1
+        wt.fc1_w0 = tf32_copy(f[0].weight)
+        if model._fc1_kind == capi.TM_FC1_2048:
+            wt.fc1_w1 = tf32_copy(f[3].weight)
+        elif model._fc1_kind == capi.TM_FC1_768:
+            wt.fc1_w1 = tf32_copy(f[4].weight)
     if training and model._fc1_kind == capi.TM_FC1_768:   # Dropout(0.6) inside the stem (TransMIL.py:123-126)
         h0 = stem768_train_forward(Kernels(stream=st), {k: t.detach() for k, t in model.named_parameters()}, x, plan["dup"], seeds[2:4])
     else:
@@ -399,7 +403,7 @@ def forward_keep_simt(model, x, training, seeds):
     S, Sp, P, l, G = plan["S"], plan["Sp"], plan["P"], plan["l"], plan["G"]
     new = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
     flags = capi.TM_FLAG_SIMT_ONLY
-    F0 = {capi.TM_FC1_SINGLE: 0, capi.TM_FC1_2048: 1024, capi.TM_FC1_768: 768}[model._fc1_kind]
+    F0 = {capi.TM_FC1_SINGLE: 0, capi.TM_FC1_2048: 1024, capi.TM_FC1_768: 768, capi.TM_FC1_TOKENS: 0}[model._fc1_kind]
     if training and model._fc1_kind == capi.TM_FC1_768:   # Dropout(0.6) inside the stem (TransMIL.py:123-126)
         h0 = stem768_train_forward(Kernels(stream=st), {k: t.detach() for k, t in model.named_parameters()}, x, plan["dup"], seeds[2:4])
     else:
@@ -455,16 +459,17 @@ class TransMILFunction(torch.autograd.Function):
         bind(capi.lib())
         training = model.training
         seeds = tuple(int(s) for s in torch.randint(0, 2 ** 62, (4,))) if training else (0, 0, 0, 0)   # to_out x 2, 768-d stem x 2
-        with torch.cuda.device(x.device):
+        with _kernels_for(x)[0]:
             logits, saved, w = forward_keep(model, x, training, seeds)
-        ctx.model, ctx.x, ctx.saved, ctx.seeds, ctx.training = model, x, saved, seeds, training
-        ctx.names = [n for n, _ in model.named_parameters()]
+        ctx.model, ctx.x, ctx.saved, ctx.seeds, ctx.training = model, x.detach(), saved, seeds, training
+        ctx.names = [n for n, _ in model._path_named_parameters()]
         return logits
 
     @staticmethod
     def backward(ctx, dlogits):
         p, g = _param_grads(ctx, dlogits)
-        return (None, None) + tuple(g[n].reshape(p[n].shape) for n in ctx.names)
+        dx = g["_dx"].reshape(ctx.x.shape) if ("_dx" in g and ctx.needs_input_grad[1]) else None   # token stems only (CTMIL)
+        return (None, dx) + tuple(g[n].reshape(p[n].shape) for n in ctx.names)
 
 
 def _kernels_for(x):
@@ -478,14 +483,20 @@ def _param_grads(ctx, dlogits, keep_dxn=False):
     if ctx.saved is None:
         raise RuntimeError("libtransmil_b200: the stages kept by this forward were released by an earlier backward (the library "
                            "backward runs once per forward; call the model again instead of backward(retain_graph=True))")
-    p = {n: t.detach() for n, t in model.named_parameters()}
+    p = {n: t.detach() for n, t in model._path_named_parameters()}
+    ppeg = getattr(model, "PPEG_NAME", "pos_layer")
+    # the backward speaks TransMIL's names; sibling models call the PPEG block pos_layer_0 (CTMIL) and the classifier _fc2 (MDMIL)
+    canon = {(("pos_layer" + n[len(ppeg):]) if n.startswith(ppeg + ".") else n): t for n, t in p.items()}
     dev, K = _kernels_for(x)
     with dev:
-        g = backward(K, p, model._weights(), model._fc1_kind, x, ctx.saved, dlogits, ctx.seeds,
+        g = backward(K, canon, model._weights(), model._fc1_kind, x, ctx.saved, dlogits, ctx.seeds,
                      TO_OUT_DROPOUT if ctx.training else 0.0, keep_dxn)
     ctx.saved = None
-    if model.HEAD != "_fc":   # sibling models name the classifier differently (MDMIL._fc2)
+    if model.HEAD != "_fc":
         g[model.HEAD + ".weight"], g[model.HEAD + ".bias"] = g.pop("_fc.weight"), g.pop("_fc.bias")
+    if ppeg != "pos_layer":
+        for k in [k for k in g if k.startswith("pos_layer.")]:
+            g[ppeg + k[len("pos_layer"):]] = g.pop(k)
     return p, g
 
 
@@ -509,7 +520,7 @@ class _HookedFunction(torch.autograd.Function):
         with _kernels_for(x)[0]:
             logits, saved, _w = forward_keep(model, x, training, seeds)
         ctx.model, ctx.x, ctx.saved, ctx.seeds, ctx.training = model, x, saved, seeds, training
-        ctx.names = [n for n, _ in model.named_parameters()]
+        ctx.names = [n for n, _ in model._path_named_parameters()]
         ctx.hooked, ctx.P, ctx.holder = hooked, int(saved["plan"]["P"]), holder
         holder.ctx = ctx
         holder.inputs = {"layer1": saved["h0"], "layer2": saved["h2"]}
@@ -551,7 +562,7 @@ def forward_with_norm_hooks(model, x, hooked):
     is called as `hook(norm_module, (layer input [B,S,512],), LayerNorm output [B,S,512])`, the way torch calls it in the
     reference, where TransLayer runs `self.norm(x)` (TransMIL.py:47).  Hooks that return a replacement output are refused."""
     holder = _Holder()
-    outs = _HookedFunction.apply(model, x, holder, tuple(hooked), *model.parameters())
+    outs = _HookedFunction.apply(model, x, holder, tuple(hooked), *model._path_parameters())
     logits, acts = outs[0], outs[1:]
     for name, act in zip(hooked, acts):
         norm = getattr(model, name).norm

@@ -20,7 +20,7 @@ import torch.nn as nn
 
 from . import capi
 
-__all__ = ["TransMIL", "MDMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention"]
+__all__ = ["TransMIL", "MDMIL", "CTMIL", "TransformerMIL", "TransLayer", "PPEG", "NystromAttention", "LazyAttention"]
 
 
 class NystromAttention(nn.Module):
@@ -85,6 +85,7 @@ def _fc1_1024_else_form():
 
 class TransMIL(nn.Module):
     HEAD = "_fc"   # attribute / state_dict name of the classifier Linear (TransMIL.py:155); MDMIL calls it _fc2
+    PPEG_NAME = "pos_layer"   # ... and of the PPEG block (TransMIL.py:91); CTMIL / TransformerMIL call it pos_layer_0
 
     def __init__(self, n_classes, in_features, out_features=512):
         super().__init__()
@@ -165,7 +166,7 @@ class TransMIL(nn.Module):
     def _weights(self):
         w = capi.Weights()
         w.fc1_kind, w.in_features, w.n_classes = self._fc1_kind, self.in_features, self.n_classes
-        f = self._fc1
+        f = getattr(self, "_fc1", None)
         D = self.in_features
         if self._fc1_kind == capi.TM_FC1_2048:
             w.fc1_w0, w.fc1_b0 = self._ptr(f[0].weight, (1024, D)), self._ptr(f[0].bias)
@@ -176,6 +177,8 @@ class TransMIL(nn.Module):
             w.fc1_ln_w, w.fc1_ln_b = self._ptr(f[3].weight, (768,)), self._ptr(f[3].bias)
             w.fc1_w1, w.fc1_b1 = self._ptr(f[4].weight, (512, 768)), self._ptr(f[4].bias)
             w.fc1_ln2_w, w.fc1_ln2_b = self._ptr(f[7].weight, (512,)), self._ptr(f[7].bias)
+        elif self._fc1_kind == capi.TM_FC1_TOKENS:
+            pass     # the stem runs outside the library (conv stem of CTMIL): the bag already holds 512-d tokens
         else:
             w.fc1_w0, w.fc1_b0 = self._ptr(f[0].weight, (512, D)), self._ptr(f[0].bias)
         w.cls_token = self._ptr(self.cls_token, (1, 1, 512))
@@ -185,7 +188,7 @@ class TransMIL(nn.Module):
             lw.qkv_w = self._ptr(layer.attn.to_qkv.weight, (1536, 512))
             lw.out_w, lw.out_b = self._ptr(layer.attn.to_out[0].weight, (512, 512)), self._ptr(layer.attn.to_out[0].bias)
             lw.conv_w = self._ptr(layer.attn.res_conv.weight, (8, 1, 33, 1))
-        p = self.pos_layer
+        p = getattr(self, self.PPEG_NAME)
         w.ppeg_w7, w.ppeg_b7 = self._ptr(p.proj.weight, (512, 1, 7, 7)), self._ptr(p.proj.bias)
         w.ppeg_w5, w.ppeg_b5 = self._ptr(p.proj1.weight, (512, 1, 5, 5)), self._ptr(p.proj1.bias)
         w.ppeg_w3, w.ppeg_b3 = self._ptr(p.proj2.weight, (512, 1, 3, 3)), self._ptr(p.proj2.bias)
@@ -283,14 +286,27 @@ class TransMIL(nn.Module):
         device = self.cls_token.device
         if device.type != "cuda":
             raise capi.TransmilError("TransMIL must be on a CUDA device (model.cuda()); there is no CPU path")
-        if x.requires_grad:
+        tokens_in = self._fc1_kind == capi.TM_FC1_TOKENS and x.requires_grad   # tokens of a torch stem: d/d(tokens) is returned
+        if x.requires_grad and not tokens_in:
             raise NotImplementedError("libtransmil_b200: the bag requires grad, but the library's backward differentiates the parameters "
                                       "only (d/dx through _fc1 is not built; the reference's bags are leaf features without grad)")
-        xd = x.detach().to(device=device, dtype=torch.float32, non_blocking=True).contiguous()   # x.float(), TransMIL.py:174
         hooked = self._hooked_norms()
+        if tokens_in:
+            if hooked:
+                raise NotImplementedError("libtransmil_b200: norm hooks together with a differentiated token stem are not built")
+            return training.TransMILFunction.apply(self, x.to(device=device, dtype=torch.float32).contiguous(), *self._path_parameters())
+        xd = x.detach().to(device=device, dtype=torch.float32, non_blocking=True).contiguous()   # x.float(), TransMIL.py:174
         if hooked:
             return training.forward_with_norm_hooks(self, xd, hooked)
-        return training.TransMILFunction.apply(self, xd, *self.parameters())
+        return training.TransMILFunction.apply(self, xd, *self._path_parameters())
+
+    def _path_named_parameters(self):
+        """The parameters the library's path reads and differentiates: all of them for TransMIL / MDMIL; the sibling models
+        with a torch stem (CTMIL, TransformerMIL) keep further sub-modules the path never touches."""
+        return list(self.named_parameters())
+
+    def _path_parameters(self):
+        return [p for _, p in self._path_named_parameters()]
 
     def stage(self, name):
         """Per-stage buffer of the last forward (needs flags |= TM_FLAG_KEEP_STAGES); parity tests only."""
@@ -424,6 +440,153 @@ class MDMIL(TransMIL):
             return TransMIL.forward(self, x), None
         logits, (attn, _padding) = TransMIL.forward(self, x, return_attn=True)
         return logits, attn
+
+
+class CTMIL(TransMIL):
+    """Sibling model of the same path: /root/reference/code/models/CTMIL.py:76-165.
+
+    `CTMIL(n_classes, in_features)` takes image-like tiles `[1, N, in_features, H, H]`, runs a two-stage conv stem on every
+    tile (CTMIL.py:90-101,137-142: Conv3x3 -> BatchNorm -> GELU -> MaxPool(3,2,1), twice), REINTERPRETS the `[N,512,h,h]`
+    result as `[N, h*h, 512]` tokens with `.view` (CTMIL.py:142 -- a view, not a transpose), and sends every tile as its own
+    bag through duplicate pad + cls, TransLayer, PPEG, TransLayer, LayerNorm, `_fc2` (CTMIL.py:143-165): logits `[N, n_classes]`.
+    The conv stem is four stock torch modules (cuDNN / ATen: library code, outside SURVEY 8's hot path; "zero new kernels");
+    everything from the tokens on is ONE `tm_transmil_fwd` call with `TM_FC1_TOKENS`.  Sub-modules are created in the
+    reference's order (pos_layer_0, conv1, conv2, _fc1 -- which the reference builds but never calls --, cls_token, layer1,
+    layer2, norm, _fc2) so the seeded init and the state_dict keys are identical.  With autograd on, d(loss)/d(tokens) comes back
+    from the library's backward and torch differentiates the conv stem."""
+    HEAD = "_fc2"
+    PPEG_NAME = "pos_layer_0"
+    _PATH_PREFIXES = ("pos_layer_0.", "cls_token", "layer1.", "layer2.", "norm.", "_fc2.")
+
+    def __init__(self, n_classes, in_features, out_features=512):
+        nn.Module.__init__(self)
+        if out_features != 512:
+            raise ValueError("libtransmil_b200 implements out_features=512 (the only value the reference configs use)")
+        self.pos_layer_0 = PPEG(dim=out_features)
+        norm_layer = nn.LayerNorm
+        self._make_conv_stem(in_features, out_features)
+        if in_features == 2048:      # CTMIL.py:103-108 (built, never called by forward)
+            self._fc1 = nn.Sequential(nn.Linear(in_features, int(in_features / 2), bias=True),
+                                      nn.Linear(int(in_features / 2), out_features), nn.GELU())
+        elif in_features == 1024:    # CTMIL.py:109-113
+            self._fc1 = nn.Sequential(nn.Linear(in_features, out_features), nn.GELU(), nn.Dropout(p=0.6), norm_layer(out_features))
+        elif in_features == 768:     # CTMIL.py:114-115
+            self._fc1 = nn.Sequential(nn.Linear(in_features, 512, bias=True), nn.ReLU())
+        self._finish(n_classes, out_features)
+
+    def _make_conv_stem(self, in_features, out_features):
+        half = int(in_features / 2)  # CTMIL.py:90-101
+        self.conv1 = nn.Sequential(nn.Conv2d(in_features, half, kernel_size=3, stride=1, padding=1, bias=False),
+                                   nn.BatchNorm2d(half), nn.GELU(), nn.MaxPool2d(kernel_size=3, stride=2, padding=1))
+        self.conv2 = nn.Sequential(nn.Conv2d(half, out_features, kernel_size=3, stride=1, padding=1, bias=False),
+                                   nn.BatchNorm2d(out_features), nn.GELU(), nn.MaxPool2d(kernel_size=3, stride=2, padding=1))
+
+    def _finish(self, n_classes, out_features):
+        self.cls_token = nn.Parameter(torch.randn(1, 1, out_features))
+        self.n_classes = n_classes
+        self.in_features = out_features          # what the library's path is fed: 512-d tokens
+        self._fc1_kind = capi.TM_FC1_TOKENS
+        self.layer1 = TransLayer(dim=out_features)
+        self.layer2 = TransLayer(dim=out_features)
+        self.norm = nn.LayerNorm(out_features)
+        self._fc2 = nn.Linear(out_features, self.n_classes)
+        self.flags = 0
+        self.keep_graph = False
+        self.skip_unread_rows = False
+        self._ws = None
+        self._stage_key = None
+
+    def _path_named_parameters(self):
+        return [(n, p) for n, p in self.named_parameters() if n.startswith(self._PATH_PREFIXES)]
+
+    def tokens(self, x):
+        """CTMIL.py:137-142: tiles [1,N,C,H,H] (or [N,C,H,H]) -> tokens [N, h*h, 512] through the torch conv stem."""
+        if x.dim() == 5:
+            x = x.squeeze(0)
+        if x.dim() != 4:
+            raise ValueError(f"expected image tiles [1, N, C, H, H], got {tuple(x.shape)}")
+        device = self.cls_token.device
+        if device.type != "cuda":
+            raise capi.TransmilError("CTMIL must be on a CUDA device (model.cuda()); there is no CPU path")
+        h = self.conv2(self.conv1(x.to(device=device, dtype=torch.float32)))
+        return h.view(h.shape[0], h.shape[2] * h.shape[2], h.shape[1])
+
+    def forward(self, x):
+        return TransMIL.forward(self, self.tokens(x))
+
+
+class _PreNorm(nn.Module):
+    """Parameter container of code/models/_transformer.py:6-13."""
+
+    def __init__(self, dim, fn):
+        super().__init__()
+        self.norm = nn.LayerNorm(dim)
+        self.fn = fn
+
+
+class _Attention(nn.Module):
+    """Parameter container of code/models/_transformer.py:16-42 (plain softmax attention: not on the Nystrom path)."""
+
+    def __init__(self, dim, heads, dim_head, dropout):
+        super().__init__()
+        inner = dim_head * heads
+        self.to_qkv = nn.Linear(dim, inner * 3, bias=False)
+        self.to_out = nn.Sequential(nn.Linear(inner, dim), nn.Dropout(dropout))
+
+
+class _FeedForward(nn.Module):
+    """Parameter container of code/models/_transformer.py:45-57."""
+
+    def __init__(self, dim, hidden_dim, dropout):
+        super().__init__()
+        self.net = nn.Sequential(nn.Linear(dim, hidden_dim), nn.GELU(), nn.Dropout(dropout), nn.Linear(hidden_dim, dim), nn.Dropout(dropout))
+
+
+class _Transformer(nn.Module):
+    """Parameter container of TransformerMIL.py:18-26."""
+
+    def __init__(self, dim, depth, heads, dim_head, mlp_dim, dropout=0.0):
+        super().__init__()
+        self.layers = nn.ModuleList([nn.ModuleList([_PreNorm(dim, _Attention(dim, heads, dim_head, dropout)),
+                                                    _PreNorm(dim, _FeedForward(dim, mlp_dim, dropout))]) for _ in range(depth)])
+
+
+class TransformerMIL(CTMIL):
+    """The Nystrom forward of /root/reference/code/models/TransformerMIL.py.
+
+    The reference file holds two forwards: the live one (TransformerMIL.py:137-151, a plain softmax-attention transformer over
+    `fc1` features -- not the Nystrom path, not built: `forward_plain` raises) and the commented-out one
+    (TransformerMIL.py:155-183), which is CTMIL's: conv stem on tiles, tokens by `.view`, duplicate pad + cls, TransLayer,
+    PPEG, TransLayer, LayerNorm, `_fc2`.  `forward` here is that Nystrom forward on this class's own parameters.  The
+    constructor mirrors TransformerMIL.py:76-135 sub-module by sub-module (pos_layer_0, conv1, conv2, fc1, cls_token, layer1,
+    layer2, norm, _fc2, transformer1, transformer2) so the seeded init and the state_dict keys are identical; `fc1`,
+    `transformer1/2` are parameter containers the Nystrom forward never reads."""
+
+    def __init__(self, n_classes, in_features, out_features=512):
+        nn.Module.__init__(self)
+        if out_features != 512:
+            raise ValueError("libtransmil_b200 implements out_features=512 (the only value the reference configs use)")
+        self.pos_layer_0 = PPEG(dim=out_features)
+        norm_layer = nn.LayerNorm
+        self._make_conv_stem(in_features, out_features)
+        if in_features == 2048:      # TransformerMIL.py:106-110
+            self.fc1 = nn.Sequential(nn.Linear(in_features, int(in_features / 2)), nn.GELU(), nn.Dropout(p=0.6), norm_layer(int(in_features / 2)),
+                                     nn.Linear(int(in_features / 2), out_features), nn.GELU())
+        elif in_features == 1024:    # TransformerMIL.py:111-115
+            self.fc1 = nn.Sequential(nn.Linear(in_features, out_features), nn.GELU(), nn.Dropout(p=0.6), norm_layer(out_features))
+        elif in_features in (768, 384):   # TransformerMIL.py:116-119
+            self.fc1 = nn.Sequential(nn.Linear(in_features, 512, bias=True), nn.ReLU())
+        self._finish(n_classes, out_features)
+        dropout, emb_dropout = 0.5, 0.5   # TransformerMIL.py:129-135
+        self.transformer1 = _Transformer(dim=out_features, depth=2, dim_head=64, heads=8, mlp_dim=512, dropout=dropout)
+        self.transformer2 = _Transformer(dim=out_features, depth=2, dim_head=64, heads=8, mlp_dim=512, dropout=dropout)
+        self.dropout = nn.Dropout(emb_dropout)
+        self.to_latent = nn.Identity()
+        self.pool = "cls"
+
+    def forward_plain(self, x):
+        raise NotImplementedError("libtransmil_b200: the plain softmax-attention forward of TransformerMIL.py:137-151 is not on the "
+                                  "Nystrom path and is not built; forward() is the Nystrom forward of TransformerMIL.py:155-183")
 
 
 def y_prob_y_hat(logits):
