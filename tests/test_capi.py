@@ -108,3 +108,39 @@ def test_sharded_entry_points_refuse_loudly_without_a_gpu(built_lib):
         assert L.tm_last_error()
     code = C.c_int32(7)
     assert L.tm_shard_comm_status(None, C.byref(code)) != 0
+
+
+def test_header_is_plain_c_and_a_c_host_links_against_the_library(built_lib, tmp_path):
+    """include/transmil_b200.h is the boundary for hosts in any language: it must compile as strict C99 (no C++-isms, no torch or
+    CUDA headers), and a C program linked against libtransmil_b200.so reaches the host-only entry points (no device needed)."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    src = tmp_path / "host.c"
+    src.write_text(r'''
+#include <stdio.h>
+#include <string.h>
+#include "transmil_b200.h"
+int main(void) {
+  tm_plan p;
+  if (tm_make_plan(50000, &p) != TM_OK) return 1;
+  if (p.G != 224 || p.S != 50177 || p.Sp != 50432 || p.P != 255 || p.l != 197) return 2;     /* SURVEY 8, cfg 3 */
+  tm_weights w;
+  memset(&w, 0, sizeof w);
+  w.fc1_kind = TM_FC1_TOKENS; w.in_features = 768; w.n_classes = 2;
+  size_t bytes = 0;
+  if (tm_workspace_bytes(1, 100, &w, 0, &bytes) == TM_OK) return 3;                          /* NULL parameters are refused */
+  if (strlen(tm_last_error()) == 0) return 4;
+  if (tm_attn3v_tc_fwd_static(&p, &p, &p, 19, 256, (float*)&p, 0, 0) != TM_ERR_BAD_SHAPE) return 5;   /* beyond the static array */
+  printf("%s\n", tm_version());
+  return 0;
+}
+''')
+    exe = tmp_path / "host"
+    libdir = os.path.dirname(built_lib)
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                    "-L", libdir, "-ltransmil_b200", "-Wl,-rpath," + libdir], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "sm_100a" in r.stdout

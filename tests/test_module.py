@@ -137,11 +137,14 @@ def test_validation_step_mirror_follows_the_reference():
 
         def forward(self, x):
             assert not torch.is_grad_enabled() and x.dtype == torch.float32 and x.is_contiguous()
+            assert not self.training          # Lightning's validation loop: eval() for the duration of the step
             return x.sum(1)[:, :3]
 
     x = torch.randn(2, 5, 4, dtype=torch.float64)
     label = torch.tensor([2, 0])
-    out = plugin.validation_step(Stub(), (x, label, (("slide_a", "slide_b"), None, ("p1", "p2"))))
+    stub = Stub().train()
+    out = plugin.validation_step(stub, (x, label, (("slide_a", "slide_b"), None, ("p1", "p2"))))
+    assert stub.training              # ... and the mode it came in is restored
     logits = x.float().sum(1)[:, :3]
     assert torch.equal(out["logits"], logits) and torch.equal(out["Y_hat"], logits.argmax(1))
     assert torch.allclose(out["Y_prob"], logits.softmax(1)) and out["label"].dtype == torch.int32

@@ -73,3 +73,9 @@ def test_768_stem_training_mode_on_device(built_lib):
         opt.step()
         losses.append(loss.item())
     assert min(losses[-4:]) < losses[0], losses
+    # train() under no_grad: the reference's Dropout layers stay active there too; eval() is deterministic
+    with torch.no_grad():
+        a, b = m(x), m(x)
+        assert not a.requires_grad and not torch.equal(a, b)
+        m.eval()
+        assert torch.equal(m(x), m(x))

@@ -108,8 +108,15 @@ def validation_step(model, batch):
     inference path (no autograd) whatever mode the module is in, as Lightning's validation loop does."""
     import torch
     input, label, (wsi_name, _, patient) = batch
-    with torch.no_grad():
-        logits, Y_prob, Y_hat = step(model, input)
+    was_training = bool(getattr(model, "training", False))
+    if was_training:
+        model.eval()            # Lightning's validation loop puts the module in eval(): Dropout off
+    try:
+        with torch.no_grad():
+            logits, Y_prob, Y_hat = step(model, input)
+    finally:
+        if was_training:
+            model.train()
     logits, Y_prob, Y_hat = logits.detach(), Y_prob.detach(), Y_hat.detach()
     loss = cross_entropy_torch(logits, label)
     return {"logits": logits, "Y_prob": Y_prob, "Y_hat": Y_hat, "label": torch.as_tensor(label).int(), "name": wsi_name,

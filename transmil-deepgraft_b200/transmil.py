@@ -226,6 +226,14 @@ class TransMIL(nn.Module):
         device = self.cls_token.device
         if device.type != "cuda":
             raise capi.TransmilError("TransMIL must be on a CUDA device (model.cuda()); there is no CPU path")
+        if self.training and not return_attn:
+            # train() under no_grad: the reference's Dropout layers (to_out 0.7, the 768-d stem's 0.6) are still active, so this is
+            # the training forward without a graph, not the eval fast path
+            from . import training
+            xd = x.detach().to(device=device, dtype=torch.float32, non_blocking=True).contiguous()
+            seeds = tuple(int(s) for s in torch.randint(0, 2 ** 62, (4,)))
+            with torch.cuda.device(device):
+                return training.forward_keep(self, xd, True, seeds)[0]
         L = capi.lib()
         B, n, D = (int(s) for s in x.shape)
         flags = int(self.flags) | (capi.TM_FLAG_KEEP_STAGES if return_attn else 0)
