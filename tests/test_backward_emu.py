@@ -224,11 +224,15 @@ def test_stem_backward_of_every_fc1_form(K, T, D, n, B):
     sd = {k: v.detach().contiguous() for k, v in m.state_dict().items()}
     x = make_input("randn", B, n, D, 78)
     dh = torch.randn(B, n, 512, generator=torch.Generator().manual_seed(14))
-    _, ref = OB.fc1_backward({k: v.double() for k, v in sd.items()}, x.double(), dh.double())
+    ref_dx, ref = OB.fc1_backward({k: v.double() for k, v in sd.items()}, x.double(), dh.double())
     g = training.fc1_backward(K, sd, m._fc1_kind, x.contiguous(), dh.clone())
     assert set(g) == set(ref) == {k for k in sd if k.startswith("_fc1.")}
     for k in sorted(ref):
         _close(g[k].reshape(ref[k].shape), ref[k], 1e-3, k)
+    # a bag that requires grad: d/dx through the stem as well (the reference's autograd propagates it; TransMIL.py:175)
+    g = training.fc1_backward(K, sd, m._fc1_kind, x.contiguous(), dh.clone(), want_dx=True)
+    _close(g.pop("_dx"), ref_dx, 1e-3, "dx")
+    assert set(g) == set(ref)
 
 
 def test_gradcam_style_hook_on_layer2_norm(K, T, monkeypatch):
@@ -399,3 +403,27 @@ def _saved_from_oracle_tokens(sd, tok):
         sv["M"] = (s["Z"] @ s["W3"]).contiguous()
         saved[name] = sv
     return logits, {k: (v.contiguous() if torch.is_tensor(v) else v) for k, v in saved.items()}
+
+
+def test_bag_that_requires_grad_gets_its_gradient_through_the_stem(K, T, monkeypatch):
+    """x.requires_grad (saliency-style consumers): the reference's autograd reaches the bag through _fc1 (TransMIL.py:175); the
+    library's autograd Function returns the same d(loss)/dx, and the parameter gradients are unchanged."""
+    import contextlib
+    from transmil_b200 import training
+    D, nc, n, B = 96, 3, 70, 2
+    m = build_model(nc, D)
+    m.keep_graph = True
+    sd = {k: v.detach().contiguous() for k, v in m.state_dict().items()}
+    x = make_input("randn", B, n, D, 82).requires_grad_(True)
+    dlogits = torch.randn(B, nc, generator=torch.Generator().manual_seed(18))
+    monkeypatch.setattr(training, "_kernels_for", lambda t: (contextlib.nullcontext(), K))
+    monkeypatch.setattr(training, "forward_keep", lambda model, t, tr, seeds: (*_saved_from_oracle(sd, t), None))
+    monkeypatch.setattr(training, "bind", lambda lib: lib)
+    monkeypatch.setattr(T.capi, "lib", lambda: K.L)
+    m._weights = lambda: _weights(T, sd, m._fc1_kind, D, nc)
+    logits = training.TransMILFunction.apply(m, x, *m._path_parameters())
+    (logits * dlogits).sum().backward()
+    ref, ref_dx = OB.backward(sd, x.detach(), dlogits.double())
+    _close(x.grad, ref_dx, 2e-3, "d(loss)/dx")
+    for k, prm in m.named_parameters():
+        _close(prm.grad, ref[k].reshape(prm.shape), 2e-3, k)

@@ -81,6 +81,21 @@ def test_parameter_gradients_match_the_backward_oracle(T, D, nc, n, B, engine):
         _close(p.grad, ref[k].reshape(p.shape), GRAD_RTOL[engine], k)
 
 
+@pytest.mark.parametrize("D,n,B", [(512, 300, 2), (2048, 200, 1), (768, 100, 1)])
+def test_bag_that_requires_grad_gets_its_gradient(T, D, n, B, engine):
+    """x.requires_grad: d(loss)/dx through _fc1 (the reference's autograd reaches the bag, TransMIL.py:175) vs the oracle's dx."""
+    m = build_model(2, D).cuda()
+    m.keep_graph = True
+    x = make_input("randn", B, n, D, 83)
+    dlogits = torch.randn(B, 2, generator=torch.Generator().manual_seed(19))
+    xd = x.cuda().requires_grad_(True)
+    m(xd).backward(dlogits.cuda())
+    sd = {k: v.detach().cpu() for k, v in m.state_dict().items()}
+    ref, ref_dx = OB.backward(sd, x, dlogits.double())
+    _close(xd.grad, ref_dx, max(GRAD_RTOL[engine], 5e-5), "dx")
+    _close(m._fc1[0].weight.grad, ref["_fc1.0.weight"], GRAD_RTOL[engine], "_fc1.0.weight")
+
+
 def test_training_step_runs_and_learns(T):
     """train(): to_out Dropout(0.7) active, CE loss, a few SGD steps on one bag drive the loss down; gradients finite."""
     m = build_model(2, 1024).cuda()

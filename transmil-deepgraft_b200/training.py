@@ -193,18 +193,24 @@ def stem768_train_forward(K, p, x, dup, seeds):
     return h0
 
 
-def fc1_backward(K, p, kind, x, dhf, stem_seeds=(0, 0), stem_drop=0.0):
-    """Backward of TransMIL._fc1 (TransMIL.py:100-133) for the parameters (the bag x is a leaf without gradient).  The stem's
-    pre-activations are recomputed.  oracle/transmil_backward.py fc1_backward."""
+def fc1_backward(K, p, kind, x, dhf, stem_seeds=(0, 0), stem_drop=0.0, want_dx=False):
+    """Backward of TransMIL._fc1 (TransMIL.py:100-133) for the parameters and, when `want_dx` (the bag requires grad: the
+    reference's autograd would propagate through _fc1 too), for the bag: g["_dx"] = dz0 . W0, one more contraction.  The
+    stem's pre-activations are recomputed.  oracle/transmil_backward.py fc1_backward."""
     B, n, D = x.shape
     R = B * n
     g = {}
     xf = x.reshape(R, D)
     dhf = dhf.reshape(R, DIM)
+
+    def dx_from(dz0, F0):
+        if want_dx:
+            g["_dx"] = K.gemm(dz0, (F0, 1), p["_fc1.0.weight"], (D, 1), K.new(dz0, B, n, D), R, D, F0, D)
     if kind == capi.TM_FC1_SINGLE:
         z0 = _linear_fwd(K, xf, p["_fc1.0.weight"], p["_fc1.0.bias"], R, D, DIM)
         K.check(K.L.tm_gelu_bwd(z0.data_ptr(), dhf.data_ptr(), z0.data_ptr(), R * DIM, K.st))
         _linear_wgrad(K, z0, xf, g, "_fc1.0", R, D, DIM)
+        dx_from(z0, DIM)
         return g
     if kind == capi.TM_FC1_2048:
         F0 = p["_fc1.0.weight"].shape[0]
@@ -220,6 +226,7 @@ def fc1_backward(K, p, kind, x, dhf, stem_seeds=(0, 0), stem_drop=0.0):
         da0, g["_fc1.2.weight"], g["_fc1.2.bias"] = K.ln_bwd(a0, p["_fc1.2.weight"], da1, R, F0, R, R, 0, None)
         K.check(K.L.tm_gelu_bwd(z0.data_ptr(), da0.data_ptr(), z0.data_ptr(), R * F0, K.st))            # z0 <- dz0
         _linear_wgrad(K, z0, xf, g, "_fc1.0", R, D, F0)
+        dx_from(z0, F0)
         return g
     if kind == capi.TM_FC1_768:
         # Linear GELU [Dropout] LN(768) Linear(768,512) GELU [Dropout] LN(512) (TransMIL.py:123-126); stem_drop = 0.6 in train()
@@ -235,11 +242,12 @@ def fc1_backward(K, p, kind, x, dhf, stem_seeds=(0, 0), stem_drop=0.0):
         _drop(K, da0, stem_seeds[0], stem_drop)
         K.check(K.L.tm_gelu_bwd(z0.data_ptr(), da0.data_ptr(), z0.data_ptr(), R * F0, K.st))            # z0 <- dz0
         _linear_wgrad(K, z0, xf, g, "_fc1.0", R, D, F0)
+        dx_from(z0, F0)
         return g
     raise ValueError(f"unknown _fc1 kind {kind}")
 
 
-def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0, 0, 0), drop=0.0, keep_dxn=False):
+def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0, 0, 0), drop=0.0, keep_dxn=False, want_dx=False):
     """Gradients of sum(logits * dlogits) for every parameter (reference state_dict keys).  p: name -> parameter tensor,
     w: capi.Weights of the same tensors, saved: stages kept by the forward.  Stage order = reverse of TransMIL.forward
     (TransMIL.py:167-211); mirrors oracle/transmil_backward.py backward()."""
@@ -282,7 +290,7 @@ def backward(K, p, w, kind, x, saved, dlogits, seeds=(0, 0, 0, 0), drop=0.0, kee
         g["_dx"] = dhf
         return g
     stem_drop = STEM768_DROPOUT if (drop > 0.0 and kind == capi.TM_FC1_768) else 0.0
-    g.update(fc1_backward(K, p, kind, x, dhf, tuple(seeds[2:4]) if len(seeds) >= 4 else (0, 0), stem_drop))
+    g.update(fc1_backward(K, p, kind, x, dhf, tuple(seeds[2:4]) if len(seeds) >= 4 else (0, 0), stem_drop, want_dx))
     return g
 
 
@@ -467,8 +475,8 @@ class TransMILFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dlogits):
-        p, g = _param_grads(ctx, dlogits)
-        dx = g["_dx"].reshape(ctx.x.shape) if ("_dx" in g and ctx.needs_input_grad[1]) else None   # token stems only (CTMIL)
+        p, g = _param_grads(ctx, dlogits, want_dx=ctx.needs_input_grad[1])
+        dx = g["_dx"].reshape(ctx.x.shape) if ("_dx" in g and ctx.needs_input_grad[1]) else None   # a bag / token tensor that requires grad
         return (None, dx) + tuple(g[n].reshape(p[n].shape) for n in ctx.names)
 
 
@@ -477,7 +485,7 @@ def _kernels_for(x):
     return torch.cuda.device(x.device), Kernels(stream=torch.cuda.current_stream(x.device).cuda_stream)
 
 
-def _param_grads(ctx, dlogits, keep_dxn=False):
+def _param_grads(ctx, dlogits, keep_dxn=False, want_dx=False):
     """The library backward for what a forward kept on `ctx`: (parameters by name, gradients by name)."""
     model, x = ctx.model, ctx.x
     if ctx.saved is None:
@@ -490,7 +498,7 @@ def _param_grads(ctx, dlogits, keep_dxn=False):
     dev, K = _kernels_for(x)
     with dev:
         g = backward(K, canon, model._weights(), model._fc1_kind, x, ctx.saved, dlogits, ctx.seeds,
-                     TO_OUT_DROPOUT if ctx.training else 0.0, keep_dxn)
+                     TO_OUT_DROPOUT if ctx.training else 0.0, keep_dxn, want_dx)
     ctx.saved = None
     if model.HEAD != "_fc":
         g[model.HEAD + ".weight"], g[model.HEAD + ".bias"] = g.pop("_fc.weight"), g.pop("_fc.bias")

@@ -294,14 +294,12 @@ class TransMIL(nn.Module):
         device = self.cls_token.device
         if device.type != "cuda":
             raise capi.TransmilError("TransMIL must be on a CUDA device (model.cuda()); there is no CPU path")
-        tokens_in = self._fc1_kind == capi.TM_FC1_TOKENS and x.requires_grad   # tokens of a torch stem: d/d(tokens) is returned
-        if x.requires_grad and not tokens_in:
-            raise NotImplementedError("libtransmil_b200: the bag requires grad, but the library's backward differentiates the parameters "
-                                      "only (d/dx through _fc1 is not built; the reference's bags are leaf features without grad)")
         hooked = self._hooked_norms()
-        if tokens_in:
+        if x.requires_grad:
+            # the bag (or the tokens of a torch stem, CTMIL) is part of a graph: d(loss)/dx comes back from the library's backward
+            # (one more contraction through _fc1), as the reference's autograd would deliver it
             if hooked:
-                raise NotImplementedError("libtransmil_b200: norm hooks together with a differentiated token stem are not built")
+                raise NotImplementedError("libtransmil_b200: norm hooks together with a bag that requires grad are not built")
             return training.TransMILFunction.apply(self, x.to(device=device, dtype=torch.float32).contiguous(), *self._path_parameters())
         xd = x.detach().to(device=device, dtype=torch.float32, non_blocking=True).contiguous()   # x.float(), TransMIL.py:174
         if hooked:
