@@ -258,7 +258,15 @@ def test_gradcam_style_hook_on_layer2_norm(K, T, monkeypatch):
         out.register_hook(lambda gr: seen.__setitem__("grad", gr.detach().clone()))
 
     m.layer2.norm.register_forward_hook(hook)
-    logits = training.forward_with_norm_hooks(m, x, ["layer2"])
+    final = {}
+
+    def final_hook(mod, inp, out):      # visualize_mil.py:227 targets the FINAL LayerNorm (model.norm)
+        final["module"], final["input"], final["act"] = mod, inp[0], out.detach().clone()
+        out.register_hook(lambda gr: final.__setitem__("grad", gr.detach().clone()))
+
+    m.norm.register_forward_hook(final_hook)
+    assert m._hooked_norms() == ["layer2", "norm"]
+    logits = training.forward_with_norm_hooks(m, x, ["layer2", "norm"])
     (logits * dlogits).sum().backward()
     # reference: float64 oracle, layer 2 re-run from its LayerNorm output under autograd
     sd64 = {k: v.double() for k, v in sd.items()}
@@ -266,9 +274,16 @@ def test_gradcam_style_hook_on_layer2_norm(K, T, monkeypatch):
     h2 = st["h2"]
     xn = F.layer_norm(h2, (512,), sd64["layer2.norm.weight"], sd64["layer2.norm.bias"], 1e-5).requires_grad_(True)
     h3 = h2 + O.nystrom(sd64, "layer2.attn.", xn)
-    out = F.linear(F.layer_norm(h3, (512,), sd64["norm.weight"], sd64["norm.bias"], 1e-5)[:, 0], sd64["_fc.weight"], sd64["_fc.bias"])
+    hn = F.layer_norm(h3, (512,), sd64["norm.weight"], sd64["norm.bias"], 1e-5)
+    hn.retain_grad()
+    out = F.linear(hn[:, 0], sd64["_fc.weight"], sd64["_fc.bias"])
     _close(out, ref_logits, 1e-9, "oracle layer-2 replay")
     (out * dlogits.double()).sum().backward()
+    assert final["module"] is m.norm and final["act"].shape == (B, n_tokens(n), 512)
+    _close(final["input"], h3.detach(), 1e-5, "final-norm hook input (h3)")
+    _close(final["act"], hn.detach(), 1e-5, "final-norm hook output (LayerNorm(h3), every row)")
+    _close(final["grad"], hn.grad, 1e-5, "gradient delivered to the final-norm activation (cls row only)")
+    assert final["grad"][:, 1:].abs().max().item() == 0.0
     assert seen["module"] is m.layer2.norm and seen["act"].shape == (B, n_tokens(n), 512)
     _close(seen["input"], h2, 1e-5, "hook input (layer input h2)")
     _close(seen["act"], xn.detach(), 1e-5, "hook output (LayerNorm(h2))")
@@ -427,3 +442,28 @@ def test_bag_that_requires_grad_gets_its_gradient_through_the_stem(K, T, monkeyp
     _close(x.grad, ref_dx, 2e-3, "d(loss)/dx")
     for k, prm in m.named_parameters():
         _close(prm.grad, ref[k].reshape(prm.shape), 2e-3, k)
+
+
+def test_hooks_fire_without_a_graph(K, T, monkeypatch):
+    """training.fire_hooks_no_graph: hook(norm_module, (input,), LayerNorm(input)) for layer norms and the final norm."""
+    import contextlib
+    from transmil_b200 import training
+    m = build_model(2, 512)
+    monkeypatch.setattr(training, "_kernels_for", lambda t: (contextlib.nullcontext(), K))
+    g = torch.Generator().manual_seed(22)
+    h = {nm: torch.randn(2, 17, 512, generator=g) for nm in ("layer1", "layer2", "norm")}
+    with torch.no_grad():
+        m.norm.weight.mul_(1.5); m.norm.bias.add_(0.25); m.layer1.norm.weight.mul_(0.5)
+    seen = []
+    handles = [m._norm_module(nm).register_forward_hook(lambda mod, inp, out: seen.append((mod, inp[0], out))) for nm in ("layer1", "norm")]
+    assert m._hooked_norms() == ["layer1", "norm"]
+    training.fire_hooks_no_graph(m, m._hooked_norms(), h)
+    assert [s_[0] for s_ in seen] == [m.layer1.norm, m.norm]
+    for (mod, inp, out), nm in zip(seen, ("layer1", "norm")):
+        assert inp is h[nm] and not out.requires_grad
+        _close(out, F.layer_norm(h[nm].double(), (512,), mod.weight.double(), mod.bias.double(), 1e-5), 1e-5, nm)
+    for hd in handles:
+        hd.remove()
+    m.norm.register_forward_hook(lambda mod, inp, out: out * 2)
+    with pytest.raises(NotImplementedError, match="replacement"):
+        training.fire_hooks_no_graph(m, ["norm"], h)

@@ -75,19 +75,27 @@ def test_forward_argument_contract_and_no_cpu_fallback():
 
 
 def test_hooks_on_the_gradcam_layers_are_never_skipped_silently():
-    """train_loop.py:87 hooks model.layer2.norm.  Forward hooks are served by the autograd path (tests/test_backward_emu.py,
-    tests/test_zzz_gradcam_hooks_gpu.py); without autograd, or for other hook kinds, the forward says so instead of skipping them."""
+    """train_loop.py:87 hooks model.layer2.norm, visualize_mil.py:227 the final model.norm.  Forward hooks are served by the autograd
+    path (tests/test_backward_emu.py, tests/test_zzz_gradcam_hooks_gpu.py) or, without a graph, fired with the kept activations;
+    other hook kinds make the forward say so instead of skipping them."""
     import transmil_b200 as T
     m = build_model(2, 512)
-    handle = m.layer2.norm.register_forward_hook(lambda mod, inp, out: None)
-    with torch.no_grad(), pytest.raises(NotImplementedError, match="layer2.norm"):
-        m(torch.zeros(1, 10, 512))
-    if not torch.cuda.is_available():
-        with pytest.raises(T.capi.TransmilError, match="no CPU path"):      # autograd on: routed to the (CUDA-only) training path
-            m(torch.zeros(1, 10, 512))
-    handle.remove()
+    for norm, name in ((m.layer2.norm, "layer2"), (m.layer1.norm, "layer1"), (m.norm, "norm")):
+        handle = norm.register_forward_hook(lambda mod, inp, out: None)
+        assert m._hooked_norms() == [name]
+        if not torch.cuda.is_available():
+            with pytest.raises(T.capi.TransmilError, match="no CPU path"):      # autograd on: routed to the (CUDA-only) training path
+                m(torch.zeros(1, 10, 512))
+            with torch.no_grad(), pytest.raises(T.capi.TransmilError, match="no CPU path"):   # no graph: the inference path, hooks fired
+                m(torch.zeros(1, 10, 512))
+        handle.remove()
+    assert m._hooked_norms() == []
     handle = m.layer1.norm.register_forward_pre_hook(lambda mod, inp: None)
     with pytest.raises(NotImplementedError, match="only forward hooks"):
+        m(torch.zeros(1, 10, 512))
+    handle.remove()
+    handle = m.norm.register_full_backward_hook(lambda mod, gi, go: None)
+    with pytest.raises(NotImplementedError, match="only forward hooks are supported on norm"):
         m(torch.zeros(1, 10, 512))
     handle.remove()
 

@@ -531,8 +531,10 @@ class _HookedFunction(torch.autograd.Function):
         ctx.names = [n for n, _ in model._path_named_parameters()]
         ctx.hooked, ctx.P, ctx.holder = hooked, int(saved["plan"]["P"]), holder
         holder.ctx = ctx
-        holder.inputs = {"layer1": saved["h0"], "layer2": saved["h2"]}
-        acts = tuple(saved[name]["xn"][:, ctx.P:].clone() for name in hooked)
+        holder.inputs = {"layer1": saved["h0"], "layer2": saved["h2"], "norm": saved["h3"]}
+        K = _kernels_for(x)[1]
+        with _kernels_for(x)[0]:
+            acts = tuple(_final_norm(K, model, saved["h3"]) if name == "norm" else saved[name]["xn"][:, ctx.P:].clone() for name in hooked)
         return (logits,) + acts
 
     @staticmethod
@@ -561,8 +563,56 @@ class _AttachGrad(torch.autograd.Function):
         holder = ctx.holder
         main = holder.ctx
         holder.params, holder.grads = _param_grads(main, dlogits.contiguous(), keep_dxn=True)
-        dacts = tuple(holder.grads[name + "._dxn"][:, main.P:].contiguous() for name in main.hooked)
+        dacts = tuple(_final_norm_grad(main, dlogits.contiguous()) if name == "norm" else holder.grads[name + "._dxn"][:, main.P:].contiguous()
+                      for name in main.hooked)
         return (dlogits, None) + dacts
+
+
+def _layer_norm_rows(K, h, weight, bias):
+    """nn.LayerNorm(512) of every row of h [..., 512] (fp32, tm_ln_rows_fwd)."""
+    out = torch.empty_like(h)
+    K.check(K.L.tm_ln_rows_fwd(h.data_ptr(), weight.data_ptr(), bias.data_ptr(), h.numel() // DIM, DIM, out.data_ptr(), K.st))
+    return out
+
+
+def _final_norm(K, model, h3):
+    """Output of `self.norm(h)` (TransMIL.py:202) on every row: what a forward hook on the final LayerNorm sees in the reference
+    (the head kernel itself normalises the cls row only)."""
+    return _layer_norm_rows(K, h3.contiguous(), model.norm.weight.detach(), model.norm.bias.detach())
+
+
+def _final_norm_grad(main, dlogits):
+    """d(loss)/d(norm output) [B,S,512]: only the cls row reaches the classifier (TransMIL.py:202-204), row 0 = dlogits . W_fc."""
+    model, h3 = main.model, main.holder.inputs["norm"]
+    dev, K = _kernels_for(h3)
+    W = getattr(model, model.HEAD).weight.detach()
+    nc = W.shape[0]
+    B = h3.shape[0]
+    d = torch.zeros_like(h3)
+    prev = K.L.tm_bgemm_engine(1)   # a [B,nc] x [nc,512] product: the fp32 CUDA-core kernel, not tensor-core work
+    try:
+        with dev:
+            row0 = K.gemm(dlogits.float().contiguous(), (nc, 1), W, (DIM, 1), K.new(h3, B, DIM), B, DIM, nc, DIM)
+    finally:
+        K.L.tm_bgemm_engine(prev)
+    d[:, 0] = row0
+    return d
+
+
+def fire_hooks_no_graph(model, hooked, inputs):
+    """Forward hooks on `layer{1,2}.norm` / `norm` on a call without a graph (no_grad, train() under no_grad, or the eval-mode
+    `return_attn=True` call of code/visualize_mil.py:580): each hook is called as `hook(norm_module, (its input [B,S,512],),
+    LayerNorm(input) [B,S,512])`, the way torch calls it in the reference (TransMIL.py:47,202).  The activation is computed in fp32
+    from the kept layer input; the input tensor is a view of the forward's workspace, valid until the next forward."""
+    for name in hooked:
+        norm = model._norm_module(name)
+        h_in = inputs[name]
+        dev, K = _kernels_for(h_in)
+        with dev:
+            act = _layer_norm_rows(K, h_in.contiguous(), norm.weight.detach(), norm.bias.detach())
+        for hook in list(norm._forward_hooks.values()):
+            if hook(norm, (h_in,), act) is not None:
+                raise NotImplementedError("libtransmil_b200: a forward hook on %s returned a replacement output" % name)
 
 
 def forward_with_norm_hooks(model, x, hooked):
@@ -573,8 +623,8 @@ def forward_with_norm_hooks(model, x, hooked):
     outs = _HookedFunction.apply(model, x, holder, tuple(hooked), *model._path_parameters())
     logits, acts = outs[0], outs[1:]
     for name, act in zip(hooked, acts):
-        norm = getattr(model, name).norm
+        norm = model._norm_module(name)
         for hook in list(norm._forward_hooks.values()):
             if hook(norm, (holder.inputs[name],), act) is not None:
-                raise NotImplementedError("libtransmil_b200: a forward hook on %s.norm returned a replacement output" % name)
+                raise NotImplementedError("libtransmil_b200: a forward hook on %s returned a replacement output" % name)
     return _AttachGrad.apply(logits, holder, *acts)

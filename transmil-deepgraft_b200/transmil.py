@@ -210,7 +210,13 @@ class TransMIL(nn.Module):
         if x is None:
             raise TypeError("forward() needs the bag tensor (positional `x` or keyword `data`)")
         hooked = self._hooked_norms()
-        if torch.is_grad_enabled() and (self.training or self.keep_graph or hooked):
+        graph = torch.is_grad_enabled() and (self.training or self.keep_graph or bool(hooked))
+        if graph and return_attn and not (self.training or self.keep_graph):
+            # eval() + hooks + return_attn with autograd on: code/visualize_mil.py:453,580 and code/gradcam_sus.py:570 build GradCAM
+            # objects (forward hooks on a norm) and then ask for the attention of the same module.  Inference path; the hooks are
+            # fired with the kept activations (no graph on this call)
+            graph = False
+        if graph:
             # training_step (code/models/model_interface.py:333-383): forward with every stage kept + the library's backward
             # (csrc/backward.cu) behind a torch.autograd.Function; train mode applies the to_out Dropout(0.7)
             if return_attn:
@@ -233,10 +239,13 @@ class TransMIL(nn.Module):
             xd = x.detach().to(device=device, dtype=torch.float32, non_blocking=True).contiguous()
             seeds = tuple(int(s) for s in torch.randint(0, 2 ** 62, (4,)))
             with torch.cuda.device(device):
-                return training.forward_keep(self, xd, True, seeds)[0]
+                logits, saved, _w = training.forward_keep(self, xd, True, seeds)
+                if hooked:
+                    training.fire_hooks_no_graph(self, hooked, {"layer1": saved["h0"], "layer2": saved["h2"], "norm": saved["h3"]})
+            return logits
         L = capi.lib()
         B, n, D = (int(s) for s in x.shape)
-        flags = int(self.flags) | (capi.TM_FLAG_KEEP_STAGES if return_attn else 0)
+        flags = int(self.flags) | (capi.TM_FLAG_KEEP_STAGES if (return_attn or hooked) else 0)
         if getattr(self, "skip_unread_rows", False) and not return_attn:
             flags |= capi.TM_FLAG_CLS_ONLY_L2
         # fp16 feature bags (half-precision feature files) are consumed as they are: x.float() of
@@ -259,6 +268,12 @@ class TransMIL(nn.Module):
             capi.check(L.tm_transmil_fwd(C.byref(w), xd.data_ptr(), B, n, logits.data_ptr(), ws.data_ptr(),
                                          ws.numel(), flags, stream))
             self._stage_key = (B, n, flags)
+            if hooked:
+                # forward hooks on layer{1,2}.norm / norm without a graph (no_grad, or the return_attn call above): fired with the
+                # LayerNorm of the kept layer inputs, as torch fires them in the reference (TransMIL.py:47,202)
+                from . import training
+                training.fire_hooks_no_graph(self, hooked, {nm: _stage_tensor(self, ws, w, st, B, n, flags)
+                                                            for nm, st in (("layer1", "h0"), ("layer2", "h2"), ("norm", "h3"))})
         if return_attn:
             plan = capi.make_plan(n)
             attn = LazyAttention(self, ws, w, B, n, flags, plan)
@@ -266,20 +281,25 @@ class TransMIL(nn.Module):
             return logits, (attn, int(plan.padding))
         return logits
 
+    HOOK_POINTS = ("layer1", "layer2", "norm")
+
+    def _norm_module(self, name):
+        return self.norm if name == "norm" else getattr(self, name).norm
+
     def _hooked_norms(self):
         """The reference's GradCAM consumers hook `layer1.norm` / `layer2.norm` (code/train_loop.py:87,
-        code/test_visualize.py:121-127).  Those sub-modules are parameter containers here -- their forward never runs.
-        With autograd on, forward hooks on them are honoured by the training path (training.forward_with_norm_hooks:
-        activation and its gradient, which is what GradCAM reads); anything else is refused rather than silently skipped."""
+        code/test_visualize.py:121-127) or the final `norm` (code/visualize_mil.py:227, code/gradcam_sus.py).  Those sub-modules are
+        parameter containers here -- their forward never runs.  Forward hooks on them are honoured all the same: with autograd on by
+        the training path (training.forward_with_norm_hooks: activation and its gradient, which is what GradCAM reads), without a
+        graph by training.fire_hooks_no_graph (activation only, as under no_grad in the reference); any other hook kind is refused
+        rather than silently skipped."""
         hooked = []
-        for name in ("layer1", "layer2"):
-            norm = getattr(self, name).norm
+        for name in self.HOOK_POINTS:
+            norm = self._norm_module(name)
+            label = name if name == "norm" else name + ".norm"
             if norm._forward_pre_hooks or norm._backward_hooks or getattr(norm, "_backward_pre_hooks", None):
-                raise NotImplementedError(f"libtransmil_b200: only forward hooks are supported on {name}.norm")
+                raise NotImplementedError(f"libtransmil_b200: only forward hooks are supported on {label}")
             if norm._forward_hooks:
-                if not torch.is_grad_enabled():
-                    raise NotImplementedError(f"libtransmil_b200: a forward hook is registered on {name}.norm; hooks are served by "
-                                              "the autograd path only (call the model with gradients enabled, as GradCAM does)")
                 hooked.append(name)
         return hooked
 
